@@ -1,0 +1,89 @@
+"""The oracle against the reference's own outputs (tests/golden/ref_*.npz, made by
+tests/golden/make_golden.py from /root/reference) -- pins the restatement."""
+import numpy as np
+import pytest
+from scipy.sparse import csr_matrix
+
+from oracle import hypergraph_oracle as orc
+from helpers import GOLDEN_CASES, load_golden, csr_from, canon, canon_dup
+
+
+def _prep(g):
+    mq, mc, mw = g["params"]
+    row, col, count, ncol = orc.hypergraph_get_data(g["in_row"], g["in_col"], g["in_count"], g["in_mapq"],
+                                                    min_quality=int(mq))
+    n = len(g["lengths"])
+    if "remove" in g:
+        k = ~np.isin(row, g["remove"])
+        row, col, count = row[k], col[k], count[k]
+    return row, col, count, n, ncol, int(mc), float(mw)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_get_data_and_incidence(name):
+    g = load_golden(name)
+    mq = int(g["params"][0])
+    row, col, count, ncol = orc.hypergraph_get_data(g["in_row"], g["in_col"], g["in_count"], g["in_mapq"], mq)
+    assert np.array_equal(row, g["gd_row"]) and np.array_equal(col, g["gd_col"])
+    assert np.array_equal(count, g["gd_count"]) and ncol == g["gd_shape"][1]
+    row, col, count, n, ncol, mc, mw = _prep(g)
+    H, rk, ck = orc.incidence_matrix(row, col, count, n, ncol, mc)
+    Href = csr_from(g, "H")
+    assert H.shape == Href.shape
+    a = canon_dup(H); b = canon_dup(Href)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    assert np.array_equal(np.where(rk)[0], g["H_nodes_idx"])
+    if mc:
+        assert np.array_equal(np.where(~rk)[0], g["H_remove_contig_idx"])
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_clique_expansion(name):
+    g = load_golden(name)
+    mw = float(g["params"][2])
+    H = csr_from(g, "H")
+    # literal float32 replay: identical pattern; values equal up to f32 summation order
+    for key, kw in (("A", {}), ("A0", {"min_weight": 0}), ("Au", {"use_high_order": False}), ("Aw", {"W": g["W"]})):
+        kw = dict(min_weight=mw, **kw) if "min_weight" not in kw else kw
+        ref = canon(csr_from(g, key))
+        A32 = canon(orc.clique_expansion(H, dtype=np.float32, **kw))
+        assert np.array_equal(A32.indptr, ref.indptr) and np.array_equal(A32.indices, ref.indices), key
+        np.testing.assert_allclose(A32.data, ref.data, rtol=2e-6)
+        # fp64 gate vs the reference's float32 result: 1e-6 relative except entries at the threshold
+        A64 = canon(orc.clique_expansion(H, dtype=np.float64, **kw))
+        Aex = canon(orc.clique_expansion_exact(H, kw.get("use_high_order", True), kw.get("W")))
+        if kw.get("min_weight", 0) == 0:
+            assert np.array_equal(A64.indices, ref.indices)
+            np.testing.assert_allclose(A64.data, ref.data, rtol=3e-6)
+            assert np.array_equal(Aex.indices, ref.indices)
+            np.testing.assert_allclose(Aex.data, A64.data, rtol=1e-12)
+
+
+def test_toy_values():
+    g = load_golden("toy_hic")
+    A = csr_from(g, "A0").toarray()
+    assert np.array_equal(A, np.array([[6, 2, 0], [2, 3, 1], [0, 1, 1]], dtype=np.float32))
+    H = csr_from(g, "H")
+    assert np.array_equal(orc.contact_counts(H).toarray(), A.astype(np.int64))
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_normalise_filter_extract(name):
+    g = load_golden(name)
+    H = csr_from(g, "H"); A = csr_from(g, "A")
+    lengths = g["lengths"][g["H_nodes_idx"]]
+    w = orc.normalize_weight_svc(H, lengths)
+    np.testing.assert_allclose(w, g["NW_diag_sqrt"], rtol=1e-6)
+    An = canon(orc.normalize_adjacency(A, w)); ref = canon(csr_from(g, "An"))
+    assert np.array_equal(An.indices, ref.indices)
+    np.testing.assert_allclose(An.data, ref.data, rtol=1e-6)
+    assert np.array_equal(orc.filter_adjacency(A, lengths), g["filter_keep"])
+    sub, rem, kept = orc.extract_incidence_matrix2(H, g["sub_idx"])
+    ref = csr_from(g, "subH")
+    assert sub.shape == ref.shape
+    for x, y in zip(canon_dup(sub), canon_dup(ref)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(np.asarray(kept, dtype=np.int64), g["sub_kept"])
+    off = np.sort(orc.find_csr_data_offsets(A.tocsr(), g["pair_r"], g["pair_c"]))
+    assert np.array_equal(off, g["pair_offsets"])
