@@ -1,0 +1,269 @@
+// Stage 2: clique expansion  A = H diag(d) H^T  on the packed edge-major form.
+//
+// Replaces HyperGraph.clique_expansion_init (/root/reference/cphasing/algorithms/hypergraph.py:358-485):
+// scipy's two-pass single-thread csr_matmat on float32 (after a CSC->CSR transpose of the scaled H)
+// becomes one pass over the hyperedge runs.  Every entry a of a hyperedge owns the pairs (a, b) with
+// b after it in the run; the term round(c_a c_b 2^F / D_e) is added with one 64-bit integer RED to
+// the packed upper triangle of a dense accumulator (L2 resident for n <= 5.6k, HBM beyond).  Integer
+// accumulation makes the result independent of the order of the atomics (deterministic) and exact
+// for the integer contact counts (use_high_order = 0).  The diagonal never sees an atomic: it is a
+// CSR row reduction (cph_diag_terms).  A 32x32-tiled epilogue mirrors the triangle through shared
+// memory, thresholds (algorithms/hypergraph.py:453-455), optionally normalises (:590-602) and
+// emits CSR with sorted indices.
+//
+// Roofline: HBM.  Algorithmic bytes per call: 8 nnz(H) read + 12 nnz(A) + 16 (n+1) written
+// (SURVEY.md 8d); the work figure is sum_e k_e (k_e - 1) / 2 REDs.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TPB = 256;
+constexpr int TILE = 32;
+
+__device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.x + threadIdx.x; }
+
+__device__ __forceinline__ u64 tri_index(u64 i, u64 j, u64 n) {   // i <= j
+    return (i * (2 * n - i + 1)) / 2 + (j - i);
+}
+
+__device__ __forceinline__ void fill_scale(double* scale, int frac_bits) {
+    // scale[D] = 2^F / D ; D = 0 unused
+    for (int d = threadIdx.x; d < 128; d += blockDim.x) scale[d] = d ? ldexp(1.0, frac_bits) / (double)d : 0.0;
+}
+
+// warp per CSR row: rowsq[i] = sum c^2
+__global__ void __launch_bounds__(TPB) row_sq_kernel(const i64* __restrict__ indptr, const u32* __restrict__ pk, u32 n,
+                                                     u64* __restrict__ rowsq) {
+    const u32 row = (u32)(gtid() >> 5), lane = threadIdx.x & 31;
+    if (row >= n) return;
+    u64 s = 0;
+    for (i64 t = indptr[row] + lane, e = indptr[row + 1]; t < e; t += 32) {
+        u64 c = pk[t] & CPH_CNTM;
+        s += c * c;
+    }
+    s = warp_sum(s);
+    if (lane == 0) rowsq[row] = s;
+}
+
+// warp per CSR row: diag_fx[i] = sum round(c^2 w 2^F / D)
+__global__ void __launch_bounds__(TPB) diag_kernel(const i64* __restrict__ indptr, const u32* __restrict__ pk,
+                                                   const float* __restrict__ ew, u32 n, int use_high_order, int frac_bits,
+                                                   u64* __restrict__ diag) {
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    __syncthreads();
+    const u32 row = (u32)(gtid() >> 5), lane = threadIdx.x & 31;
+    if (row >= n) return;
+    u64 s = 0;
+    for (i64 t = indptr[row] + lane, e = indptr[row + 1]; t < e; t += 32) {
+        u32 p = pk[t];
+        double c = (double)(p & CPH_CNTM);
+        double sc = scale[use_high_order ? (p >> 24) : 1u];
+        if (ew) sc *= (double)ew[t];
+        s += __double2ull_rn((c * sc) * c);
+    }
+    s = warp_sum(s);
+    if (lane == 0) diag[row] = s;
+}
+
+// thread per pem entry; owns the pairs with the later entries of its hyperedge
+__global__ void __launch_bounds__(TPB) expand_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk,
+                                                     const float* __restrict__ ew, u64 nnz, u32 n, int use_high_order, int frac_bits,
+                                                     unsigned long long* __restrict__ acc) {
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t a = gtid(); a < nnz; a += stride) {
+        size_t b = a + 1;
+        if (b >= nnz) break;
+        u32 rb = pem_row[b];
+        if (rb & CPH_HEAD) continue;          // last entry of its hyperedge: owns nothing
+        const u32 pa = pem_pk[a];
+        const u64 i = pem_row[a] & CPH_ROWM;
+        double sc = scale[use_high_order ? (pa >> 24) : 1u];
+        if (ew) sc *= (double)ew[a];
+        const double fa = (double)(pa & CPH_CNTM) * sc;
+        for (;;) {
+            const u64 j = rb & CPH_ROWM;
+            const double cb = (double)(pem_pk[b] & CPH_CNTM);
+            unsigned long long v = __double2ull_rn(fa * cb);
+            u64 lo = i < j ? i : j, hi = i < j ? j : i;
+            if (i == j) v += v;   // duplicated (row, col): both orders land on the diagonal
+            atomicAdd(&acc[tri_index(lo, hi, n)], v);
+            if (++b >= nnz) break;
+            rb = pem_row[b];
+            if (rb & CPH_HEAD) break;
+        }
+    }
+}
+
+struct Epi {
+    const u64* acc;
+    const u64* diag;
+    u32 n;
+    u32 nt;
+    double inv_scale;
+    float min_weight;
+};
+
+// loads the (I, J) tile (I <= J) of the symmetric matrix into shared memory as doubles
+__device__ __forceinline__ void load_tile(const Epi& p, u32 I, u32 J, double (*t)[TILE + 1]) {
+    const u32 warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (u32 r = warp; r < TILE; r += TPB / 32) {
+        u64 i = (u64)I * TILE + r, j = (u64)J * TILE + lane;
+        double v = 0.0;
+        if (i < p.n && j < p.n) {
+            u64 raw = (i <= j) ? p.acc[tri_index(i, j, p.n)] : p.acc[tri_index(j, i, p.n)];
+            if (i == j) raw += p.diag[i];
+            v = (double)raw * p.inv_scale;
+        }
+        t[r][lane] = v;
+    }
+}
+
+__device__ __forceinline__ bool keep_entry(double v, float min_weight) {
+    // algorithms/hypergraph.py:453-455  A.data[A.data < min_weight] = 0 ; eliminate_zeros  (float32 compare)
+    if (v == 0.0) return false;
+    if (min_weight > 0.0f && (float)v < min_weight) return false;
+    return true;
+}
+
+__global__ void __launch_bounds__(TPB) epi_count_kernel(Epi p, u64* __restrict__ cnt) {
+    const u32 I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ double t[TILE][TILE + 1];
+    load_tile(p, I, J, t);
+    __syncthreads();
+    const u32 warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (u32 r = warp; r < TILE; r += TPB / 32) {
+        u32 i = I * TILE + r;
+        u32 m = __ballot_sync(0xffffffffu, keep_entry(t[r][lane], p.min_weight));
+        if (lane == 0 && i < p.n) cnt[(u64)i * p.nt + J] = __popc(m);
+        if (I != J) {
+            u32 jr = J * TILE + r;   // transposed: row jr of A, columns of tile I
+            u32 m2 = __ballot_sync(0xffffffffu, keep_entry(t[lane][r], p.min_weight));
+            if (lane == 0 && jr < p.n) cnt[(u64)jr * p.nt + I] = __popc(m2);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(TPB) epi_emit_kernel(Epi p, const u64* __restrict__ off, const double* __restrict__ node_w,
+                                                       i32* __restrict__ indices, float* __restrict__ d32, double* __restrict__ d64) {
+    const u32 I = blockIdx.y, J = blockIdx.x;
+    if (I > J) return;
+    __shared__ double t[TILE][TILE + 1];
+    load_tile(p, I, J, t);
+    __syncthreads();
+    const u32 warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const u32 lt = lanemask_lt();
+    for (u32 r = warp; r < TILE; r += TPB / 32) {
+        {
+            u32 i = I * TILE + r, j = J * TILE + lane;
+            double v = t[r][lane];
+            bool k = keep_entry(v, p.min_weight);
+            u32 m = __ballot_sync(0xffffffffu, k);
+            if (k) {
+                u64 pos = off[(u64)i * p.nt + J] + __popc(m & lt);
+                indices[pos] = (i32)j;
+                float nw = node_w ? (float)(node_w[i] * node_w[j]) : 1.0f;   // hyperpartition.py:568 NW float32
+                if (d32) d32[pos] = node_w ? (float)v * nw : (float)v;
+                if (d64) d64[pos] = node_w ? v * (double)nw : v;
+            }
+        }
+        if (I != J) {
+            u32 i = J * TILE + r, j = I * TILE + lane;
+            double v = t[lane][r];
+            bool k = keep_entry(v, p.min_weight);
+            u32 m = __ballot_sync(0xffffffffu, k);
+            if (k) {
+                u64 pos = off[(u64)i * p.nt + I] + __popc(m & lt);
+                indices[pos] = (i32)j;
+                float nw = node_w ? (float)(node_w[i] * node_w[j]) : 1.0f;
+                if (d32) d32[pos] = node_w ? (float)v * nw : (float)v;
+                if (d64) d64[pos] = node_w ? v * (double)nw : v;
+            }
+        }
+    }
+}
+
+__global__ void __launch_bounds__(TPB) epi_indptr_kernel(const u64* __restrict__ off, u32 n, u32 nt, i64* __restrict__ indptr) {
+    size_t i = gtid();
+    if (i <= n) indptr[i] = (i64)off[(u64)i * nt];   // off has n*nt + 1 entries; entry n*nt is the total
+}
+
+}  // namespace
+
+extern "C" int cph_row_sq_sums(const i64* indptr, const u32* pk, u32 n, u64* rowsq, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(indptr && rowsq && n > 0);
+    row_sq_kernel<<<grid_for((size_t)n * 32, TPB), TPB, 0, st>>>(indptr, pk, n, rowsq);
+    KERNEL_CHECK();
+    return CPH_OK;
+}
+
+extern "C" int cph_diag_terms(const i64* indptr, const u32* pk, const float* csr_entry_w, u32 n, int use_high_order, int frac_bits,
+                              u64* diag_fx, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(indptr && diag_fx && n > 0);
+    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
+    diag_kernel<<<grid_for((size_t)n * 32, TPB), TPB, 0, st>>>(indptr, pk, csr_entry_w, n, use_high_order, frac_bits, diag_fx);
+    KERNEL_CHECK();
+    return CPH_OK;
+}
+
+extern "C" int cph_expand_accumulate(const u32* pem_row, const u32* pem_pk, const float* entry_w, u64 nnz, u32 n, int use_high_order,
+                                     int frac_bits, int zero_first, u64* acc, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(acc && n > 0);
+    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
+    const size_t tri = (size_t)n * ((size_t)n + 1) / 2;
+    if (zero_first) CUDA_TRY(cudaMemsetAsync(acc, 0, tri * sizeof(u64), st));
+    if (nnz == 0) return CPH_OK;
+    ARG_CHECK(pem_row && pem_pk);
+    // persistent-ish grid: 148 SMs x 8 resident CTAs of 256 threads
+    size_t want = ceil_div(nnz, TPB);
+    unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
+    expand_kernel<<<grid, TPB, 0, st>>>(pem_row, pem_pk, entry_w, nnz, n, use_high_order, frac_bits, (unsigned long long*)acc);
+    KERNEL_CHECK();
+    return CPH_OK;
+}
+
+extern "C" int cph_expand_count(const u64* acc, const u64* diag_fx, u32 n, int frac_bits, float min_weight, u64* h_nnz, void* ws,
+                                size_t ws_bytes, size_t* h_ws_need, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(n > 0);
+    const u32 nt = (u32)ceil_div(n, TILE);
+    ARG_CHECK(nt <= 65535);
+    WS_BEGIN(ar);
+    const size_t cells = (size_t)n * nt + 1;
+    u64* cnt = ar.take<u64>(cells);
+    u64* total = ar.take<u64>(1);
+    if (!ar.dry) {
+        ARENA_CHECK(ar);
+        ARG_CHECK(acc && diag_fx && h_nnz);
+        CUDA_TRY(cudaMemsetAsync(cnt, 0, cells * sizeof(u64), st));
+        Epi p{acc, diag_fx, n, nt, ldexp(1.0, -frac_bits), min_weight};
+        epi_count_kernel<<<dim3(nt, nt), TPB, 0, st>>>(p, cnt);
+        KERNEL_CHECK();
+    }
+    TRY(scan_u64(cnt, cells, total, ar, st));
+    WS_QUERY_RETURN(ar);
+    CUDA_TRY(cudaMemcpyAsync(h_nnz, total, sizeof(u64), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return CPH_OK;
+}
+
+extern "C" int cph_expand_emit(const u64* acc, const u64* diag_fx, u32 n, int frac_bits, float min_weight, const double* node_w,
+                               const void* ws, i64* indptr, i32* indices, float* data32, double* data64, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(acc && diag_fx && ws && indptr && n > 0);
+    const u32 nt = (u32)ceil_div(n, TILE);
+    const u64* off = (const u64*)ws;   // first carve of cph_expand_count
+    Epi p{acc, diag_fx, n, nt, ldexp(1.0, -frac_bits), min_weight};
+    epi_emit_kernel<<<dim3(nt, nt), TPB, 0, st>>>(p, off, node_w, indices, data32, data64);
+    KERNEL_CHECK();
+    epi_indptr_kernel<<<grid_for((size_t)n + 1, TPB), TPB, 0, st>>>(off, n, nt, indptr);
+    KERNEL_CHECK();
+    return CPH_OK;
+}

@@ -1,0 +1,152 @@
+/* libcph -- C-ABI of the B200-native hyperpartition hot path (sm_100a).
+ *
+ * The reference (wangyibin/CPhasing, pure Python) has no FFI: the seam is its Python API
+ * (SURVEY.md 8b).  Every entry point below names the reference code it replaces
+ * (paths under /root/reference/cphasing/).  Conventions:
+ *   - plain pointers and sizes only; every non-`h_` pointer is a DEVICE pointer owned by the caller
+ *     (a torch tensor on the Python side); `h_` pointers are host memory;
+ *   - every function returns 0 (CPH_OK) or a positive CPH_ERR_* code, never throws;
+ *     cph_last_error() gives the message of the calling thread's last failure;
+ *   - no function allocates device memory: temporaries are carved from `ws` (ws_bytes big);
+ *     calling with ws == NULL returns the required size in *h_ws_need and does nothing else;
+ *   - functions that report data-dependent sizes write them to a host array and synchronise
+ *     `stream` before returning; all other functions are asynchronous on `stream`.
+ *
+ * Device formats
+ *   RAW EDGE-MAJOR (rem): the hyperedge triplets of cphasing.algorithms.hypergraph.HyperEdges
+ *     (algorithms/hypergraph.py:100-123) ordered by (col, arrival), i.e. the CSC view of H:
+ *       rem_row[t]   uint32  contig index | (1u<<31 if t is the first entry of its hyperedge)
+ *       rem_col[t]   uint32  hyperedge (read / pair) id
+ *       rem_count[t] uint32  alignment count      rem_mapq[t] int8  max MAPQ
+ *   PACKED EDGE-MAJOR (pem): two uint32 per entry after the row/column filters:
+ *       pem_row = new row index | head bit   pem_pk = (D_e << 24) | count,  count < 2^24,
+ *       D_e = max(int8(k_e) - 1, 1), the reference's hyperedge degree term (algorithms/hypergraph.py:385,418)
+ *   CSR of H (contig-major): indptr int64[n+1], indices int32 (renumbered hyperedge id), pk uint32 (same .y)
+ *   ACC: packed upper triangle (i<=j) of A as unsigned 64-bit fixed point with `frac_bits` fraction bits:
+ *       acc[i*(2n-i+1)/2 + (j-i)]
+ */
+#ifndef CPH_H
+#define CPH_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CPH_OK 0
+#define CPH_ERR_CUDA 1
+#define CPH_ERR_ARG 2
+#define CPH_ERR_WORKSPACE 3
+#define CPH_ERR_TOO_LARGE 4
+#define CPH_ERR_NOT_CONVERGED 5
+
+#define CPH_ROW_MASK 0x7fffffffu
+#define CPH_HEAD_BIT 0x80000000u
+#define CPH_COUNT_MASK 0x00ffffffu
+
+typedef void* cph_stream_t; /* cudaStream_t */
+
+int cph_version(void);
+const char* cph_last_error(void);
+/* number of kernel launches issued by this library on the calling process so far */
+uint64_t cph_launch_count(void);
+
+/* ---- stage 1a: Hi-C pairs -> raw edge-major -------------------------------------------------
+ * Replaces Extractor.generate_edges (hypergraph.py:895-1300): mapq filter (:970-971), both-ends
+ * edge filter (:977-992), col = running number of the surviving pairs (:1031), two triplets per
+ * pair with count 1 (:1033-1044, 1287-1292).  Outputs need capacity 2*n_pairs.
+ * h_counts[0] = nnz (2 * surviving pairs), h_counts[1] = number of columns. */
+int cph_pairs_to_edges(const uint32_t* chrom1, const uint32_t* chrom2, const int8_t* mapq,
+                       const uint32_t* pos1, const uint32_t* pos2, const int64_t* contig_len,
+                       uint64_t n_pairs, uint32_t n_contigs, int min_mapq, uint64_t edge_length,
+                       uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
+                       uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* ---- stage 1b: Pore-C alignment records -> raw edge-major -----------------------------------
+ * Replaces process_pore_c_table (hypergraph.py:1395-1481) + the mapq filter of
+ * _load_and_filter_single (:1774-1775): edge filter (:1438-1457), distinct-contig order filter
+ * (:1461-1468), group_by(read, contig) -> count, max(mapq) (:1470-1477); read ids are shifted by
+ * `read_offset` (generate_edges :1871-1875).  start/end/contig_len may be NULL when edge_length==0.
+ * `sorted_by_read` != 0 promises read_idx is non-decreasing (skips the global sort).
+ * Outputs need capacity n_records.  h_counts[0] = nnz, h_counts[1] = max col + 1 (0 if empty). */
+int cph_porec_to_edges(const uint32_t* read_idx, const uint32_t* contig_idx, const int8_t* mapq,
+                       const uint32_t* start, const uint32_t* end, const int64_t* contig_len,
+                       uint64_t n_records, uint32_t n_contigs, int min_mapq, uint32_t min_order,
+                       uint32_t max_order, uint64_t edge_length, uint32_t read_offset, int sorted_by_read,
+                       uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
+                       uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* ---- HyperEdges wire order <-> raw edge-major --------------------------------------------------
+ * cph_edges_to_triplets: the `sort by chrom_idx` + casts of generate_edges (hypergraph.py:1877-1889,
+ * 1044): (row, col, count, mapq) sorted by (row, col).
+ * cph_triplets_to_edges: the inverse, for HyperEdges that arrive from the host (.hg files,
+ * algorithms/hypergraph.py:66-79) or from scipy CSR matrices; input order is free. */
+int cph_edges_to_triplets(const uint32_t* rem_row, const uint32_t* rem_col, const uint32_t* rem_count,
+                          const int8_t* rem_mapq, uint64_t nnz, uint32_t n_contigs,
+                          int32_t* row, int32_t* col, uint32_t* count, int8_t* mapq,
+                          void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+int cph_triplets_to_edges(const int32_t* row, const int32_t* col, const uint32_t* count, const int8_t* mapq,
+                          uint64_t nnz, uint32_t n_cols,
+                          uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
+                          void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* ---- stage 1c: filters + incidence matrix ------------------------------------------------------
+ * cph_row_sums: per-contig sum of counts over the entries that pass the HyperGraph.get_data mapq
+ * filter (algorithms/hypergraph.py:175-184; disabled when rem_mapq == NULL) and whose contig is not
+ * flagged in row_drop (remove_rows :207-223; may be NULL): the `matrix.sum(axis=1)` of :287.
+ * rowsum (uint64[n_contigs]) is overwritten.  `packed` != 0: counts carry D_e in the top byte. */
+int cph_row_sums(const uint32_t* rem_row, const uint32_t* rem_count, const int8_t* rem_mapq, uint64_t nnz,
+                 uint32_t n_contigs, int min_mapq, const uint8_t* row_drop, int packed,
+                 uint64_t* rowsum, cph_stream_t stream);
+
+/* cph_incidence_build: HyperGraph.incidence_matrix (algorithms/hypergraph.py:249-314) and
+ * extract_incidence_matrix2 (:938-954) on the edge-major form.  row_map[c] = new row of contig c or
+ * -1 to drop it; entries with mapq < min_mapq are dropped when rem_mapq != NULL; a hyperedge
+ * survives when the summed count of its surviving entries >= col_min_sum (2 in the reference; 0
+ * keeps every hyperedge AND the original column ids, the `min_contacts=0` branch :309-311).
+ * With packed != 0 the input is itself a pem (rem_row = pem_row, rem_count = pem_pk, rem_col may be
+ * NULL when col_min_sum > 0).  Outputs (capacity nnz): pem_row, pem_pk; CSR indptr[n_rows_out+1], indices, pk.
+ * h_counts[0] = nnz_out, h_counts[1] = number of columns of H. */
+int cph_incidence_build(const uint32_t* rem_row, const uint32_t* rem_col, const uint32_t* rem_count,
+                        const int8_t* rem_mapq, uint64_t nnz, uint32_t n_contigs, int min_mapq,
+                        const int32_t* row_map, uint32_t n_rows_out, uint32_t col_min_sum, int packed,
+                        uint32_t* pem_row, uint32_t* pem_pk, int64_t* indptr, int32_t* indices, uint32_t* pk,
+                        uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* float32 `data` array of the scipy csr_matrix the reference returns (:282): data[t] = count. */
+int cph_csr_counts_f32(const uint32_t* pk, uint64_t nnz, float* data, cph_stream_t stream);
+
+/* ---- stage 2: clique expansion  A = H diag(d) H^T  ----------------------------------------------
+ * Replaces HyperGraph.clique_expansion_init (algorithms/hypergraph.py:358-485): d_e = 1/D_e
+ * (use_high_order) or 1 (:385-395, 418), A_ij = sum_e d_e c_ie c_je (:432-446), entries below
+ * min_weight dropped (:453-455).  Accumulation is 64-bit fixed point (deterministic, exact for the
+ * integer contact counts); the caller picks frac_bits from cph_row_sq_sums so that nothing overflows:
+ *     frac_bits <= min(52, 61 - ceil(log2(max_i rowsq[i] + 1))).
+ * cph_row_sq_sums  : rowsq[i] = sum_e c_ie^2  (an upper bound of A_ii, hence of every A_ij)
+ * cph_diag_terms   : diag_fx[i] = sum_e round(c_ie^2 2^frac_bits / D_e)   (no atomics: CSR row reduce)
+ * cph_expand_accumulate: acc[i,j] += round(c_ie c_je 2^frac_bits / D_e) for every unordered pair of
+ *     distinct entries of a hyperedge (x2 when both entries sit on the same contig: the duplicated
+ *     (row,col) of intra-contig Hi-C pairs, :277-282).  acc is zeroed first when zero_first != 0.
+ *     entry_w (float per pem entry, constant inside a hyperedge; NULL = 1) is the W of :427-430.
+ * Between accumulate and count the caller may sum acc / diag_fx over ranks (NCCL all-reduce).
+ * cph_expand_count : thresholds and counts; leaves per-(row, column tile) offsets in ws; *h_nnz = nnz(A)
+ * cph_expand_emit  : writes CSR(A) (sorted indices); ws must be the buffer cph_expand_count filled.
+ *     node_w (double[n], may be NULL): A_ij *= float(node_w[i]*node_w[j]) -- the NW of
+ *     hyperpartition.py:554-568 applied as in normalize_adjacency_matrix (:590-602) AFTER thresholding.
+ *     data32 / data64: either may be NULL. */
+int cph_row_sq_sums(const int64_t* indptr, const uint32_t* pk, uint32_t n, uint64_t* rowsq, cph_stream_t stream);
+int cph_diag_terms(const int64_t* indptr, const uint32_t* pk, const float* csr_entry_w, uint32_t n,
+                   int use_high_order, int frac_bits, uint64_t* diag_fx, cph_stream_t stream);
+int cph_expand_accumulate(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz, uint32_t n,
+                          int use_high_order, int frac_bits, int zero_first, uint64_t* acc, cph_stream_t stream);
+int cph_expand_count(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
+                     uint64_t* h_nnz, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+int cph_expand_emit(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
+                    const double* node_w, const void* ws, int64_t* indptr, int32_t* indices,
+                    float* data32, double* data64, cph_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
