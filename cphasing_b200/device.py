@@ -1,0 +1,313 @@
+"""Device-resident stages of the hyperpartition hot path: thin Python over the libcph C-ABI.
+
+Every function takes / returns torch CUDA tensors; nothing here computes on the host beyond
+O(n_contigs) bookkeeping (row maps, frac-bit choice).  The reference-facing classes in
+``cphasing_b200.algorithms.hypergraph`` / ``cphasing_b200.hypergraph`` are built on these.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import call_ws, check, lib, ptr, stream
+
+
+def _dev(device=None):
+    if not torch.cuda.is_available():
+        raise _lib.CphError("no CUDA device: cphasing_b200 has no CPU fallback")
+    return torch.device(device if device is not None else f"cuda:{torch.cuda.current_device()}")
+
+
+def to_dev(x, dtype, device):
+    """numpy / tensor -> contiguous device tensor of `dtype` (None passes through)."""
+    if x is None:
+        return None
+    if isinstance(x, torch.Tensor):
+        return x.to(device=device, dtype=dtype, non_blocking=True).contiguous()
+    a = np.ascontiguousarray(x)
+    want = {torch.uint32: np.uint32, torch.int32: np.int32, torch.int8: np.int8, torch.int64: np.int64,
+            torch.float32: np.float32, torch.float64: np.float64, torch.uint8: np.uint8}[dtype]
+    if a.dtype != want:
+        a = a.astype(want)
+    return torch.from_numpy(a).to(device, non_blocking=True)
+
+
+@dataclass
+class RawEdges:
+    """RAW EDGE-MAJOR triplets (include/cph.h): the CSC view of H, hyperedge runs marked by a head bit."""
+    row: torch.Tensor      # uint32 contig | head bit
+    col: torch.Tensor      # uint32 hyperedge id
+    count: torch.Tensor    # uint32
+    mapq: torch.Tensor     # int8 (or None)
+    nnz: int
+    n_cols: int            # max col + 1
+    n_contigs: int
+
+    def trimmed(self):
+        k = self.nnz
+        return RawEdges(self.row[:k], self.col[:k], self.count[:k], None if self.mapq is None else self.mapq[:k],
+                        k, self.n_cols, self.n_contigs)
+
+
+@dataclass
+class DeviceH:
+    """Filtered incidence matrix on the device in both orders (packed edge-major + CSR)."""
+    pem_row: torch.Tensor   # uint32 [nnz]  new row | head bit
+    pem_pk: torch.Tensor    # uint32 [nnz]  D_e<<24 | count
+    indptr: torch.Tensor    # int64 [n+1]
+    indices: torch.Tensor   # int32 [nnz]
+    pk: torch.Tensor        # uint32 [nnz]
+    nnz: int
+    n_rows: int
+    n_cols: int
+    row_keep: torch.Tensor  # bool [n_contigs] which input contigs survived (None = all)
+    rowsum: torch.Tensor    # uint64-as-int64 [n_contigs] summed counts before the row filter
+    pem_col: torch.Tensor = None   # uint32 [nnz] hyperedge id per pem entry; only set when columns keep their ids
+
+    @property
+    def device(self):
+        return self.pem_row.device
+
+    def counts_f32(self):
+        out = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
+        check(lib().cph_csr_counts_f32(ptr(self.pk), self.nnz, ptr(out), stream()))
+        return out
+
+
+@dataclass
+class DeviceCSR:
+    indptr: torch.Tensor    # int64 [n+1]
+    indices: torch.Tensor   # int32 [nnz]
+    data32: torch.Tensor    # float32 or None
+    data64: torch.Tensor    # float64 or None
+    n: int
+    nnz: int
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 1: tables -> raw edge-major
+# ------------------------------------------------------------------------------------------------
+def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, contig_len=None, min_mapq=1,
+                   min_order=2, max_order=50, edge_length=0, read_offset=0, device=None) -> RawEdges:
+    dev = _dev(device)
+    r = to_dev(read_idx, torch.uint32, dev)
+    c = to_dev(contig_idx, torch.uint32, dev)
+    q = to_dev(mapq, torch.int8, dev)
+    N = r.numel()
+    if edge_length:
+        st = to_dev(start, torch.uint32, dev); en = to_dev(end, torch.uint32, dev)
+        ln = to_dev(contig_len, torch.int64, dev)
+    else:
+        st = en = ln = None
+    cap = max(N, 1)
+    o_row = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_col = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
+    h = (C.c_uint64 * 2)()
+    call_ws("cph_porec_to_edges", dev, ptr(r), ptr(c), ptr(q), ptr(st), ptr(en), ptr(ln), N, int(n_contigs),
+            int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0,
+            ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+
+
+def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig_len=None, min_mapq=1,
+                   edge_length=0, device=None) -> RawEdges:
+    dev = _dev(device)
+    c1 = to_dev(chrom1, torch.uint32, dev)
+    c2 = to_dev(chrom2, torch.uint32, dev)
+    q = to_dev(mapq, torch.int8, dev)
+    P = c1.numel()
+    if edge_length:
+        p1 = to_dev(pos1, torch.uint32, dev); p2 = to_dev(pos2, torch.uint32, dev)
+        ln = to_dev(contig_len, torch.int64, dev)
+    else:
+        p1 = p2 = ln = None
+    cap = max(2 * P, 2)
+    o_row = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_col = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
+    h = (C.c_uint64 * 2)()
+    call_ws("cph_pairs_to_edges", dev, ptr(c1), ptr(c2), ptr(q), ptr(p1), ptr(p2), ptr(ln), P, int(n_contigs),
+            int(min_mapq), int(edge_length or 0), ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+
+
+def edges_to_triplets(e: RawEdges):
+    """-> (row i32, col i32, count u32, mapq i8) device tensors in HyperEdges wire order (row, col)."""
+    dev = e.row.device
+    k = e.nnz
+    row = torch.empty(k, dtype=torch.int32, device=dev)
+    col = torch.empty(k, dtype=torch.int32, device=dev)
+    cnt = torch.empty(k, dtype=torch.uint32, device=dev)
+    mq = torch.empty(k, dtype=torch.int8, device=dev) if e.mapq is not None else None
+    call_ws("cph_edges_to_triplets", dev, ptr(e.row), ptr(e.col), ptr(e.count), ptr(e.mapq), k, int(e.n_contigs),
+            ptr(row), ptr(col), ptr(cnt), ptr(mq))
+    return row, col, cnt, mq
+
+
+def triplets_to_edges(row, col, count, mapq, n_contigs, n_cols=None, device=None) -> RawEdges:
+    """HyperEdges wire triplets (any order) -> raw edge-major."""
+    dev = _dev(device)
+    r = to_dev(row, torch.int32, dev)
+    c = to_dev(col, torch.int32, dev)
+    cnt = to_dev(count, torch.uint32, dev)
+    mq = to_dev(mapq, torch.int8, dev) if mapq is not None and len(mapq) == len(row) else None
+    k = r.numel()
+    if n_cols is None:
+        n_cols = int(c.max().item()) + 1 if k else 1
+    o_row = torch.empty(max(k, 1), dtype=torch.uint32, device=dev)
+    o_col = torch.empty(max(k, 1), dtype=torch.uint32, device=dev)
+    o_cnt = torch.empty(max(k, 1), dtype=torch.uint32, device=dev)
+    o_mq = torch.empty(max(k, 1), dtype=torch.int8, device=dev) if mq is not None else None
+    call_ws("cph_triplets_to_edges", dev, ptr(r), ptr(c), ptr(cnt), ptr(mq), k, int(max(n_cols, 1)),
+            ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq))
+    return RawEdges(o_row, o_col, o_cnt, o_mq, k, int(n_cols), int(n_contigs)).trimmed()
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 1c: filters + incidence matrix
+# ------------------------------------------------------------------------------------------------
+def row_sums(e, min_mapq=0, row_drop=None, use_mapq=True, packed=False):
+    """per-contig summed count (uint64 bits in an int64 tensor): matrix.sum(axis=1) of
+    algorithms/hypergraph.py:287 over the entries get_data (:175-184) / remove_rows (:207-223) keep."""
+    dev = e.row.device
+    out = torch.empty(e.n_contigs, dtype=torch.int64, device=dev)
+    mq = e.mapq if (use_mapq and min_mapq > 0 and e.mapq is not None) else None
+    check(lib().cph_row_sums(ptr(e.row), ptr(e.count), ptr(mq), e.nnz, e.n_contigs, int(min_mapq), ptr(row_drop),
+                             int(packed), ptr(out), stream()))
+    return out
+
+
+def incidence(e: RawEdges, min_contacts=1, min_mapq=0, row_drop=None, mapq_filter=True, rowsum_hook=None) -> DeviceH:
+    """HyperGraph.get_data + remove_rows + incidence_matrix (algorithms/hypergraph.py:162-314).
+
+    row_drop: uint8[n_contigs] flags of contigs removed by remove_rows (or None).
+    rowsum_hook: callable applied to the row-sum tensor before the min_contacts test (the multi-GPU
+    path all-reduces it across concatemer shards here).
+    """
+    dev = e.row.device
+    n = e.n_contigs
+    use_mq = bool(mapq_filter and min_mapq > 0 and e.mapq is not None and e.nnz > 1)   # :175
+    rs = row_sums(e, min_mapq, row_drop, use_mq)
+    if rowsum_hook is not None:
+        rs = rowsum_hook(rs)
+    if min_contacts:
+        keep = rs >= int(np.ceil(min_contacts))                                          # :287
+        col_min = 2                                                                      # :305
+    else:
+        keep = torch.ones(n, dtype=torch.bool, device=dev)
+        col_min = 0
+    if row_drop is not None:
+        # removed rows stay in the matrix as empty rows unless min_contacts drops them (:207-223 keeps nodes)
+        live = row_drop == 0
+    else:
+        live = None
+    new_id = torch.cumsum(keep.to(torch.int32), 0, dtype=torch.int32) - 1
+    row_map = torch.where(keep if live is None else (keep & live), new_id, torch.full_like(new_id, -1))
+    n_rows = int(keep.sum().item())
+    return _incidence_build(e.row, e.col, e.count, e.mapq if use_mq else None, e.nnz, n, min_mapq if use_mq else 0,
+                            row_map, n_rows, col_min, False, keep, rs, e.n_cols)
+
+
+def _incidence_build(row, col, count, mapq, nnz, n_contigs, min_mapq, row_map, n_rows, col_min, packed, keep, rs,
+                     n_cols_in):
+    dev = row.device
+    cap = max(nnz, 1)
+    pem_row = torch.empty(cap, dtype=torch.uint32, device=dev)
+    pem_pk = torch.empty(cap, dtype=torch.uint32, device=dev)
+    indptr = torch.empty(n_rows + 1, dtype=torch.int64, device=dev)
+    indices = torch.empty(cap, dtype=torch.int32, device=dev)
+    pk = torch.empty(cap, dtype=torch.uint32, device=dev)
+    h = (C.c_uint64 * 2)()
+    call_ws("cph_incidence_build", dev, ptr(row), ptr(col), ptr(count), ptr(mapq), nnz, int(n_contigs), int(min_mapq),
+            ptr(row_map), int(n_rows), int(col_min), int(packed), ptr(pem_row), ptr(pem_pk), ptr(indptr), ptr(indices),
+            ptr(pk), h)
+    k = int(h[0])
+    n_cols = int(h[1]) if col_min > 0 else int(n_cols_in)
+    return DeviceH(pem_row[:k], pem_pk[:k], indptr, indices[:k], pk[:k], k, int(n_rows), n_cols, keep, rs)
+
+
+def sub_incidence(H: DeviceH, idx, col_min=2) -> DeviceH:
+    """extract_incidence_matrix2 (algorithms/hypergraph.py:938-954): rows `idx` (in that order) of H,
+    hyperedges whose remaining summed count <= 1 dropped and renumbered."""
+    dev = H.device
+    idx_t = to_dev(np.asarray(idx, dtype=np.int64), torch.int64, dev)
+    row_map = torch.full((H.n_rows,), -1, dtype=torch.int32, device=dev)
+    row_map[idx_t] = torch.arange(idx_t.numel(), dtype=torch.int32, device=dev)
+    return _incidence_build(H.pem_row, None, H.pem_pk, None, H.nnz, H.n_rows, 0, row_map, int(idx_t.numel()), col_min,
+                            True, None, None, H.n_cols)
+
+
+# ------------------------------------------------------------------------------------------------
+# stage 2: clique expansion
+# ------------------------------------------------------------------------------------------------
+def choose_frac_bits(H: DeviceH):
+    rowsq = torch.empty(H.n_rows, dtype=torch.int64, device=H.device)
+    check(lib().cph_row_sq_sums(ptr(H.indptr), ptr(H.pk), H.n_rows, ptr(rowsq), stream()))
+    mx = int(rowsq.max().item()) if H.n_rows else 0
+    return max(0, min(52, 61 - int(mx + 1).bit_length())), mx
+
+
+@dataclass
+class Accumulator:
+    acc: torch.Tensor       # int64 (uint64 bits) packed upper triangle
+    diag: torch.Tensor      # int64 (uint64 bits) [n]
+    n: int
+    frac_bits: int
+    use_high_order: bool
+
+
+def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w=None, frac_bits=None,
+                      acc=None) -> Accumulator:
+    """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446)."""
+    dev = H.device
+    n = H.n_rows
+    if frac_bits is None:
+        frac_bits, _ = choose_frac_bits(H)
+        if not use_high_order and entry_w is None:
+            frac_bits = 0            # pure integer contact counts: bit-exact
+    tri = n * (n + 1) // 2
+    zero = acc is None
+    if acc is None:
+        acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
+    diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
+    check(lib().cph_diag_terms(ptr(H.indptr), ptr(H.pk), ptr(csr_entry_w), n, int(use_high_order), int(frac_bits),
+                               ptr(diag), stream()))
+    check(lib().cph_expand_accumulate(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, n, int(use_high_order),
+                                      int(frac_bits), int(zero), ptr(acc), stream()))
+    return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
+
+
+def expand_emit(a: Accumulator, min_weight=0.1, node_w=None, want32=True, want64=True) -> DeviceCSR:
+    """threshold (:453-455), optional w_i w_j normalisation (:590-602), CSR emit."""
+    dev = a.acc.device
+    n = a.n
+    need = C.c_size_t(0)
+    hn = C.c_uint64(0)
+    fn = lib().cph_expand_count
+    check(fn(ptr(a.acc), ptr(a.diag), n, a.frac_bits, float(min_weight), C.byref(hn), None, 0, C.byref(need), None))
+    ws = torch.empty(need.value, dtype=torch.uint8, device=dev)     # private: emit reads it back
+    check(fn(ptr(a.acc), ptr(a.diag), n, a.frac_bits, float(min_weight), C.byref(hn), ptr(ws), ws.numel(),
+             C.byref(need), stream()))
+    nnz = int(hn.value)
+    indptr = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    indices = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)
+    d32 = torch.empty(max(nnz, 1), dtype=torch.float32, device=dev) if want32 else None
+    d64 = torch.empty(max(nnz, 1), dtype=torch.float64, device=dev) if want64 else None
+    nw = to_dev(node_w, torch.float64, dev) if node_w is not None else None
+    check(lib().cph_expand_emit(ptr(a.acc), ptr(a.diag), n, a.frac_bits, float(min_weight), ptr(nw), ptr(ws),
+                                ptr(indptr), ptr(indices), ptr(d32), ptr(d64), stream()))
+    return DeviceCSR(indptr, indices[:nnz], None if d32 is None else d32[:nnz], None if d64 is None else d64[:nnz],
+                     n, nnz)
+
+
+def clique_expansion(H: DeviceH, use_high_order=True, min_weight=0.1, node_w=None, entry_w=None, csr_entry_w=None,
+                     want32=True, want64=True):
+    acc = expand_accumulate(H, use_high_order, entry_w, csr_entry_w)
+    return expand_emit(acc, min_weight, node_w, want32, want64), acc

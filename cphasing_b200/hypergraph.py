@@ -1,0 +1,199 @@
+"""Drop-in for ``cphasing.hypergraph``: ``Extractor`` (4DN pairs) and ``HyperExtractor`` (Pore-C
+tables) -> ``HyperEdges`` (reference: cphasing/hypergraph.py:621-1306, 1395-1911).
+
+Text decoding (gzip / TSV -> columns) stays on the host, as SURVEY.md 8(a1) scopes it; the name ->
+index join is a pandas categorical lookup; every filter, the per-read order filter, the
+``group_by(read, contig)`` and the sort by contig run on the device (csrc/edges.cu).  Both classes
+also accept in-memory columnar input (``from_arrays``), which is what bench.py's end-to-end leg and
+the parity tests use.  HCR-BED filtering and contig splitting are host-side pre-filters in the
+reference (hypergraph.py:786-893, 1406-1424) and are not re-implemented here (out of scope, 8(a1)).
+"""
+from __future__ import annotations
+
+import logging
+import sys
+
+import msgspec
+import numpy as np
+import pandas as pd
+import torch
+
+from . import device as D
+from .algorithms.hypergraph import HyperEdges, LazyTriplets, numpy_enc_hook
+
+logger = logging.getLogger(__name__)
+
+
+def _edges_from_raw(raw: D.RawEdges, contig_idx, contigsizes, lazy=True):
+    """RawEdges -> HyperEdges in the reference's wire order (sorted by row, hypergraph.py:1877-1889, 1044)."""
+    cache = {}
+
+    def trip(i):
+        def get():
+            if "t" not in cache:
+                cache["t"] = D.edges_to_triplets(raw)
+            return cache["t"][i]
+        return get
+    cols = (LazyTriplets(trip(0), raw.nnz, np.int32), LazyTriplets(trip(1), raw.nnz, np.int32),
+            LazyTriplets(trip(2), raw.nnz, np.uint32), LazyTriplets(trip(3), raw.nnz, np.int8))
+    if not lazy:
+        cols = tuple(np.asarray(c) for c in cols)
+    e = HyperEdges(idx=contig_idx, row=cols[0], col=cols[1], count=cols[2], contigsizes=contigsizes, mapq=cols[3])
+    e._raw = raw
+    return e
+
+
+def _materialise(edges):
+    for f in ("row", "col", "count", "mapq"):
+        v = getattr(edges, f)
+        if isinstance(v, LazyTriplets):
+            setattr(edges, f, np.asarray(v))
+    return edges
+
+
+def _save(edges, output):
+    _materialise(edges)
+    with open(output, "wb") as out:
+        out.write(msgspec.msgpack.encode(edges, enc_hook=numpy_enc_hook))      # hypergraph.py:1302-1306, 1907-1911
+    logger.info(f"Successful output graph into `{output}`")
+
+
+def _lengths(contig_idx, contigsizes):
+    n = len(contig_idx)
+    ln = np.zeros(n, dtype=np.int64)
+    for c, i in contig_idx.items():
+        ln[i] = int(contigsizes.get(c, 0)) if hasattr(contigsizes, "get") else int(contigsizes[c])
+    return ln
+
+
+def _name_codes(series, contig_idx):
+    """contig names -> index (n_contigs for names outside the index: the inner join of :1435 drops them)."""
+    cat = pd.Categorical(series)
+    lut = np.array([contig_idx.get(c, len(contig_idx)) for c in cat.categories], dtype=np.uint32)
+    codes = np.asarray(cat.codes)
+    out = np.where(codes >= 0, lut[np.maximum(codes, 0)], len(contig_idx)).astype(np.uint32)
+    return out
+
+
+class HyperExtractor:
+    """hypergraph.py:1483-1911."""
+
+    def __init__(self, pore_c_table_pathes, contig_idx, contigsizes, min_order=2, max_order=50, min_alignments=30,
+                 min_quality=1, edge_length=2e6, split_length=None, split_contig_boundarys=None, hcr_bed=None,
+                 hcr_invert=False, threads=4, is_parquet=False, log_dir="logs", _tables=None):
+        if split_length or hcr_bed:
+            raise NotImplementedError("contig splitting / HCR BED pre-filters are host-side steps outside the "
+                                      "accelerated path (SURVEY.md 8a1)")
+        self.pore_c_table_pathes = list(pore_c_table_pathes) if pore_c_table_pathes is not None else []
+        self.contig_idx = contig_idx
+        self.contigsizes = contigsizes
+        self.min_order, self.max_order = int(min_order), int(max_order)
+        self.min_quality = int(min_quality)
+        self.edge_length = int(edge_length) if edge_length else 0
+        self.threads = threads
+        self.is_parquet = is_parquet
+        tables = _tables if _tables is not None else [self._load(p) for p in self.pore_c_table_pathes]
+        self.edges = self.generate_edges(tables)
+
+    @classmethod
+    def from_arrays(cls, read_idx, contig_idx_col, mapq, contig_idx, contigsizes, start=None, end=None, **kw):
+        """in-memory columnar input: one table of (read_idx u32, contig index u32, mapq i8[, start, end])."""
+        t = {"read_idx": read_idx, "contig": contig_idx_col, "mapq": mapq, "start": start, "end": end}
+        return cls(None, contig_idx, contigsizes, _tables=[t], **kw)
+
+    def _load(self, path):
+        # porec table columns (hypergraph.py:1500-1504, 1706-1717): read_idx(0) chrom(5) start(6) end(7) mapq(8)
+        if self.is_parquet:
+            df = pd.read_parquet(path, columns=["read_idx", "chrom", "start", "end", "mapping_quality"])
+            df.columns = ["read_idx", "chrom", "start", "end", "mapq"]
+        else:
+            try:
+                df = pd.read_csv(path, sep="\t", header=None, comment="#", usecols=[0, 5, 6, 7, 8],
+                                 names=["read_idx", "chrom", "start", "end", "mapq"],
+                                 dtype={"read_idx": np.uint32, "start": np.uint32, "end": np.uint32, "mapq": np.int8})
+            except (pd.errors.EmptyDataError, ValueError):
+                logger.error(f"The pore-c table `{path}` is empty or malformed, please check it.")   # :1621-1630
+                sys.exit(-1)
+        return {"read_idx": df["read_idx"].to_numpy(), "contig": _name_codes(df["chrom"], self.contig_idx),
+                "mapq": df["mapq"].to_numpy(), "start": df["start"].to_numpy(), "end": df["end"].to_numpy()}
+
+    def generate_edges(self, tables):
+        n = len(self.contig_idx)
+        ln = _lengths(self.contig_idx, self.contigsizes) if self.edge_length else None
+        parts = []
+        offset = 0
+        for t in tables:
+            raw = D.porec_to_edges(t["read_idx"], t["contig"], t["mapq"], n, start=t.get("start"), end=t.get("end"),
+                                   contig_len=ln, min_mapq=self.min_quality, min_order=self.min_order,
+                                   max_order=self.max_order, edge_length=self.edge_length, read_offset=offset)
+            parts.append(raw)
+            # disjoint read ids per input file (hypergraph.py:1871-1875)
+            r = t["read_idx"]
+            mx = int(r.max()) if len(r) else 0
+            offset += mx + 1
+        raw = parts[0] if len(parts) == 1 else _concat_raw(parts, n)
+        logger.info(f"Only retained Pore-C concatemer that: {self.min_order} <= contig order <= {self.max_order}.")
+        e = _edges_from_raw(raw, self.contig_idx, self.contigsizes)
+        logger.info(f"Result of {raw.nnz:,} raw hyperedges of {raw.n_cols:,} concatemers.")
+        return e
+
+    def save(self, output):
+        _save(self.edges, output)
+
+
+def _concat_raw(parts, n):
+    cat = lambda f: torch.cat([getattr(p, f) for p in parts])
+    return D.RawEdges(cat("row"), cat("col"), cat("count"), cat("mapq"), sum(p.nnz for p in parts),
+                      max(p.n_cols for p in parts), n)
+
+
+class Extractor:
+    """hypergraph.py:621-1306 (the live definition)."""
+
+    def __init__(self, pairs_pathes, contig_idx, contigsizes, min_quality=1, hcr_bed=None, hcr_invert=False, threads=4,
+                 edge_length=2e6, split_length=None, split_contig_boundarys=None, max_q0_ratio=0.0, low_memory=True,
+                 log_dir="logs", _tables=None):
+        if split_length or hcr_bed:
+            raise NotImplementedError("contig splitting / HCR BED pre-filters are host-side steps outside the "
+                                      "accelerated path (SURVEY.md 8a1)")
+        self.pairs_pathes = list(pairs_pathes) if pairs_pathes is not None else []
+        self.contig_idx = contig_idx
+        self.contigsizes = contigsizes
+        self.min_mapq = int(min_quality)
+        self.edge_length = int(edge_length) if edge_length else 0
+        tables = _tables if _tables is not None else [self._load(p) for p in self.pairs_pathes]
+        self.edges = self.generate_edges(tables)
+
+    @classmethod
+    def from_arrays(cls, chrom1, chrom2, mapq, contig_idx, contigsizes, pos1=None, pos2=None, **kw):
+        t = {"chrom1": chrom1, "chrom2": chrom2, "mapq": mapq, "pos1": pos1, "pos2": pos2}
+        return cls(None, contig_idx, contigsizes, _tables=[t], **kw)
+
+    def _load(self, path):
+        # 4DN pairs columns (hypergraph.py:904-909): chrom1(1) pos1(2) chrom2(3) pos2(4) mapq(7)
+        try:
+            df = pd.read_csv(path, sep="\t", header=None, comment="#", usecols=[1, 2, 3, 4, 7],
+                             names=["chrom1", "pos1", "chrom2", "pos2", "mapq"])
+        except (pd.errors.EmptyDataError, ValueError):
+            logger.error(f"The pairs `{path}` is empty, can not load anything, please check it.")
+            sys.exit(-1)
+        return {"chrom1": _name_codes(df["chrom1"], self.contig_idx), "chrom2": _name_codes(df["chrom2"], self.contig_idx),
+                "mapq": df["mapq"].to_numpy().astype(np.int8), "pos1": df["pos1"].to_numpy().astype(np.uint32),
+                "pos2": df["pos2"].to_numpy().astype(np.uint32)}
+
+    def generate_edges(self, tables):
+        n = len(self.contig_idx)
+        ln = _lengths(self.contig_idx, self.contigsizes) if self.edge_length else None
+        if len(tables) != 1:
+            # the reference concatenates multi-file pairs before numbering (:1160-1240); do the same on the host side
+            keys = tables[0].keys()
+            tables = [{k: (np.concatenate([np.asarray(t[k]) for t in tables]) if tables[0][k] is not None else None)
+                       for k in keys}]
+        t = tables[0]
+        raw = D.pairs_to_edges(t["chrom1"], t["chrom2"], t["mapq"], n, pos1=t.get("pos1"), pos2=t.get("pos2"),
+                               contig_len=ln, min_mapq=self.min_mapq, edge_length=self.edge_length)
+        logger.info(f"Result of {raw.nnz:,} raw hyperedges of {raw.n_cols:,} pairs.")
+        return _edges_from_raw(raw, self.contig_idx, self.contigsizes)
+
+    def save(self, output):
+        _save(self.edges, output)

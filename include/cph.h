@@ -146,6 +146,30 @@ int cph_expand_emit(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, in
                     const double* node_w, const void* ws, int64_t* indptr, int32_t* indices,
                     float* data32, double* data64, cph_stream_t stream);
 
+/* ---- CSR(A) epilogues ------------------------------------------------------------------------------
+ * A is CSR with SORTED column indices (what cph_expand_emit writes).  Pair lists are int64 device arrays.
+ * cph_csr_find_pairs   : find_csr_data_offsets (algorithms/hypergraph.py:81-97): offsets[t] = position of
+ *                        (pair_r[t], pair_c[t]) in indices/data, or -1 when it is not a stored entry.
+ * cph_csr_reweight_pairs: stored entries addressed by the allelic list are multiplied by allelic_factor, those
+ *                        addressed by the weak list by weak_factor (a factor of 0 stores an exact 0); a pair listed
+ *                        twice is applied once and weak wins over allelic, as in the reference's fancy-index
+ *                        assignments (algorithms/hypergraph.py:464-481, 632-709 numeric branch, 1158-1170).
+ *                        mark: nnz bytes of scratch.
+ * cph_csr_scale_nodes  : normalize_adjacency_matrix (algorithms/hypergraph.py:590-602) with NW = outer(w, w) of
+ *                        hyperpartition.py:554-568 formed on the fly: data[t] *= float(w[i] * w[j]).
+ * cph_csr_abs_degree   : deg[i] = sum_j |A_ij| (algorithms/hypergraph.py:545) (diagonal skipped if skip_diag),
+ *                        diag[i] = A_ii (may be NULL). */
+int cph_csr_find_pairs(const int64_t* indptr, const int32_t* indices, uint32_t n, const int64_t* pair_r,
+                       const int64_t* pair_c, uint64_t n_pairs, int64_t* offsets, cph_stream_t stream);
+int cph_csr_reweight_pairs(const int64_t* indptr, const int32_t* indices, uint32_t n, uint64_t nnz,
+                           const int64_t* al_r, const int64_t* al_c, uint64_t n_al, float allelic_factor,
+                           const int64_t* wk_r, const int64_t* wk_c, uint64_t n_wk, float weak_factor,
+                           float* data32, double* data64, uint8_t* mark, cph_stream_t stream);
+int cph_csr_scale_nodes(const int64_t* indptr, const int32_t* indices, uint32_t n, const double* node_w,
+                        float* data32, double* data64, cph_stream_t stream);
+int cph_csr_abs_degree(const int64_t* indptr, const int32_t* indices, uint32_t n, const float* data32,
+                       const double* data64, int skip_diag, double* deg, double* diag, cph_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,256 @@
+"""GPU parity: the CUDA path (through the libcph C-ABI and the reference-facing classes) against the
+reference's golden outputs and the CPU oracle.  Integer / index work is bit-exact; weighted A is held
+to 1e-6 relative against the fp64 oracle (north_star) and 3e-6 against the reference's own float32."""
+import numpy as np
+import pytest
+from scipy.sparse import csr_matrix
+
+from helpers import GOLDEN_CASES, load_golden, csr_from, canon, canon_dup, assert_same_structure_close
+from oracle import hypergraph_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    import cphasing_b200.algorithms.hypergraph as ah
+    import cphasing_b200.hypergraph as hg
+    from cphasing_b200 import device as D, synth
+    return ah, hg, D, synth
+
+
+def _edges(ah, g):
+    n = len(g["lengths"])
+    names = [f"c{i}" for i in range(n)]
+    return ah.HyperEdges(idx={c: i for i, c in enumerate(names)}, row=g["in_row"].copy(), col=g["in_col"].copy(),
+                         count=g["in_count"].copy(), contigsizes={c: int(l) for c, l in zip(names, g["lengths"])},
+                         mapq=g["in_mapq"].copy()), names
+
+
+def _build_H(ah, g):
+    mq, mc, mw = g["params"]
+    edges, names = _edges(ah, g)
+    HG = ah.HyperGraph(edges, min_quality=int(mq), mapq_filter=True)
+    if "remove" in g:
+        HG.remove_rows([names[i] for i in g["remove"]])
+    H = HG.incidence_matrix(min_contacts=int(mc))
+    return HG, H, names
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_incidence_matches_reference(api, name):
+    ah = api[0]
+    g = load_golden(name)
+    HG, H, names = _build_H(ah, g)
+    ref = csr_from(g, "H")
+    assert H.shape == ref.shape
+    assert HG.shape == ref.shape
+    for x, y in zip(canon_dup(H), canon_dup(ref)):
+        assert np.array_equal(x, y)
+    assert H.dtype == np.float32
+    idx = {c: i for i, c in enumerate(names)}
+    assert np.array_equal(np.array([idx[c] for c in HG.nodes]), g["H_nodes_idx"])
+    if int(g["params"][1]):
+        assert np.array_equal(np.asarray(HG.remove_contig_idx), g["H_remove_contig_idx"])
+    # the triplet attributes of the reference class
+    assert np.array_equal(np.sort(HG.row), np.sort(g["gd_row"])) or "remove" in g
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+@pytest.mark.parametrize("from_host", [False, True])
+def test_clique_expansion_matches_reference(api, name, from_host):
+    ah = api[0]
+    g = load_golden(name)
+    mw = float(g["params"][2])
+    if from_host:
+        H = csr_from(g, "H")                         # plain scipy input: uploaded by clique_expansion_init
+    else:
+        _, H, _ = _build_H(ah, g)                    # device twin travels with the matrix
+    Hs = csr_from(g, "H")
+    cases = [("A", dict(min_weight=mw)), ("A0", dict(min_weight=0)), ("Au", dict(min_weight=mw, use_high_order=False))]
+    if from_host or int(g["params"][1]):
+        cases.append(("Aw", dict(min_weight=mw, W=g["W"])))
+    for key, kw in cases:
+        A = ah.HyperGraph.clique_expansion_init(H, **kw)
+        assert A.dtype == np.float32 and A.shape == (Hs.shape[0],) * 2
+        ref = csr_from(g, key)
+        thr = kw["min_weight"] if kw["min_weight"] > 0 else None
+        assert_same_structure_close(A, ref, rtol=3e-6, thr=thr)
+        # fp64 gate: 1e-6 relative against the exact fp64 oracle
+        ex = orc.clique_expansion_exact(Hs, kw.get("use_high_order", True), kw.get("W"))
+        h = ah.device_handle(A)
+        A64 = csr_matrix((h.data64.cpu().numpy(), h.indices.cpu().numpy(), h.indptr.cpu().numpy()), shape=A.shape)
+        if thr is None:
+            exc = canon(ex); exc.eliminate_zeros()
+            assert np.array_equal(canon(A64).indices, exc.indices)
+            np.testing.assert_allclose(canon(A64).data, exc.data, rtol=1e-9)
+        else:
+            E = ex.tocsr().copy(); E.data[E.data.astype(np.float32) < np.float32(thr)] = 0; E.eliminate_zeros()
+            assert_same_structure_close(A64, E, rtol=1e-6, thr=thr)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_contact_counts_bit_exact(api, name):
+    ah, _, D, _ = api
+    g = load_golden(name)
+    Hs = csr_from(g, "H")
+    dH = ah.upload_incidence(Hs)
+    A, acc = D.clique_expansion(dH, use_high_order=False, min_weight=0.0)
+    assert acc.frac_bits == 0
+    C = canon(orc.contact_counts(Hs)); C.eliminate_zeros()
+    got = csr_matrix((A.data64.cpu().numpy(), A.indices.cpu().numpy(), A.indptr.cpu().numpy()), shape=C.shape)
+    assert np.array_equal(got.indptr, C.indptr) and np.array_equal(got.indices, C.indices)
+    assert np.array_equal(got.data.astype(np.int64), C.data)      # bit-exact integers
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_normalise_reweight_extract(api, name):
+    ah = api[0]
+    g = load_golden(name)
+    A = csr_from(g, "A")
+    w = g["NW_diag_sqrt"]
+    An = ah.HyperGraph.normalize_adjacency_matrix(A, w)
+    ref = canon(csr_from(g, "An"))
+    assert np.array_equal(canon(An).indices, ref.indices)
+    np.testing.assert_allclose(canon(An).data, ref.data, rtol=1e-6)
+    # dense NW accepted too (the reference's calling convention)
+    if A.shape[0] <= 200:
+        An2 = ah.HyperGraph.normalize_adjacency_matrix(A, np.outer(w, w).astype(np.float32))
+        np.testing.assert_allclose(canon(An2).data, ref.data, rtol=2e-6)
+    # fused normalisation inside the expansion epilogue
+    H = csr_from(g, "H")
+    Af = ah.HyperGraph.clique_expansion_init(H, NW=w, min_weight=float(g["params"][2]))
+    assert_same_structure_close(Af, ref, rtol=3e-6, thr=None if float(g["params"][2]) == 0 else None)
+    # extract_incidence_matrix2
+    sub, rem, kept = ah.extract_incidence_matrix2(H, g["sub_idx"])
+    rs = csr_from(g, "subH")
+    assert sub.shape == rs.shape
+    for x, y in zip(canon_dup(sub), canon_dup(rs)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(np.asarray(kept, dtype=np.int64), g["sub_kept"])
+    # find_csr_data_offsets + IRMM-style re-weighting
+    from cphasing_b200 import graphops
+    a = graphops.upload_adjacency(A)
+    off = graphops.find_pairs(a, g["pair_r"], g["pair_c"]).cpu().numpy()
+    assert np.array_equal(np.sort(off[off >= 0]), g["pair_offsets"])
+    P = (g["pair_r"], g["pair_c"])
+    Ar = ah.HyperGraph.reweight_pairs(A, P, None, -1.0)
+    exp = canon(A).copy(); exp.data[g["pair_offsets"]] *= -1.0
+    assert np.array_equal(canon(Ar).data, exp.data)
+
+
+def _oracle_vs_device_porec(D, t, n, **kw):
+    exp = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], t.get("start"), t.get("end"), kw.pop("contig_len", None),
+                          n_contigs=n, **kw)
+    return exp
+
+
+@pytest.mark.parametrize("law,edge_length,min_mapq,shuffle", [("poisson", 0, 1, False), ("exp", 0, 0, False),
+                                                             ("poisson", 300000, 1, False), ("poisson", 0, 10, True),
+                                                             ("exp", 500000, 30, True)])
+def test_porec_edges_bit_exact(api, law, edge_length, min_mapq, shuffle):
+    _, hg, D, synth = api
+    g = synth.make_genome(150, 5, 2, seed=5)
+    t = synth.porec_table(g, 20000, seed=6, law=law)
+    if shuffle:
+        p = np.random.default_rng(1).permutation(len(t["read_idx"]))
+        t = {k: v[p] for k, v in t.items()}
+    exp = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], t["start"], t["end"], g.length, min_mapq=min_mapq,
+                          min_order=2, max_order=50, edge_length=edge_length, n_contigs=g.n)
+    raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, start=t["start"], end=t["end"],
+                           contig_len=g.length, min_mapq=min_mapq, min_order=2, max_order=50, edge_length=edge_length)
+    row, col, cnt, mq = D.edges_to_triplets(raw)
+    got = (row.cpu().numpy(), col.cpu().numpy(), cnt.view(__import__("torch").int32).cpu().numpy().view(np.uint32),
+           mq.cpu().numpy())
+    for a, b in zip(got, exp):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+    assert raw.n_cols == (int(exp[1].max()) + 1 if len(exp[1]) else 0)
+    # and through the reference-facing class
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes,
+                                       start=t["start"], end=t["end"], min_quality=min_mapq, edge_length=edge_length)
+    assert np.array_equal(np.asarray(ex.edges.row), exp[0]) and np.array_equal(np.asarray(ex.edges.count), exp[2])
+
+
+def test_porec_order_bounds_and_empty(api):
+    _, _, D, _ = api
+    # read 0: one contig twice (order 1 -> dropped); read 1: contigs 0,1 ; read 2: 3 contigs (max_order=2 -> dropped)
+    r = np.array([0, 0, 1, 1, 1, 2, 2, 2], np.uint32)
+    c = np.array([4, 4, 0, 1, 0, 1, 2, 3], np.uint32)
+    q = np.array([60, 60, 5, 60, 50, 60, 60, 60], np.int8)
+    raw = D.porec_to_edges(r, c, q, 5, min_mapq=1, min_order=2, max_order=2)
+    row, col, cnt, mq = [x.cpu().numpy() for x in D.edges_to_triplets(raw)]
+    assert row.tolist() == [0, 1] and col.tolist() == [1, 1] and cnt.view(np.uint32).tolist() == [2, 1]
+    assert mq.tolist() == [50, 60]
+    raw = D.porec_to_edges(r, c, q, 5, min_mapq=61)
+    assert raw.nnz == 0 and raw.n_cols == 0
+    raw = D.porec_to_edges(np.zeros(0, np.uint32), np.zeros(0, np.uint32), np.zeros(0, np.int8), 5)
+    assert raw.nnz == 0
+
+
+@pytest.mark.parametrize("edge_length,min_mapq", [(0, 1), (400000, 1), (0, 0)])
+def test_pairs_edges_bit_exact(api, edge_length, min_mapq):
+    _, hg, D, synth = api
+    g = synth.make_genome(80, 4, 2, seed=8)
+    t = synth.pairs_table(g, 50000, seed=9)
+    exp = orc.pairs_edges(t["chrom1"], t["chrom2"], t["mapq"], t["pos1"], t["pos2"], g.length, min_mapq=min_mapq,
+                          edge_length=edge_length, n_contigs=g.n)
+    ex = hg.Extractor.from_arrays(t["chrom1"], t["chrom2"], t["mapq"], g.contig_idx, g.contigsizes, pos1=t["pos1"],
+                                  pos2=t["pos2"], min_quality=min_mapq, edge_length=edge_length)
+    e = ex.edges
+    # duplicated (row, col) of intra-contig pairs: compare as multisets per (row, col, mapq)
+    got = np.lexsort((np.asarray(e.mapq), np.asarray(e.col), np.asarray(e.row)))
+    want = np.lexsort((exp[3], exp[1], exp[0]))
+    for a, b in zip((e.row, e.col, e.count, e.mapq), exp):
+        assert np.array_equal(np.asarray(a)[got], b[want])
+
+
+def test_hyperedges_msgpack_roundtrip(api, tmp_path):
+    ah, hg, D, synth = api
+    import msgspec
+    g = synth.make_genome(30, 3, 2, seed=3)
+    t = synth.porec_table(g, 500, seed=4)
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes, edge_length=0)
+    p = tmp_path / "x.hg"
+    ex.save(str(p))
+    e2 = msgspec.msgpack.decode(open(p, "rb").read(), type=ah.HyperEdges, dec_hook=ah.numpy_dec_hook)
+    e2.to_numpy()
+    assert np.array_equal(e2.row, np.asarray(ex.edges.row)) and e2.idx == g.contig_idx
+    H1 = ah.HyperGraph(e2, min_quality=1).incidence_matrix(5)
+    H2 = ah.HyperGraph(ex.edges, min_quality=1).incidence_matrix(5)
+    assert (H1 != H2).nnz == 0
+
+
+def test_empty_edges_raise(api):
+    ah = api[0]
+    e = ah.HyperEdges(idx={"a": 0}, row=np.zeros(0, np.int32), col=np.zeros(0, np.int32), count=np.zeros(0, np.uint32),
+                      contigsizes={"a": 10}, mapq=np.zeros(0, np.int8))
+    with pytest.raises(ValueError, match="No hyperedges found"):
+        ah.HyperGraph(e)
+
+
+def test_expansion_properties_medium(api):
+    """size-independent properties at a size the oracle does not need: symmetry, the sum identity
+    sum_ij C_ij = sum_e (sum_i c_ie)^2, and idempotence of the build."""
+    ah, hg, D, synth = api
+    import torch
+    g = synth.make_genome(1500, 6, 4, seed=41)
+    t = synth.porec_table(g, 300000, seed=42, law="exp")
+    raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=1)
+    H = D.incidence(raw, min_contacts=25)
+    A, acc = D.clique_expansion(H, use_high_order=False, min_weight=0.0)
+    M = csr_matrix((A.data64.cpu().numpy(), A.indices.cpu().numpy(), A.indptr.cpu().numpy()), shape=(A.n, A.n))
+    assert (abs(M - M.T)).nnz == 0
+    cnt = (H.pk.view(torch.int32) & 0xFFFFFF).to(torch.int64)
+    colsum = torch.zeros(H.n_cols, dtype=torch.int64, device=cnt.device).index_add_(0, H.indices.long(), cnt)
+    assert int(M.sum()) == int((colsum * colsum).sum().item())
+    A2, _ = D.clique_expansion(H, use_high_order=False, min_weight=0.0)
+    assert torch.equal(A2.data64, A.data64) and torch.equal(A2.indices, A.indices)
+    # weighted: deterministic run to run (fixed-point accumulation)
+    B1, _ = D.clique_expansion(H, use_high_order=True, min_weight=0.1)
+    B2, _ = D.clique_expansion(H, use_high_order=True, min_weight=0.1)
+    assert torch.equal(B1.data64, B2.data64)
+    Hs = ah.wrap_incidence(H)
+    ex = orc.clique_expansion_exact(csr_matrix(Hs), True)
+    E = ex.tocsr(); E.data[E.data.astype(np.float32) < np.float32(0.1)] = 0; E.eliminate_zeros()
+    B = csr_matrix((B1.data64.cpu().numpy(), B1.indices.cpu().numpy(), B1.indptr.cpu().numpy()), shape=E.shape)
+    assert_same_structure_close(B, E, rtol=1e-6, thr=0.1)
