@@ -1,0 +1,424 @@
+#!/usr/bin/env python
+"""bench.py -- the hyperpartition hot path on synthetic contact tables of BASELINE.json's shapes.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload C|B|E|A|D] [--impl reference]
+
+One "step" = one pass of the hot path over one table: contact table -> hyperedges (filters,
+group-by, order filter) -> filtered incidence matrix H -> clique expansion A = H W H^T (CSR out)
+[-> kprune scoring -> Louvain/Leiden when --full].  `value` = concatemers/s with the table already
+resident in HBM (CUDA events, max over ranks); `e2e` = the same through the reference-facing
+classes with HOST (pinned) buffers in and the scipy CSR of A out.  Prints ONE JSON line.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# workload per GPU count: N=1 -> config C (potato-scale Pore-C, 4k contigs, 50M concatemers); N>1 -> config D's
+# genome (20k contigs) with 62.5M concatemers per GPU (500M at N=8): weak scaling over concatemer shards.
+PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight=2.0)   # cphasing/_config.py:38-45
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default=None, help="A|B|C|D|E (default: C at 1 GPU, D-shaped shards at N>1)")
+    ap.add_argument("--m", type=int, default=None, help="override the number of concatemers per GPU")
+    ap.add_argument("--cpu-sample", type=int, default=2_000_000, help="concatemers in the CPU-baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload(args):
+    from cphasing_b200 import synth
+    name = args.workload or ("C" if args.gpus == 1 else "D")
+    cfg = dict(synth.CONFIGS[name])
+    if name == "D":
+        cfg["m"] = cfg["m"] // 8                 # per GPU: 62.5M (the named 500M at 8 GPUs)
+    elif args.gpus > 1:
+        pass                                     # other shapes: every GPU takes a full-size shard
+    if args.m:
+        cfg["m"] = args.m
+    return name, cfg
+
+
+class Clocks:
+    """nvidia-smi sampler for the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.p = None
+        self.path = f"/tmp/cph_clocks_{os.getpid()}.csv"
+
+    def start(self):
+        try:
+            self.f = open(self.path, "w")
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={self.idx}", f"--query-gpu={self.Q}",
+                                       "--format=csv,noheader,nounits", "-lms", "100"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.close()
+        sm, mx, reasons = [], [], set()
+        for line in open(self.path):
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        if sm:
+            out = {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+        try:
+            os.remove(self.path)
+        except OSError:
+            pass
+        return out
+
+
+# ------------------------------------------------------------------------------------------------
+# own arm
+# ------------------------------------------------------------------------------------------------
+def gen_table(cfg, rank, dev):
+    from cphasing_b200 import synth
+    g = synth.make_genome(cfg["n"], cfg["chromosomes"], cfg["ploidy"], cfg["seed"])
+    first = rank * cfg["m"]
+    if cfg["kind"] == "pairs":
+        t = synth.pairs_table_device(g, cfg["m"], cfg["seed"], first=first, device=dev)
+    else:
+        t = synth.porec_table_device(g, cfg["m"], cfg["seed"], law=cfg["law"], first=first, device=dev)
+    return g, t
+
+
+def device_step(D, cfg, g, t, ev, world, rank):
+    """one pass with the table resident in HBM; ev: list of (name, cuda event) appended in order."""
+    import torch
+    import torch.distributed as dist
+
+    def mark(name):
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        ev.append((name, e))
+    mark("start")
+    if cfg["kind"] == "pairs":
+        raw = D.pairs_to_edges(t["chrom1"], t["chrom2"], t["mapq"], g.n, min_mapq=PARAMS["min_mapq"])
+    else:
+        raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=PARAMS["min_mapq"],
+                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"])
+    mark("edges")
+    hook = None
+    if world > 1:
+        def hook(rs):
+            dist.all_reduce(rs)          # global per-contig contact sums for the min_contacts row filter
+            return rs
+    H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0, rowsum_hook=hook)
+    mark("incidence")
+    fb = None
+    if world > 1:
+        # the fixed-point scale must agree across ranks: derive it from the global row-square bound
+        _, mx = D.choose_frac_bits(H)
+        mxt = torch.tensor([mx], dtype=torch.int64, device=H.device)
+        dist.all_reduce(mxt)
+        fb = max(0, min(52, 61 - int(mxt.item() + 1).bit_length()))
+    acc = D.expand_accumulate(H, use_high_order=True, frac_bits=fb)
+    mark("accumulate")
+    if world > 1:
+        dist.all_reduce(acc.acc)
+        dist.all_reduce(acc.diag)
+        mark("allreduce")
+    A = D.expand_emit(acc, min_weight=PARAMS["min_weight"], want32=True, want64=True)
+    mark("emit")
+    return raw, H, A
+
+
+def e2e_step(cfg, g, host, names):
+    """host (pinned) buffers -> reference-facing classes -> scipy CSR of A on the host."""
+    import torch
+    from cphasing_b200 import hypergraph as hg
+    from cphasing_b200.algorithms import hypergraph as ah
+    idx, sizes = names
+    if cfg["kind"] == "pairs":
+        ex = hg.Extractor.from_arrays(host["chrom1"], host["chrom2"], host["mapq"], idx, sizes,
+                                      min_quality=PARAMS["min_mapq"], edge_length=0)
+    else:
+        ex = hg.HyperExtractor.from_arrays(host["read_idx"], host["contig_idx"], host["mapq"], idx, sizes,
+                                           min_quality=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
+                                           max_order=PARAMS["max_order"], edge_length=0)
+    HG = ah.HyperGraph(ex.edges, min_quality=PARAMS["min_mapq"], mapq_filter=False)
+    H = HG.incidence_matrix(PARAMS["min_contacts"])
+    A = ah.HyperGraph.clique_expansion_init(H, min_weight=PARAMS["min_weight"])
+    d2h = A.data.nbytes + A.indices.nbytes + A.indptr.nbytes        # touching .data materialises the scipy CSR
+    torch.cuda.synchronize()
+    return A, d2h
+
+
+def cpu_baseline(cfg, g, t, n_sample):
+    """the oracle (numpy/scipy port of the reference path) on the first n_sample concatemers of the same
+    table, one core."""
+    import torch
+    from oracle import hypergraph_oracle as orc
+    if cfg["kind"] == "pairs":
+        k = min(n_sample, cfg["m"])
+        c1 = t["chrom1"][:k].cpu().numpy(); c2 = t["chrom2"][:k].cpu().numpy(); q = t["mapq"][:k].cpu().numpy()
+        t0 = time.perf_counter()
+        r, c, cnt, mq = orc.pairs_edges(c1, c2, q, min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
+    else:
+        rid = t["read_idx"].view(torch.int32)
+        first = int(rid[0].item())
+        k = min(n_sample, cfg["m"])
+        cut = int(torch.searchsorted(rid, torch.tensor([first + k], dtype=torch.int32, device=rid.device)).item())
+        ri = t["read_idx"][:cut].cpu().numpy(); ci = t["contig_idx"][:cut].cpu().numpy(); q = t["mapq"][:cut].cpu().numpy()
+        t0 = time.perf_counter()
+        r, c, cnt, mq = orc.porec_edges(ri, ci, q, min_mapq=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
+                                        max_order=PARAMS["max_order"], n_contigs=g.n)
+    rr, cc, kk, ncol = orc.hypergraph_get_data(r, c, cnt, mq, PARAMS["min_mapq"], mapq_filter=False)
+    H, _, _ = orc.incidence_matrix(rr, cc, kk, g.n, ncol, PARAMS["min_contacts"])
+    A = orc.clique_expansion(H, min_weight=PARAMS["min_weight"], dtype=np.float32)     # the reference's own float32 path
+    dt = time.perf_counter() - t0
+    return {"value": k / dt, "unit": "concatemers/s", "cores": 1, "kind": "port",
+            "sample": f"first {k} concatemers of the same table ({len(r)} H entries), oracle/hypergraph_oracle.py "
+                      f"(numpy+scipy restatement; polars/MKL absent), {dt:.1f} s"}, A
+
+
+def run_own(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from cphasing_b200 import _lib, device as D
+    name, cfg = workload(args)
+    g, t = gen_table(cfg, rank, dev)
+    n_rec = int(next(iter(t.values())).numel())
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        ev = []
+        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
+    barrier()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    l0 = _lib.launches()
+    all_ev = []
+    t_start = torch.cuda.Event(enable_timing=True); t_end = torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    for _ in range(args.steps):
+        ev = []
+        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
+        all_ev.append(ev)
+    t_end.record()
+    barrier()
+    launches = _lib.launches() - l0
+    ms_total = t_start.elapsed_time(t_end)
+    if world > 1:
+        mt = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms_total = float(mt.item())
+    clk = clocks.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    stages = {}
+    for ev in all_ev:
+        for (n0, e0), (n1, e1) in zip(ev[:-1], ev[1:]):
+            stages.setdefault(n1, []).append(e0.elapsed_time(e1))
+    stages = {k: sum(v) / len(v) for k, v in stages.items()}
+
+    # roofline of the clique-expansion accumulate kernel (the SpGEMM): algorithmic bytes of stage 2 that this
+    # launch moves = 8 B per H entry read (row + packed count/degree) -- SURVEY.md 8(d); its share of A is written
+    # by the emit kernels.  Pair updates (the work figure) reported beside it.
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    nnzH, nnzA, n_rows = H.nnz, A.nnz, H.n_rows
+    bytes_acc = 8 * nnzH
+    acc_ms = stages.get("accumulate", float("nan"))
+    stage1_bytes = 9 * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
+    stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
+    s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
+    s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
+    roof = {"bound": "hbm", "kernel": "expand_kernel (cph_expand_accumulate)", "achieved": bytes_acc / acc_ms / 1e6,
+            "peak": peak, "unit": "GB/s", "frac": bytes_acc / acc_ms / 1e6 / peak, "traffic": None,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+            "stage1_GBps": stage1_bytes / s1_ms / 1e6 if s1_ms else None,
+            "stage2_GBps": stage2_bytes / s2_ms / 1e6 if s2_ms else None}
+    out = {"metric": "concatemers/sec (H build + H*W*H^T)", "value": cfg["m"] * world / (ms_step / 1e3),
+           "unit": "concatemers/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 fixed-point / f64",
+           "data": "synthetic", "gpu_launches": launches,
+           "config": {"workload": f"{name}: n={cfg['n']} contigs, m={cfg['m']} concatemers/GPU x {world} GPU, law={cfg['law']}, "
+                                  f"kind={cfg['kind']}", "records_per_gpu": n_rec, "nnz_H": nnzH, "nnz_A": nnzA,
+                      "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
+                      "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
+           "stages_ms": stages, "roofline": roof, "clocks": clk}
+    if rank == 0 and world == 1 and not args.no_e2e:
+        import torch
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in t.items()}
+        names = (g.contig_idx, g.contigsizes)
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        del t
+        _lib.release_workspace(); torch.cuda.empty_cache()
+        for _ in range(2):
+            Ah, d2h = e2e_step(cfg, g, host, names)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        ne = max(2, min(args.steps, 3))
+        for _ in range(ne):
+            Ah, d2h = e2e_step(cfg, g, host, names)
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / ne
+        out["e2e"] = {"value": cfg["m"] / dt, "unit": "concatemers/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                      "ms_per_step": dt * 1e3, "api": "HyperExtractor.from_arrays -> HyperGraph.incidence_matrix -> "
+                                                      "HyperGraph.clique_expansion_init -> scipy csr (host)"}
+        t = {k: v.to(dev) for k, v in host.items()} if not args.no_cpu_baseline else None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cb, _ = cpu_baseline(cfg, g, t, args.cpu_sample)
+        out["cpu_baseline"] = cb
+    if rank == 0:
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU algorithm (oracle port; the reference itself is pure Python over
+# polars / scipy / igraph and cannot be installed or travel -- DESIGN.md) on the host cores
+# ------------------------------------------------------------------------------------------------
+def _ref_worker(conn, cfg, first, m):
+    from cphasing_b200 import synth
+    from oracle import hypergraph_oracle as orc
+    from scipy.sparse import csr_matrix
+    g = synth.make_genome(cfg["n"], cfg["chromosomes"], cfg["ploidy"], cfg["seed"])
+    if cfg["kind"] == "pairs":
+        t = synth.pairs_table(g, m, cfg["seed"], first=first)
+    else:
+        t = synth.porec_table(g, m, cfg["seed"], law=cfg["law"], first=first)
+    conn.send(("ready", len(next(iter(t.values())))))
+    st = {}
+    while True:
+        cmd = conn.recv()
+        if cmd[0] == "stop":
+            break
+        if cmd[0] == "phase1":      # table -> triplets -> local row sums
+            if cfg["kind"] == "pairs":
+                r, c, cnt, mq = orc.pairs_edges(t["chrom1"], t["chrom2"], t["mapq"], min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
+            else:
+                r, c, cnt, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=PARAMS["min_mapq"],
+                                                min_order=PARAMS["min_order"], max_order=PARAMS["max_order"], n_contigs=g.n)
+            c = c - first if len(c) else c
+            H, _, _ = orc.incidence_matrix(r, c, cnt, g.n, int(c.max()) + 1 if len(c) else 1, 0)
+            st["H"] = H
+            conn.send(np.asarray(H.sum(axis=1)).ravel())
+        elif cmd[0] == "phase2":    # global row filter, local column filter, partial A
+            keep = cmd[1]
+            H = st["H"][keep]
+            H = H[:, np.asarray(H.sum(axis=0)).ravel() >= 2]
+            A = orc.clique_expansion(H, min_weight=0, dtype=np.float32)
+            conn.send(A)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    name, cfg = workload(args)
+    cores = min(os.cpu_count() or 1, 32)
+    per = 400_000
+    m = per * cores
+    ctx = mp.get_context("spawn")
+    procs = []
+    for i in range(cores):
+        a, b = ctx.Pipe()
+        p = ctx.Process(target=_ref_worker, args=(b, cfg, i * per, per), daemon=True)
+        p.start()
+        procs.append((p, a))
+    n_rec = sum(a.recv()[1] for _, a in procs)
+
+    def step():
+        for _, a in procs:
+            a.send(("phase1",))
+        rs = sum(a.recv() for _, a in procs)
+        keep = rs >= PARAMS["min_contacts"]
+        for _, a in procs:
+            a.send(("phase2", keep))
+        A = None
+        for _, a in procs:
+            P = a.recv()
+            A = P if A is None else A + P
+        A = A.tocsr()
+        A.data[A.data < np.float32(PARAMS["min_weight"])] = 0
+        A.eliminate_zeros()
+        return A
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        A = step()
+    dt = (time.perf_counter() - t0) / args.steps
+    for p, a in procs:
+        a.send(("stop",))
+    v = m / dt
+    sample = (f"{m} concatemers ({n_rec} records) of workload {name} per step, {cores} worker processes each running "
+              f"oracle/hypergraph_oracle.py on a {per}-concatemer shard (phase 1 triplets+row sums, phase 2 partial A), "
+              f"partials summed on rank 0")
+    print(json.dumps({"impl": "reference", "metric": "concatemers/sec (H build + H*W*H^T)", "value": v, "unit": "concatemers/s",
+                      "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+                      "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (reference arithmetic)",
+                      "data": "synthetic",
+                      "config": {"workload": f"{name}: n={cfg['n']} contigs, law={cfg['law']}, kind={cfg['kind']} (bounded sample)",
+                                 "params": PARAMS},
+                      "cpu_baseline": {"value": v, "unit": "concatemers/s", "cores": cores, "kind": "port", "sample": sample},
+                      "e2e": {"value": v, "unit": "concatemers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_own(a)

@@ -128,9 +128,9 @@ class HyperExtractor:
                                    max_order=self.max_order, edge_length=self.edge_length, read_offset=offset)
             parts.append(raw)
             # disjoint read ids per input file (hypergraph.py:1871-1875)
-            r = t["read_idx"]
-            mx = int(r.max()) if len(r) else 0
-            offset += mx + 1
+            if len(tables) > 1:
+                r = np.asarray(t["read_idx"])
+                offset += (int(r.max()) if len(r) else 0) + 1
         raw = parts[0] if len(parts) == 1 else _concat_raw(parts, n)
         logger.info(f"Only retained Pore-C concatemer that: {self.min_order} <= contig order <= {self.max_order}.")
         e = _edges_from_raw(raw, self.contig_idx, self.contigsizes)

@@ -263,3 +263,64 @@ CONFIGS = {
 def genome_for(name):
     c = CONFIGS[name]
     return make_genome(c["n"], c["chromosomes"], c["ploidy"], c["seed"])
+
+
+# ---- device twins (csrc/synth.cu): the bench generates its tables straight into HBM ---------------
+_LAW = {"poisson": 0, "exp": 1, "pair": 2}
+
+
+def _genome_dev(g: Genome, dev):
+    import torch
+    glen = g.cum[g.gstart[1:]] - g.cum[g.gstart[:-1]]
+    gcum = np.concatenate(([0.0], np.cumsum(glen)))
+    t = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a.astype(dt))).to(dev)
+    return (t(g.cum, np.float64), t(gcum, np.float64), t(g.gstart, np.int32), t(g.order, np.int32), t(g.length, np.int64))
+
+
+def porec_table_device(g: Genome, m, seed, law="poisson", first=0, positions=False, device=None):
+    """dict of device tensors: read_idx u32, contig_idx u32, mapq i8 [, start u32, end u32]."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    from .device import _dev
+    dev = _dev(device)
+    L = _lib.lib()
+    off = torch.empty(m + 1, dtype=torch.int64, device=dev)
+    tot = C.c_uint64(0)
+    _lib.call_ws("cph_synth_porec_count", dev, int(seed), int(first), int(m), _LAW[law], off.data_ptr(), C.byref(tot))
+    N = int(tot.value)
+    cum, gcum, gstart, order, length = _genome_dev(g, dev)
+    out = {"read_idx": torch.empty(max(N, 1), dtype=torch.uint32, device=dev)[:N],
+           "contig_idx": torch.empty(max(N, 1), dtype=torch.uint32, device=dev)[:N],
+           "mapq": torch.empty(max(N, 1), dtype=torch.int8, device=dev)[:N]}
+    if positions:
+        out["start"] = torch.empty(max(N, 1), dtype=torch.uint32, device=dev)[:N]
+        out["end"] = torch.empty(max(N, 1), dtype=torch.uint32, device=dev)[:N]
+    _lib.check(L.cph_synth_porec_fill(int(seed), int(first), int(m), _LAW[law], g.n, g.G, g.ploidy, cum.data_ptr(),
+                                      gcum.data_ptr(), gstart.data_ptr(), order.data_ptr(), length.data_ptr(),
+                                      off.data_ptr(), out["read_idx"].data_ptr(), out["contig_idx"].data_ptr(),
+                                      out["start"].data_ptr() if positions else None,
+                                      out["end"].data_ptr() if positions else None, out["mapq"].data_ptr(), _lib.stream()))
+    torch.cuda.current_stream().synchronize()
+    return out
+
+
+def pairs_table_device(g: Genome, m, seed, first=0, intra=0.05, positions=False, device=None):
+    import torch
+    from . import _lib
+    from .device import _dev
+    dev = _dev(device)
+    cum, gcum, gstart, order, length = _genome_dev(g, dev)
+    out = {"chrom1": torch.empty(m, dtype=torch.uint32, device=dev), "chrom2": torch.empty(m, dtype=torch.uint32, device=dev),
+           "mapq": torch.empty(m, dtype=torch.int8, device=dev)}
+    if positions:
+        out["pos1"] = torch.empty(m, dtype=torch.uint32, device=dev)
+        out["pos2"] = torch.empty(m, dtype=torch.uint32, device=dev)
+    _lib.check(_lib.lib().cph_synth_pairs(int(seed), int(first), int(m), float(intra), g.n, g.G, g.ploidy, cum.data_ptr(),
+                                          gcum.data_ptr(), gstart.data_ptr(), order.data_ptr(), length.data_ptr(),
+                                          out["chrom1"].data_ptr(), out["chrom2"].data_ptr(),
+                                          out["pos1"].data_ptr() if positions else None,
+                                          out["pos2"].data_ptr() if positions else None, out["mapq"].data_ptr(),
+                                          _lib.stream()))
+    torch.cuda.current_stream().synchronize()
+    return out

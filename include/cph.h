@@ -170,6 +170,23 @@ int cph_csr_scale_nodes(const int64_t* indptr, const int32_t* indices, uint32_t 
 int cph_csr_abs_degree(const int64_t* indptr, const int32_t* indices, uint32_t n, const float* data32,
                        const double* data64, int skip_diag, double* deg, double* diag, cph_stream_t stream);
 
+/* ---- synthetic workload generators (bench infrastructure; device twin of cphasing_b200/synth.py) ---
+ * Seeded, counter-based tables of the shapes BASELINE.json names, written straight to HBM.
+ * cph_synth_porec_count: nrec_off (u64[m+1]) <- exclusive prefix of the records per concatemer, *h_total = N.
+ * cph_synth_porec_fill : Pore-C alignment records of concatemers [first, first+m), sorted by read_idx
+ *                        (start/end may be NULL).  law: 0 = 2+Poisson(2), 1 = 2+floor(Exp(8)), 2 = pairs.
+ * cph_synth_pairs      : Hi-C pairs (pos1/pos2 may be NULL); `intra` = fraction of intra-contig pairs. */
+int cph_synth_porec_count(uint64_t seed, uint64_t first, uint64_t m, int law, uint64_t* nrec_off, uint64_t* h_total,
+                          void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+int cph_synth_porec_fill(uint64_t seed, uint64_t first, uint64_t m, int law, uint32_t n, uint32_t G, uint32_t ploidy,
+                         const double* cum, const double* gcum, const int32_t* gstart, const int32_t* order,
+                         const int64_t* length, const uint64_t* nrec_off, uint32_t* read_idx, uint32_t* contig_idx,
+                         uint32_t* start, uint32_t* end, int8_t* mapq, cph_stream_t stream);
+int cph_synth_pairs(uint64_t seed, uint64_t first, uint64_t m, double intra, uint32_t n, uint32_t G, uint32_t ploidy,
+                    const double* cum, const double* gcum, const int32_t* gstart, const int32_t* order,
+                    const int64_t* length, uint32_t* chrom1, uint32_t* chrom2, uint32_t* pos1, uint32_t* pos2,
+                    int8_t* mapq, cph_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
