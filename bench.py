@@ -30,12 +30,12 @@ PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default=None, help="A|B|C|D|E (default: C at 1 GPU, D-shaped shards at N>1)")
     ap.add_argument("--m", type=int, default=None, help="override the number of concatemers per GPU")
-    ap.add_argument("--cpu-sample", type=int, default=2_000_000, help="concatemers in the CPU-baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=10_000_000, help="concatemers in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()

@@ -267,8 +267,9 @@ extern "C" int cph_pairs_to_edges(const u32* chrom1, const u32* chrom2, const in
     PairsIn in{chrom1, chrom2, mapq, pos1, pos2, contig_len, n_pairs, n_contigs, min_mapq, (i64)edge_length};
     if (!ar.dry) {
         ARENA_CHECK(ar);
-        ARG_CHECK(chrom1 && chrom2 && rem_row && rem_col && rem_count && rem_mapq && h_counts);
-        ARG_CHECK(edge_length == 0 || (pos1 && pos2 && contig_len));
+        ARG_CHECK(n_pairs == 0 || (chrom1 && chrom2));
+        ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq && h_counts);
+        ARG_CHECK(n_pairs == 0 || edge_length == 0 || (pos1 && pos2 && contig_len));
         if (n_pairs > 0) {
             pairs_flag_kernel<<<grid_for(n_pairs, TPB), TPB, 0, st>>>(in, keep);
             KERNEL_CHECK();
@@ -309,8 +310,9 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
     u32 h_scal[4] = {0, 0, 0, 0};
     if (!ar.dry) {
         ARENA_CHECK(ar);
-        ARG_CHECK(read_idx && contig_idx && mapq && rem_row && rem_col && rem_count && rem_mapq && h_counts);
-        ARG_CHECK(edge_length == 0 || (start && end && contig_len));
+        ARG_CHECK(N == 0 || (read_idx && contig_idx && mapq));
+        ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq && h_counts);
+        ARG_CHECK(N == 0 || edge_length == 0 || (start && end && contig_len));
         CUDA_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
         if (N > 0) {
             max_u32_kernel<<<148 * 8, TPB, 0, st>>>(read_idx, N, scal);
