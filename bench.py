@@ -137,19 +137,14 @@ def device_step(D, cfg, g, t, ev, world, rank):
     mark("edges")
     hook = None
     if world > 1:
-        def hook(rs):
+        def hook(rs, mx):
             dist.all_reduce(rs)          # global per-contig contact sums for the min_contacts row filter
-            return rs
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            return rs, mx
     H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0, rowsum_hook=hook)
     mark("incidence")
-    fb = None
-    if world > 1:
-        # the fixed-point scale must agree across ranks: derive it from the global row-square bound
-        _, mx = D.choose_frac_bits(H)
-        mxt = torch.tensor([mx], dtype=torch.int64, device=H.device)
-        dist.all_reduce(mxt)
-        fb = max(0, min(52, 61 - int(mxt.item() + 1).bit_length()))
-    acc = D.expand_accumulate(H, use_high_order=True, frac_bits=fb)
+    # the fixed-point scale derives from the (all-reduced) row sums, so every rank picks the same one
+    acc = D.expand_accumulate(H, use_high_order=True)
     mark("accumulate")
     if world > 1:
         dist.all_reduce(acc.acc)

@@ -44,7 +44,9 @@ _SIGS = {
                                 _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_edges_to_triplets": (_I, [_P, _P, _P, _P, _U64, _U32, _P, _P, _P, _P] + _WS),
     "cph_triplets_to_edges": (_I, [_P, _P, _P, _P, _U64, _U32, _P, _P, _P, _P] + _WS),
-    "cph_row_sums": (_I, [_P, _P, _P, _U64, _U32, _I, _P, _I, _P, _P]),
+    "cph_row_sums": (_I, [_P, _P, _P, _U64, _U32, _I, _P, _I, _P, _P, _P]),
+    "cph_incidence_csr": (_I, [_P, _P, _P, _U64, _U32, _P, _P, _P] + _WS),
+    "cph_diag_hist": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _P, _P]),
     "cph_incidence_build": (_I, [_P, _P, _P, _P, _U64, _U32, _I, _P, _U32, _U32, _I, _P, _P, _P, _P, _P,
                                  C.POINTER(_U64)] + _WS),
     "cph_csr_counts_f32": (_I, [_P, _U64, _P, _P]),

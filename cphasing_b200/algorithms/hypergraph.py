@@ -220,7 +220,7 @@ class HyperGraph:
         self._row_drop = None
         self._use_mapq = bool(self.min_quality > 0 and len(self.edges.mapq) > 1 and self.mapq_filter)
         if self._use_mapq:
-            rs = D.row_sums(raw, self.min_quality, None, True)
+            rs, _ = D.row_sums(raw, self.min_quality, None, True)
             has = (rs > 0).cpu().numpy()
             self.remove_contigs = self.nodes[~has]
             logger.info(f"Total {int((~has).sum()):,} low-quality (mapq < {self.min_quality}) contigs were removed. ")
@@ -308,17 +308,16 @@ class HyperGraph:
             raise NotImplementedError("cis_count is never passed by the reference's live callers "
                                       "(hyperpartition.py:350 sets it to None)")
         dH = upload_incidence(H)
-        entry_w = csr_w = None
+        entry_w = None
         if W is not None:                                                 # :427-430  W.data[0] * d_e
             wv = np.asarray(W.data[0] if hasattr(W, "data") and getattr(W.data, "ndim", 1) == 2 else W, dtype=np.float32)
             wd = D.to_dev(wv, torch.float32, dH.device)
-            csr_w = wd[dH.indices.long()]
             entry_w = _edge_major_weights(dH, wd)
         node_w = None
         if NW is not None:
             node_w = _node_weights_from_NW(NW)
         A, _acc = D.clique_expansion(dH, use_high_order=use_high_order, min_weight=float(min_weight), node_w=node_w,
-                                     entry_w=entry_w, csr_entry_w=csr_w, want32=True, want64=True)
+                                     entry_w=entry_w, want32=True, want64=True)
         out = wrap_adjacency(A)
         if P_allelic_idx or P_weak_idx:                                   # :464-481
             out = HyperGraph.reweight_pairs(out, P_allelic_idx, P_weak_idx, allelic_factor)

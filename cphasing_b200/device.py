@@ -53,27 +53,53 @@ class RawEdges:
                         k, self.n_cols, self.n_contigs)
 
 
-@dataclass
 class DeviceH:
-    """Filtered incidence matrix on the device in both orders (packed edge-major + CSR)."""
-    pem_row: torch.Tensor   # uint32 [nnz]  new row | head bit
-    pem_pk: torch.Tensor    # uint32 [nnz]  D_e<<24 | count
-    indptr: torch.Tensor    # int64 [n+1]
-    indices: torch.Tensor   # int32 [nnz]
-    pk: torch.Tensor        # uint32 [nnz]
-    nnz: int
-    n_rows: int
-    n_cols: int
-    row_keep: torch.Tensor  # bool [n_contigs] which input contigs survived (None = all)
-    rowsum: torch.Tensor    # uint64-as-int64 [n_contigs] summed counts before the row filter
-    pem_col: torch.Tensor = None   # uint32 [nnz] hyperedge id per pem entry; only set when columns keep their ids
+    """Filtered incidence matrix on the device.  The packed edge-major form (pem) is what the kernels
+    consume; the CSR view (what scipy callers see) is built on first use (cph_incidence_csr)."""
+
+    def __init__(self, pem_row, pem_pk, nnz, n_rows, n_cols, row_keep=None, rowsum=None, pem_col=None, value_bound=None):
+        self.pem_row = pem_row      # uint32 [nnz]  new row | head bit
+        self.pem_pk = pem_pk        # uint32 [nnz]  D_e<<24 | count
+        self.nnz = int(nnz)
+        self.n_rows = int(n_rows)
+        self.n_cols = int(n_cols)
+        self.row_keep = row_keep    # bool [n_contigs] which input contigs survived (None = all)
+        self.rowsum = rowsum        # uint64-as-int64 [n_contigs] summed counts before the row filter
+        self.pem_col = pem_col      # uint32 [nnz] hyperedge id per entry; only set when columns keep their ids
+        self._bound = value_bound   # python int >= max_ij sum_e c_ie c_je  (for the fixed-point scale)
+        self._csr = None
 
     @property
     def device(self):
         return self.pem_row.device
 
+    def _build_csr(self):
+        if self._csr is None:
+            dev = self.device
+            cap = max(self.nnz, 1)
+            indptr = torch.empty(self.n_rows + 1, dtype=torch.int64, device=dev)
+            indices = torch.empty(cap, dtype=torch.int32, device=dev)
+            pk = torch.empty(cap, dtype=torch.uint32, device=dev)
+            call_ws("cph_incidence_csr", dev, ptr(self.pem_row), ptr(self.pem_pk), ptr(self.pem_col), self.nnz,
+                    max(self.n_rows, 1), ptr(indptr), ptr(indices), ptr(pk))
+            self._csr = (indptr, indices[:self.nnz], pk[:self.nnz])
+        return self._csr
+
+    indptr = property(lambda s: s._build_csr()[0])      # int64 [n+1]
+    indices = property(lambda s: s._build_csr()[1])     # int32 [nnz] (sorted inside each row)
+    pk = property(lambda s: s._build_csr()[2])          # uint32 [nnz]
+
+    def value_bound(self):
+        if self._bound is None:
+            rs = torch.empty(max(self.n_rows, 1), dtype=torch.int64, device=self.device)
+            mx = torch.zeros(1, dtype=torch.int32, device=self.device)
+            check(lib().cph_row_sums(ptr(self.pem_row), ptr(self.pem_pk), None, self.nnz, max(self.n_rows, 1), 0, None, 1,
+                                     ptr(rs), ptr(mx), stream()))
+            self._bound = int(rs.max().item()) * max(int(mx.item()), 1)
+        return self._bound
+
     def counts_f32(self):
-        out = torch.empty(self.nnz, dtype=torch.float32, device=self.device)
+        out = torch.empty(max(self.nnz, 1), dtype=torch.float32, device=self.device)[:self.nnz]
         check(lib().cph_csr_counts_f32(ptr(self.pk), self.nnz, ptr(out), stream()))
         return out
 
@@ -175,28 +201,30 @@ def triplets_to_edges(row, col, count, mapq, n_contigs, n_cols=None, device=None
 # ------------------------------------------------------------------------------------------------
 def row_sums(e, min_mapq=0, row_drop=None, use_mapq=True, packed=False):
     """per-contig summed count (uint64 bits in an int64 tensor): matrix.sum(axis=1) of
-    algorithms/hypergraph.py:287 over the entries get_data (:175-184) / remove_rows (:207-223) keep."""
+    algorithms/hypergraph.py:287 over the entries get_data (:175-184) / remove_rows (:207-223) keep.
+    Returns (rowsum int64[n], max_count int32[1])."""
     dev = e.row.device
     out = torch.empty(e.n_contigs, dtype=torch.int64, device=dev)
+    mx = torch.zeros(1, dtype=torch.int32, device=dev)
     mq = e.mapq if (use_mapq and min_mapq > 0 and e.mapq is not None) else None
     check(lib().cph_row_sums(ptr(e.row), ptr(e.count), ptr(mq), e.nnz, e.n_contigs, int(min_mapq), ptr(row_drop),
-                             int(packed), ptr(out), stream()))
-    return out
+                             int(packed), ptr(out), ptr(mx), stream()))
+    return out, mx
 
 
 def incidence(e: RawEdges, min_contacts=1, min_mapq=0, row_drop=None, mapq_filter=True, rowsum_hook=None) -> DeviceH:
     """HyperGraph.get_data + remove_rows + incidence_matrix (algorithms/hypergraph.py:162-314).
 
     row_drop: uint8[n_contigs] flags of contigs removed by remove_rows (or None).
-    rowsum_hook: callable applied to the row-sum tensor before the min_contacts test (the multi-GPU
-    path all-reduces it across concatemer shards here).
+    rowsum_hook(rowsum, max_count) -> (rowsum, max_count): applied before the min_contacts test (the multi-GPU
+    path all-reduces both across concatemer shards here).
     """
     dev = e.row.device
     n = e.n_contigs
     use_mq = bool(mapq_filter and min_mapq > 0 and e.mapq is not None and e.nnz > 1)   # :175
-    rs = row_sums(e, min_mapq, row_drop, use_mq)
+    rs, mx = row_sums(e, min_mapq, row_drop, use_mq)
     if rowsum_hook is not None:
-        rs = rowsum_hook(rs)
+        rs, mx = rowsum_hook(rs, mx)
     if min_contacts:
         keep = rs >= int(np.ceil(min_contacts))                                          # :287
         col_min = 2                                                                      # :305
@@ -210,9 +238,16 @@ def incidence(e: RawEdges, min_contacts=1, min_mapq=0, row_drop=None, mapq_filte
         live = None
     new_id = torch.cumsum(keep.to(torch.int32), 0, dtype=torch.int32) - 1
     row_map = torch.where(keep if live is None else (keep & live), new_id, torch.full_like(new_id, -1))
-    n_rows = int(keep.sum().item())
-    return _incidence_build(e.row, e.col, e.count, e.mapq if use_mq else None, e.nnz, n, min_mapq if use_mq else 0,
-                            row_map, n_rows, col_min, False, keep, rs, e.n_cols)
+    # one host round trip for the three scalars the host needs
+    sc = torch.stack((keep.sum(), rs.max() if n else rs.sum(), mx[0].to(torch.int64))).cpu()
+    n_rows, bound = int(sc[0]), int(sc[1]) * max(int(sc[2]), 1)
+    if int(sc[2]) > 0x00FFFFFF:
+        raise _lib.CphError("an alignment count >= 2^24 cannot be represented exactly (the reference stores counts "
+                            "as float32)")
+    H = _incidence_build(e.row, e.col, e.count, e.mapq if use_mq else None, e.nnz, n, min_mapq if use_mq else 0,
+                         row_map, n_rows, col_min, False, keep, rs, e.n_cols)
+    H._bound = bound
+    return H
 
 
 def _incidence_build(row, col, count, mapq, nnz, n_contigs, min_mapq, row_map, n_rows, col_min, packed, keep, rs,
@@ -221,16 +256,12 @@ def _incidence_build(row, col, count, mapq, nnz, n_contigs, min_mapq, row_map, n
     cap = max(nnz, 1)
     pem_row = torch.empty(cap, dtype=torch.uint32, device=dev)
     pem_pk = torch.empty(cap, dtype=torch.uint32, device=dev)
-    indptr = torch.empty(n_rows + 1, dtype=torch.int64, device=dev)
-    indices = torch.empty(cap, dtype=torch.int32, device=dev)
-    pk = torch.empty(cap, dtype=torch.uint32, device=dev)
     h = (C.c_uint64 * 2)()
     call_ws("cph_incidence_build", dev, ptr(row), ptr(col), ptr(count), ptr(mapq), nnz, int(n_contigs), int(min_mapq),
-            ptr(row_map), int(n_rows), int(col_min), int(packed), ptr(pem_row), ptr(pem_pk), ptr(indptr), ptr(indices),
-            ptr(pk), h)
+            ptr(row_map), int(n_rows), int(col_min), int(packed), ptr(pem_row), ptr(pem_pk), None, None, None, h)
     k = int(h[0])
     n_cols = int(h[1]) if col_min > 0 else int(n_cols_in)
-    return DeviceH(pem_row[:k], pem_pk[:k], indptr, indices[:k], pk[:k], k, int(n_rows), n_cols, keep, rs)
+    return DeviceH(pem_row[:k], pem_pk[:k], k, int(n_rows), n_cols, keep, rs)
 
 
 def sub_incidence(H: DeviceH, idx, col_min=2) -> DeviceH:
@@ -247,11 +278,14 @@ def sub_incidence(H: DeviceH, idx, col_min=2) -> DeviceH:
 # ------------------------------------------------------------------------------------------------
 # stage 2: clique expansion
 # ------------------------------------------------------------------------------------------------
+def frac_bits_for(bound):
+    """largest fixed-point scale such that sums bounded by `bound` stay below 2^61."""
+    return max(0, min(52, 61 - int(bound + 1).bit_length()))
+
+
 def choose_frac_bits(H: DeviceH):
-    rowsq = torch.empty(H.n_rows, dtype=torch.int64, device=H.device)
-    check(lib().cph_row_sq_sums(ptr(H.indptr), ptr(H.pk), H.n_rows, ptr(rowsq), stream()))
-    mx = int(rowsq.max().item()) if H.n_rows else 0
-    return max(0, min(52, 61 - int(mx + 1).bit_length())), mx
+    b = H.value_bound()
+    return frac_bits_for(b), b
 
 
 @dataclass
@@ -269,7 +303,10 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     dev = H.device
     n = H.n_rows
     if frac_bits is None:
-        frac_bits, _ = choose_frac_bits(H)
+        b = H.value_bound()
+        if entry_w is not None and H.nnz:
+            b = int(np.ceil(b * max(float(entry_w.max().item()), 1.0)))
+        frac_bits = frac_bits_for(b)
         if not use_high_order and entry_w is None:
             frac_bits = 0            # pure integer contact counts: bit-exact
     tri = n * (n + 1) // 2
@@ -277,8 +314,8 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     if acc is None:
         acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    check(lib().cph_diag_terms(ptr(H.indptr), ptr(H.pk), ptr(csr_entry_w), n, int(use_high_order), int(frac_bits),
-                               ptr(diag), stream()))
+    check(lib().cph_diag_hist(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, max(n, 1), int(use_high_order),
+                              int(frac_bits), ptr(diag), stream()))
     check(lib().cph_expand_accumulate(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, n, int(use_high_order),
                                       int(frac_bits), int(zero), ptr(acc), stream()))
     return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))

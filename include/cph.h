@@ -95,10 +95,12 @@ int cph_triplets_to_edges(const int32_t* row, const int32_t* col, const uint32_t
  * cph_row_sums: per-contig sum of counts over the entries that pass the HyperGraph.get_data mapq
  * filter (algorithms/hypergraph.py:175-184; disabled when rem_mapq == NULL) and whose contig is not
  * flagged in row_drop (remove_rows :207-223; may be NULL): the `matrix.sum(axis=1)` of :287.
- * rowsum (uint64[n_contigs]) is overwritten.  `packed` != 0: counts carry D_e in the top byte. */
+ * rowsum (uint64[n_contigs]) is overwritten.  `packed` != 0: counts carry D_e in the top byte.
+ * max_count (device uint32, may be NULL) receives the largest count seen; with the row sums it bounds every
+ * A_ij (<= max_count * min(rowsum_i, rowsum_j)), which is how the caller picks frac_bits without a CSR pass. */
 int cph_row_sums(const uint32_t* rem_row, const uint32_t* rem_count, const int8_t* rem_mapq, uint64_t nnz,
                  uint32_t n_contigs, int min_mapq, const uint8_t* row_drop, int packed,
-                 uint64_t* rowsum, cph_stream_t stream);
+                 uint64_t* rowsum, uint32_t* max_count, cph_stream_t stream);
 
 /* cph_incidence_build: HyperGraph.incidence_matrix (algorithms/hypergraph.py:249-314) and
  * extract_incidence_matrix2 (:938-954) on the edge-major form.  row_map[c] = new row of contig c or
@@ -107,12 +109,19 @@ int cph_row_sums(const uint32_t* rem_row, const uint32_t* rem_count, const int8_
  * keeps every hyperedge AND the original column ids, the `min_contacts=0` branch :309-311).
  * With packed != 0 the input is itself a pem (rem_row = pem_row, rem_count = pem_pk, rem_col may be
  * NULL when col_min_sum > 0).  Outputs (capacity nnz): pem_row, pem_pk; CSR indptr[n_rows_out+1], indices, pk.
+ * indptr == NULL skips the CSR view (the clique expansion only needs the pem; cph_incidence_csr builds it later).
  * h_counts[0] = nnz_out, h_counts[1] = number of columns of H. */
 int cph_incidence_build(const uint32_t* rem_row, const uint32_t* rem_col, const uint32_t* rem_count,
                         const int8_t* rem_mapq, uint64_t nnz, uint32_t n_contigs, int min_mapq,
                         const int32_t* row_map, uint32_t n_rows_out, uint32_t col_min_sum, int packed,
                         uint32_t* pem_row, uint32_t* pem_pk, int64_t* indptr, int32_t* indices, uint32_t* pk,
                         uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* CSR view (sorted indices) of a pem, built on demand: what scipy hands back from incidence_matrix (:282-306).
+ * pem_col: explicit hyperedge id per entry, or NULL = running number of the hyperedge heads. */
+int cph_incidence_csr(const uint32_t* pem_row, const uint32_t* pem_pk, const uint32_t* pem_col, uint64_t nnz,
+                      uint32_t n_rows, int64_t* indptr, int32_t* indices, uint32_t* pk,
+                      void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 
 /* float32 `data` array of the scipy csr_matrix the reference returns (:282): data[t] = count. */
 int cph_csr_counts_f32(const uint32_t* pk, uint64_t nnz, float* data, cph_stream_t stream);
@@ -125,6 +134,7 @@ int cph_csr_counts_f32(const uint32_t* pk, uint64_t nnz, float* data, cph_stream
  *     frac_bits <= min(52, 61 - ceil(log2(max_i rowsq[i] + 1))).
  * cph_row_sq_sums  : rowsq[i] = sum_e c_ie^2  (an upper bound of A_ii, hence of every A_ij)
  * cph_diag_terms   : diag_fx[i] = sum_e round(c_ie^2 2^frac_bits / D_e)   (no atomics: CSR row reduce)
+ * cph_diag_hist    : the same from the pem (no CSR needed): shared-memory u64 histogram, one flush per CTA
  * cph_expand_accumulate: acc[i,j] += round(c_ie c_je 2^frac_bits / D_e) for every unordered pair of
  *     distinct entries of a hyperedge (x2 when both entries sit on the same contig: the duplicated
  *     (row,col) of intra-contig Hi-C pairs, :277-282).  acc is zeroed first when zero_first != 0.
@@ -138,6 +148,8 @@ int cph_csr_counts_f32(const uint32_t* pk, uint64_t nnz, float* data, cph_stream
 int cph_row_sq_sums(const int64_t* indptr, const uint32_t* pk, uint32_t n, uint64_t* rowsq, cph_stream_t stream);
 int cph_diag_terms(const int64_t* indptr, const uint32_t* pk, const float* csr_entry_w, uint32_t n,
                    int use_high_order, int frac_bits, uint64_t* diag_fx, cph_stream_t stream);
+int cph_diag_hist(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz, uint32_t n,
+                  int use_high_order, int frac_bits, uint64_t* diag_fx, cph_stream_t stream);
 int cph_expand_accumulate(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz, uint32_t n,
                           int use_high_order, int frac_bits, int zero_first, uint64_t* acc, cph_stream_t stream);
 int cph_expand_count(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
