@@ -205,6 +205,312 @@ __global__ void __launch_bounds__(TPB) porec_emit_kernel(KeyView kv, const u32* 
 }
 
 // ------------------------------------------------------------------------------------------------
+// Fast path for tables already grouped by read (what the reference's mappers write): ONE pass of a
+// shared-memory tile kernel.  A CTA takes a ticket (so lower tiles are always already running), owns
+// the reads that START inside its tile of PT_TILE records, stages the tile plus a PT_HALO look-ahead
+// in shared memory (coalesced 9 B/record) and does every per-read step there:
+//   heads      bitmask of read starts (ballot)                      -> segment start/end in O(1) by clz/ffs
+//   P1         first record of each (read, contig) = representative; the others add their count and
+//              max MAPQ to it with shared-memory atomics            (hypergraph.py:1470-1477)
+//   P2         distinct-contig order = popcount of representatives in the segment, order filter (:1461-1468)
+//   look-back  decoupled look-back over per-tile totals (64-bit status|value words) gives the tile's output
+//              offset without a second pass over the input
+//   emit       compacted, coalesced stores of (contig|head, read, count, mapq)
+// HBM traffic: 9 B per record + 13 B per surviving entry.  The one read per tile that can overflow the
+// window is handled by a slow cooperative walk over global memory.
+// ------------------------------------------------------------------------------------------------
+constexpr int PT_THREADS = 512;
+constexpr int PT_TILE = 4096;
+constexpr int PT_HALO = 1024;
+constexpr int PT_WIN = PT_TILE + PT_HALO;
+constexpr int PT_WORDS = PT_WIN / 32;
+constexpr u32 PT_INVALID = 0x00ffffffu;          // contig field of a filtered-out record (n_contigs < 2^23)
+constexpr u64 PT_AGG = 1ull << 62, PT_INCL = 2ull << 62, PT_VAL = (1ull << 62) - 1;
+
+__device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (contig or INVALID) << 8 | mapq + 128
+    u32 c = in.contig[t];
+    int8_t q = in.mapq[t];
+    bool ok = c < in.n_contigs;
+    if (in.min_mapq > 0) ok = ok && (int)q >= in.min_mapq;                      // hypergraph.py:1774-1775
+    if (ok && in.edge_length > 0) {                                             // :1449-1456
+        i64 st = in.start[t], en = in.end[t];
+        i64 pos = st + (en - st) / 2;
+        i64 L = in.len[c];
+        ok = (pos < in.edge_length) || ((L - pos) < in.edge_length);
+    }
+    return ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
+}
+
+struct PtSmem {
+    u32 read[PT_WIN];
+    u32 cvq[PT_WIN];
+    u32 cnt[PT_WIN];
+    u32 head[PT_WORDS];
+    u32 rep[PT_WORDS];
+    u32 rpref[PT_WORDS + 1];
+    u32 keep[PT_WORDS];
+    u32 kpref[PT_WORDS + 1];
+    int beg, end, last;
+    u32 tile, base, long_order, scan[PT_THREADS / 32 + 1];
+    unsigned long long long_end;
+};
+
+// exclusive prefix of popcounts over PT_WORDS words by warp 0; pref[PT_WORDS] = total
+__device__ __forceinline__ void pt_word_prefix(const u32* __restrict__ words, u32* __restrict__ pref, int tid) {
+    if (tid < 32) {
+        constexpr int PER = PT_WORDS / 32;
+        u32 loc[PER], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            loc[k] = sum;
+            sum += __popc(words[tid * PER + k]);
+        }
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (tid >= o) incl += v;
+        }
+        u32 ex = incl - sum;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) pref[tid * PER + k] = ex + loc[k];
+        if (tid == 31) pref[PT_WORDS] = incl;
+    }
+}
+__device__ __forceinline__ u32 pt_rank(const u32* __restrict__ words, const u32* __restrict__ pref, int x) {   // set bits in [0, x)
+    int w = x >> 5;
+    return w >= PT_WORDS ? pref[PT_WORDS] : pref[w] + __popc(words[w] & ((1u << (x & 31)) - 1u));
+}
+__device__ __forceinline__ int pt_seg_start(const u32* __restrict__ head, int i) {   // last head <= i (exists)
+    int w = i >> 5;
+    u32 m = head[w] & (0xffffffffu >> (31 - (i & 31)));
+    while (m == 0) m = head[--w];
+    return w * 32 + 31 - __clz(m);
+}
+__device__ __forceinline__ int pt_seg_end(const u32* __restrict__ head, int i, int fend) {   // first head > i, capped
+    int w = i >> 5;
+    u32 m = head[w] & ~((2u << (i & 31)) - 1u);
+    while (m == 0 && ++w < PT_WORDS) m = head[w];
+    int e = m ? w * 32 + __ffs(m) - 1 : fend;
+    return min(e, fend);
+}
+
+__global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, u32 min_order, u32 max_order, u32 read_offset,
+                                                                unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
+                                                                u32* __restrict__ rem_row, u32* __restrict__ rem_col,
+                                                                u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
+    extern __shared__ __align__(16) unsigned char pt_raw[];
+    PtSmem& S = *reinterpret_cast<PtSmem*>(pt_raw);
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid == 0) {
+        S.tile = atomicAdd(&scal[3], 1u);        // ticket: every lower tile has already started
+        S.beg = 0x7fffffff;
+        S.end = 0x7fffffff;
+        S.last = -1;
+        S.long_order = 0;
+    }
+    __syncthreads();
+    const u32 tile = S.tile;
+    const size_t lo = (size_t)tile * PT_TILE;
+    const size_t N = in.n;
+    const int own = (int)min((size_t)PT_TILE, N - lo);           // records of the tile proper
+    const int wn = (int)min((size_t)PT_WIN, N - lo);             // records staged
+    for (int i = tid; i < wn; i += PT_THREADS) {
+        size_t t = lo + i;
+        S.read[i] = in.read[t];
+        S.cvq[i] = porec_cvq(in, t);
+        S.cnt[i] = 1u;
+    }
+    __syncthreads();
+    const u32 prev_read = lo > 0 ? in.read[lo - 1] : 0u;
+    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+        int i = i0 + tid;
+        bool head = false;
+        if (i < wn) {
+            u32 r = S.read[i];
+            u32 p = i > 0 ? S.read[i - 1] : prev_read;
+            head = (lo + i == 0) || (p != r);
+            if (i < own && (lo + i) > 0 && p > r) scal[1] = 1u;   // not grouped by read (benign race)
+        }
+        u32 m = __ballot_sync(0xffffffffu, head);
+        if (lane == 0) {
+            S.head[i >> 5] = m;
+            if (m) {
+                u32 inside = (i + 32 <= own) ? m : (i < own ? (m & ((1u << (own - i)) - 1u)) : 0u);
+                u32 after = m & ~inside;
+                if (inside) {
+                    atomicMin(&S.beg, i + __ffs(inside) - 1);
+                    atomicMax(&S.last, i + 31 - __clz(inside));
+                }
+                if (after) atomicMin(&S.end, i + __ffs(after) - 1);
+            }
+        }
+    }
+    __syncthreads();
+    const int beg = S.beg;
+    const bool empty = beg == 0x7fffffff;    // a longer read covers the whole tile: its owner emits it
+    bool is_long = false;
+    int fend = 0;
+    if (!empty) {
+        if (S.end != 0x7fffffff) fend = S.end;
+        else if (lo + wn == N) fend = wn;
+        else {
+            is_long = true;
+            fend = S.last;            // the last read of the tile overflows the window
+        }
+    }
+    // P1: representative = first valid record of its (read, contig); later ones fold count / max MAPQ into it
+    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+        int i = i0 + tid;
+        bool rep = false;
+        if (!empty && i >= beg && i < fend) {
+            const u32 x = S.cvq[i], c = x >> 8;
+            if (c != PT_INVALID) {
+                rep = true;
+                const int s0 = pt_seg_start(S.head, i);
+                for (int j = s0; j < i; ++j)
+                    if ((S.cvq[j] >> 8) == c) {
+                        rep = false;
+                        atomicAdd(&S.cnt[j], 1u);
+                        atomicMax(&S.cvq[j], x);      // same contig bits, larger MAPQ byte wins
+                        break;
+                    }
+            }
+        }
+        u32 m = __ballot_sync(0xffffffffu, rep);
+        if (lane == 0) S.rep[i >> 5] = m;
+    }
+    __syncthreads();
+    pt_word_prefix(S.rep, S.rpref, tid);
+    __syncthreads();
+    // P2: distinct-contig order of the read = representatives in its segment
+    u32 my_max_read = 0;
+    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+        int i = i0 + tid;
+        bool keep = false;
+        if (!empty && i >= beg && i < fend && ((S.rep[i >> 5] >> (i & 31)) & 1u)) {
+            const int s0 = pt_seg_start(S.head, i), e0 = pt_seg_end(S.head, i, fend);
+            const u32 rs = pt_rank(S.rep, S.rpref, s0);
+            const u32 order = pt_rank(S.rep, S.rpref, e0) - rs;
+            keep = order >= min_order && order <= max_order;
+            if (keep) {
+                my_max_read = S.read[i];
+                if (pt_rank(S.rep, S.rpref, i) == rs) S.cnt[i] |= CPH_HEAD;     // first entry of the hyperedge
+            }
+        }
+        u32 m = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) S.keep[i >> 5] = m;
+    }
+    __syncthreads();
+    pt_word_prefix(S.keep, S.kpref, tid);
+    // slow path, part 1: order of the read that starts at `fend` and runs past the window
+    u32 long_kept = 0;
+    size_t ls = 0, le = 0;
+    u32 rid = 0;
+    auto long_rep = [&](size_t t) -> bool {
+        u32 c = porec_cvq(in, t) >> 8;
+        if (c == PT_INVALID) return false;
+        for (size_t u = t; u-- > ls;)
+            if ((porec_cvq(in, u) >> 8) == c) return false;
+        return true;
+    };
+    if (is_long) {
+        ls = lo + fend;
+        rid = S.read[fend];
+        if (tid == 0) {
+            size_t e = lo + wn;
+            while (e < N && in.read[e] == rid) ++e;
+            S.long_end = e;
+        }
+        __syncthreads();
+        le = S.long_end;
+        u32 nrep = 0;
+        for (size_t t = ls + tid; t < le; t += PT_THREADS) nrep += long_rep(t) ? 1u : 0u;
+        nrep = warp_sum(nrep);
+        if (lane == 0 && nrep) atomicAdd(&S.long_order, nrep);
+        __syncthreads();
+        const u32 order = S.long_order;
+        if (order >= min_order && order <= max_order) {
+            long_kept = order;
+            my_max_read = rid;
+        }
+    }
+    __syncthreads();
+    const u32 fast_total = empty ? 0u : S.kpref[PT_WORDS];
+    const u32 total = fast_total + long_kept;
+    // decoupled look-back (warp 0): exclusive prefix of the tile totals
+    if (tid < 32) {
+        u32 base = 0;
+        if (tile == 0) {
+            if (lane == 0) atomicExch(&tile_state[0], PT_INCL | (u64)total);
+        } else {
+            if (lane == 0) atomicExch(&tile_state[tile], PT_AGG | (u64)total);
+            u64 running = 0;
+            long j = (long)tile - 1;
+            for (;;) {
+                long idx = j - lane;
+                u64 st = idx >= 0 ? *((volatile unsigned long long*)&tile_state[idx]) : PT_INCL;
+                u32 inval = __ballot_sync(0xffffffffu, (st >> 62) == 0);
+                u32 incl = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                u32 first = incl ? (u32)__ffs(incl) - 1u : 32u;
+                u32 need = first >= 31u ? 0xffffffffu : ((2u << first) - 1u);
+                if (inval & need) continue;                 // a predecessor has not published yet: re-read
+                u64 v = ((u32)lane <= first) ? (st & PT_VAL) : 0ull;
+                running += warp_sum(v);
+                if (incl) break;
+                j -= 32;
+            }
+            base = (u32)running;
+            if (lane == 0) atomicExch(&tile_state[tile], PT_INCL | (running + total));
+        }
+        if (lane == 0) S.base = base;
+    }
+    __syncthreads();
+    const u32 base = S.base;
+    if (!empty) {
+        for (int i = beg + tid; i < fend; i += PT_THREADS) {
+            u32 w = S.keep[i >> 5];
+            if ((w >> (i & 31)) & 1u) {
+                u32 p = base + S.kpref[i >> 5] + __popc(w & ((1u << (i & 31)) - 1u));
+                u32 a = S.cnt[i], x = S.cvq[i];
+                rem_row[p] = (x >> 8) | (a & CPH_HEAD);
+                rem_col[p] = S.read[i] + read_offset;             // generate_edges :1871-1875
+                rem_count[p] = a & CPH_ROWM;
+                rem_mapq[p] = (int8_t)((int)(x & 0xffu) - 128);
+            }
+        }
+    }
+    if (long_kept) {     // slow path, part 2: emit the long read after the tile's fast entries
+        u32 carry = 0;
+        for (size_t t0 = ls; t0 < le; t0 += PT_THREADS) {
+            size_t t = t0 + tid;
+            bool rp = t < le && long_rep(t);
+            u32 tot;
+            u32 ex = block_excl_scan<u32, PT_THREADS>(rp ? 1u : 0u, S.scan, &tot);
+            if (rp) {
+                u32 c = porec_cvq(in, t) >> 8, cnt = 1;
+                int q = in.mapq[t];
+                for (size_t u = t + 1; u < le; ++u)
+                    if ((porec_cvq(in, u) >> 8) == c) {
+                        ++cnt;
+                        q = max(q, (int)in.mapq[u]);
+                    }
+                u32 k = carry + ex;
+                u32 p = base + fast_total + k;
+                rem_row[p] = c | (k == 0 ? CPH_HEAD : 0u);
+                rem_col[p] = rid + read_offset;
+                rem_count[p] = cnt;
+                rem_mapq[p] = (int8_t)q;
+            }
+            carry += tot;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) my_max_read = max(my_max_read, __shfl_xor_sync(0xffffffffu, my_max_read, o));
+    if (lane == 0 && total > 0 && my_max_read) atomicMax(&scal[0], my_max_read);
+}
+
+// ------------------------------------------------------------------------------------------------
 // wire order <-> edge-major
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(TPB) e2t_key_kernel(const u32* __restrict__ rem_row, const u32* __restrict__ rem_col,
@@ -299,14 +605,46 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
     ARG_CHECK(n_contigs > 0 && n_contigs < (1u << 23));
     const int cb = bits_for(n_contigs);   // contig ids < n_contigs <= 2^cb - 1
     WS_BEGIN(ar);
+    PorecIn in{read_idx, contig_idx, mapq, start, end, contig_len, N, n_contigs, min_mapq, (i64)edge_length};
+    // ---- fast path: table grouped by read (two passes of the shared-memory tile kernel) ----
+    const u32 ntiles = (u32)ceil_div(N > 0 ? N : 1, (size_t)PT_TILE);
+    u32* scal = ar.take<u32>(4);   // [0] max kept read (fast) / max read (slow)  [1] unsorted flag  [2] scan total  [3] ticket
+    u64* tile_state = ar.take<u64>((size_t)ntiles);
+    if (!ar.dry) {
+        ARENA_CHECK(ar);
+        ARG_CHECK(N == 0 || (read_idx && contig_idx && mapq));
+        ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq && h_counts);
+        ARG_CHECK(N == 0 || edge_length == 0 || (start && end && contig_len));
+        if (N == 0) {
+            h_counts[0] = h_counts[1] = 0;
+            return CPH_OK;
+        }
+        CUDA_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
+        CUDA_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
+        CUDA_TRY(cudaFuncSetAttribute(porec_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmem)));
+        porec_tile_kernel<<<ntiles, PT_THREADS, sizeof(PtSmem), st>>>(in, min_order, max_order, read_offset,
+                                                                     (unsigned long long*)tile_state, scal, rem_row, rem_col,
+                                                                     rem_count, rem_mapq);
+        KERNEL_CHECK();
+        u32 hs[4] = {0, 0, 0, 0};
+        u64 last = 0;
+        CUDA_TRY(cudaMemcpyAsync(hs, scal, 2 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (hs[1] == 0) {
+            const u64 total = last & ((1ull << 62) - 1);
+            h_counts[0] = total;
+            h_counts[1] = total ? (u64)hs[0] + read_offset + 1 : 0;
+            return CPH_OK;
+        }
+    }
+    // ---- general path: not grouped by read -> key, radix sort by read, run-local kernels ----
     u64* ka = ar.take<u64>(N);
     u64* kb = ar.take<u64>(N);
     u8* rep = ar.take<u8>(N);
     u32* keep = ar.take<u32>(N + 1);
     u32* aux = ar.take<u32>(N);
     int8_t* mq = ar.take<int8_t>(N);
-    u32* scal = ar.take<u32>(4);   // [0] max read  [1] unsorted flag  [2] scan total
-    PorecIn in{read_idx, contig_idx, mapq, start, end, contig_len, N, n_contigs, min_mapq, (i64)edge_length};
     u32 h_scal[4] = {0, 0, 0, 0};
     if (!ar.dry) {
         ARENA_CHECK(ar);

@@ -265,3 +265,41 @@ def test_expansion_properties_medium(api):
     E = ex.tocsr(); E.data[E.data.astype(np.float32) < np.float32(0.1)] = 0; E.eliminate_zeros()
     B = csr_matrix((B1.data64.cpu().numpy(), B1.indices.cpu().numpy(), B1.indptr.cpu().numpy()), shape=E.shape)
     assert_same_structure_close(B, E, rtol=1e-6, thr=0.1)
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_porec_long_reads_and_tile_boundaries(api, seed):
+    """reads far longer than the shared-memory window (slow cooperative path), reads straddling tile
+    boundaries, invalid records inside runs -- against the oracle, bit-exact."""
+    _, _, D, _ = api
+    import torch
+    rng = np.random.default_rng(seed)
+    n = 300
+    lens = []
+    while sum(lens) < 60000:
+        u = rng.random()
+        if u < 0.002:
+            lens.append(int(rng.integers(1100, 9000)))      # longer than PT_HALO / whole tiles
+        elif u < 0.02:
+            lens.append(int(rng.integers(100, 1000)))
+        else:
+            lens.append(int(rng.integers(1, 12)))
+    lens = np.array(lens)
+    read = np.repeat(np.arange(len(lens), dtype=np.uint32) * 3 + 5, lens)
+    ncont = np.where(lens > 60, rng.integers(2, 40, size=len(lens)), 1000)
+    contig = np.concatenate([rng.integers(0, min(n, k), size=l) for l, k in zip(lens, ncont)]).astype(np.uint32)
+    contig[rng.random(contig.size) < 0.02] = n + 7          # outside the contig index -> dropped
+    mapq = rng.choice(np.array([0, 3, 20, 60], dtype=np.int8), size=contig.size)
+    for min_mapq, max_order in ((1, 50), (0, 8), (21, 50)):
+        exp = orc.porec_edges(read, contig, mapq, min_mapq=min_mapq, min_order=2, max_order=max_order, n_contigs=n)
+        raw = D.porec_to_edges(read, contig, mapq, n, min_mapq=min_mapq, min_order=2, max_order=max_order, read_offset=11)
+        row, col, cnt, mq = D.edges_to_triplets(raw)
+        got = (row.cpu().numpy(), col.cpu().numpy() - 11, cnt.view(torch.int32).cpu().numpy().view(np.uint32), mq.cpu().numpy())
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b)
+        assert raw.n_cols == (int(exp[1].max()) + 12 if len(exp[1]) else 0)
+        # head bits: exactly one per surviving read, on its first entry
+        heads = (raw.row.view(torch.int32) < 0).cpu().numpy()
+        cols = raw.col.view(torch.int32).cpu().numpy()
+        assert heads.sum() == len(np.unique(cols))
+        assert np.all(heads[np.concatenate(([True], cols[1:] != cols[:-1]))])
