@@ -109,6 +109,286 @@ __global__ void __launch_bounds__(TPB) edge_flag_kernel(const u32* __restrict__ 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Fast path (no CSR view requested): one pass of a shared-memory tile kernel, same skeleton as the
+// Pore-C tile kernel of edges.cu -- ticketed tiles own the hyperedges that START inside them, the tile
+// plus a look-ahead halo is staged in shared memory, per-hyperedge sums run there, a decoupled
+// look-back over per-tile totals yields the output offset.  HBM traffic: 9 B read + 8 B written per entry.
+// ------------------------------------------------------------------------------------------------
+constexpr int IT_THREADS = 512;
+constexpr int IT_TILE = 4096;
+constexpr int IT_HALO = 1024;
+constexpr int IT_WIN = IT_TILE + IT_HALO;
+constexpr int IT_WORDS = IT_WIN / 32;
+constexpr u64 IT_AGG = 1ull << 62, IT_INCL = 2ull << 62, IT_VAL = (1ull << 62) - 1;
+
+struct IncIn {
+    const u32* row;
+    const u32* cnt;
+    const int8_t* mapq;
+    u64 nnz;
+    u32 n;
+    int min_mapq;
+    const i32* row_map;
+    u32 col_min_sum;
+    u32 cmask;
+};
+
+struct ItSmem {
+    u32 row[IT_WIN];        // new row (or ROWM if the entry is dropped)
+    u32 cnt[IT_WIN];
+    u32 res[IT_WIN];        // at a hyperedge start: keep | D << 8
+    u32 head[IT_WORDS];
+    u32 ok[IT_WORDS];
+    u32 opref[IT_WORDS + 1];
+    u32 keep[IT_WORDS];
+    u32 kpref[IT_WORDS + 1];
+    int beg, end, last;
+    u32 tile, base, long_k, long_res, scan[IT_THREADS / 32 + 1];
+    unsigned long long long_end, long_sum;
+};
+
+__device__ __forceinline__ void it_word_prefix(const u32* __restrict__ words, u32* __restrict__ pref, int tid) {
+    if (tid < 32) {
+        constexpr int PER = IT_WORDS / 32;
+        u32 loc[PER], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) {
+            loc[k] = sum;
+            sum += __popc(words[tid * PER + k]);
+        }
+        u32 incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            u32 v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (tid >= o) incl += v;
+        }
+        u32 ex = incl - sum;
+#pragma unroll
+        for (int k = 0; k < PER; ++k) pref[tid * PER + k] = ex + loc[k];
+        if (tid == 31) pref[IT_WORDS] = incl;
+    }
+}
+__device__ __forceinline__ u32 it_rank(const u32* __restrict__ words, const u32* __restrict__ pref, int x) {
+    int w = x >> 5;
+    return w >= IT_WORDS ? pref[IT_WORDS] : pref[w] + __popc(words[w] & ((1u << (x & 31)) - 1u));
+}
+__device__ __forceinline__ int it_seg_start(const u32* __restrict__ head, int i) {
+    int w = i >> 5;
+    u32 m = head[w] & (0xffffffffu >> (31 - (i & 31)));
+    while (m == 0) m = head[--w];
+    return w * 32 + 31 - __clz(m);
+}
+__device__ __forceinline__ u32 edge_degree(u32 k) {
+    // D_e = max(int8(k) - 1, 1) with numpy's int8 wrap-around (algorithms/hypergraph.py:385, 418)
+    int d8 = (int)(int8_t)(u8)((k - 1u) & 0xffu);
+    return (u32)max(d8, 1);
+}
+__device__ __forceinline__ u32 inc_new_row(const IncIn& in, size_t t) {   // new row of entry t or ROWM when dropped
+    u32 r = in.row[t] & CPH_ROWM;
+    bool ok = entry_ok(in.mapq, in.min_mapq, t) && r < in.n;
+    i32 nr = ok ? in.row_map[r] : -1;
+    return nr >= 0 ? (u32)nr : CPH_ROWM;
+}
+
+__global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, unsigned long long* __restrict__ tile_state,
+                                                                    u32* __restrict__ scal, unsigned long long* __restrict__ heads_total,
+                                                                    u32* __restrict__ pem_row, u32* __restrict__ pem_pk) {
+    extern __shared__ __align__(16) unsigned char it_raw[];
+    ItSmem& S = *reinterpret_cast<ItSmem*>(it_raw);
+    const int tid = threadIdx.x, lane = tid & 31;
+    if (tid == 0) {
+        S.tile = atomicAdd(&scal[3], 1u);
+        S.beg = 0x7fffffff;
+        S.end = 0x7fffffff;
+        S.last = -1;
+        S.long_k = 0;
+        S.long_sum = 0;
+    }
+    __syncthreads();
+    const u32 tile = S.tile;
+    const size_t lo = (size_t)tile * IT_TILE;
+    const size_t N = in.nnz;
+    const int own = (int)min((size_t)IT_TILE, N - lo);
+    const int wn = (int)min((size_t)IT_WIN, N - lo);
+    // stage + heads + ok bits
+    for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS) {
+        int i = i0 + tid;
+        bool head = false, ok = false;
+        if (i < wn) {
+            size_t t = lo + i;
+            u32 r = in.row[t];
+            u32 c = in.cnt[t];
+            if (in.cmask == 0xffffffffu && c > CPH_CNTM) scal[0] = 1u;      // not representable as float32 count
+            u32 nr = inc_new_row(in, t);
+            ok = nr != CPH_ROWM;
+            S.row[i] = nr;
+            S.cnt[i] = c & in.cmask;
+            head = (r & CPH_HEAD) || t == 0;
+        }
+        u32 mh = __ballot_sync(0xffffffffu, head), mo = __ballot_sync(0xffffffffu, ok);
+        if (lane == 0) {
+            S.head[i >> 5] = mh;
+            S.ok[i >> 5] = mo;
+            if (mh) {
+                u32 inside = (i + 32 <= own) ? mh : (i < own ? (mh & ((1u << (own - i)) - 1u)) : 0u);
+                u32 after = mh & ~inside;
+                if (inside) {
+                    atomicMin(&S.beg, i + __ffs(inside) - 1);
+                    atomicMax(&S.last, i + 31 - __clz(inside));
+                }
+                if (after) atomicMin(&S.end, i + __ffs(after) - 1);
+            }
+        }
+    }
+    __syncthreads();
+    const int beg = S.beg;
+    const bool empty = beg == 0x7fffffff;
+    bool is_long = false;
+    int fend = 0;
+    if (!empty) {
+        if (S.end != 0x7fffffff) fend = S.end;
+        else if (lo + wn == N) fend = wn;
+        else {
+            is_long = true;
+            fend = S.last;
+        }
+    }
+    it_word_prefix(S.ok, S.opref, tid);
+    __syncthreads();
+    // per hyperedge (thread at its start): surviving entries k, their summed count -> keep, D_e
+    u32 my_heads = 0;
+    for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS) {
+        int i = i0 + tid;
+        if (!empty && i >= beg && i < fend && ((S.head[i >> 5] >> (i & 31)) & 1u)) {
+            // segment end = next head (or fend)
+            int w = i >> 5;
+            u32 m = S.head[w] & ~((2u << (i & 31)) - 1u);
+            while (m == 0 && ++w < IT_WORDS) m = S.head[w];
+            int e = m ? w * 32 + __ffs(m) - 1 : fend;
+            e = min(e, fend);
+            const u32 k = it_rank(S.ok, S.opref, e) - it_rank(S.ok, S.opref, i);
+            u64 colsum = 0;
+            for (int j = i; j < e; ++j)
+                if (S.row[j] != CPH_ROWM) colsum += S.cnt[j];
+            const bool edge_keep = k > 0 && colsum >= (u64)in.col_min_sum;     // algorithms/hypergraph.py:305-306
+            S.res[i] = (edge_keep ? 1u : 0u) | (edge_degree(k) << 8);
+            my_heads += edge_keep ? 1u : 0u;
+        }
+    }
+    __syncthreads();
+    for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS) {
+        int i = i0 + tid;
+        bool keep = false;
+        if (!empty && i >= beg && i < fend && S.row[i] != CPH_ROWM) {
+            const int s0 = it_seg_start(S.head, i);
+            const u32 rs = S.res[s0];
+            keep = rs & 1u;
+            if (keep) {
+                const bool first = it_rank(S.ok, S.opref, i) == it_rank(S.ok, S.opref, s0);
+                S.row[i] |= first ? CPH_HEAD : 0u;
+                S.cnt[i] |= (rs >> 8) << 24;
+            }
+        }
+        u32 m = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) S.keep[i >> 5] = m;
+    }
+    __syncthreads();
+    it_word_prefix(S.keep, S.kpref, tid);
+    // slow path, part 1: the hyperedge that starts at `fend` and runs past the window
+    u32 long_kept = 0, long_D = 1;
+    size_t ls = 0, le = 0;
+    if (is_long) {
+        ls = lo + fend;
+        if (tid == 0) {
+            size_t e = lo + wn;
+            while (e < N && !(in.row[e] & CPH_HEAD)) ++e;
+            S.long_end = e;
+        }
+        __syncthreads();
+        le = S.long_end;
+        u32 k = 0;
+        u64 sum = 0;
+        for (size_t t = ls + tid; t < le; t += IT_THREADS)
+            if (inc_new_row(in, t) != CPH_ROWM) {
+                ++k;
+                sum += in.cnt[t] & in.cmask;
+            }
+        k = warp_sum(k);
+        sum = warp_sum(sum);
+        if (lane == 0 && k) {
+            atomicAdd(&S.long_k, k);
+            atomicAdd(&S.long_sum, (unsigned long long)sum);
+        }
+        __syncthreads();
+        if (S.long_k > 0 && S.long_sum >= (u64)in.col_min_sum) {
+            long_kept = S.long_k;
+            long_D = edge_degree(S.long_k);
+            if (tid == 0) ++my_heads;
+        }
+    }
+    __syncthreads();
+    const u32 fast_total = empty ? 0u : S.kpref[IT_WORDS];
+    const u32 total = fast_total + long_kept;
+    my_heads = warp_sum(my_heads);
+    if (lane == 0 && my_heads) atomicAdd(heads_total, (unsigned long long)my_heads);
+    if (tid < 32) {
+        u32 base = 0;
+        if (tile == 0) {
+            if (lane == 0) atomicExch(&tile_state[0], IT_INCL | (u64)total);
+        } else {
+            if (lane == 0) atomicExch(&tile_state[tile], IT_AGG | (u64)total);
+            u64 running = 0;
+            long j = (long)tile - 1;
+            for (;;) {
+                long idx = j - lane;
+                u64 st = idx >= 0 ? *((volatile unsigned long long*)&tile_state[idx]) : IT_INCL;
+                u32 inval = __ballot_sync(0xffffffffu, (st >> 62) == 0);
+                u32 incl = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                u32 first = incl ? (u32)__ffs(incl) - 1u : 32u;
+                u32 need = first >= 31u ? 0xffffffffu : ((2u << first) - 1u);
+                if (inval & need) continue;
+                u64 v = ((u32)lane <= first) ? (st & IT_VAL) : 0ull;
+                running += warp_sum(v);
+                if (incl) break;
+                j -= 32;
+            }
+            base = (u32)running;
+            if (lane == 0) atomicExch(&tile_state[tile], IT_INCL | (running + total));
+        }
+        if (lane == 0) S.base = base;
+    }
+    __syncthreads();
+    const u32 base = S.base;
+    if (!empty) {
+        for (int i = beg + tid; i < fend; i += IT_THREADS) {
+            u32 w = S.keep[i >> 5];
+            if ((w >> (i & 31)) & 1u) {
+                u32 p = base + S.kpref[i >> 5] + __popc(w & ((1u << (i & 31)) - 1u));
+                pem_row[p] = S.row[i];
+                pem_pk[p] = S.cnt[i];
+            }
+        }
+    }
+    if (long_kept) {
+        u32 carry = 0;
+        for (size_t t0 = ls; t0 < le; t0 += IT_THREADS) {
+            size_t t = t0 + tid;
+            u32 nr = t < le ? inc_new_row(in, t) : CPH_ROWM;
+            bool ok = nr != CPH_ROWM;
+            u32 tot;
+            u32 ex = block_excl_scan<u32, IT_THREADS>(ok ? 1u : 0u, S.scan, &tot);
+            if (ok) {
+                u32 k = carry + ex;
+                u32 p = base + fast_total + k;
+                pem_row[p] = nr | (k == 0 ? CPH_HEAD : 0u);
+                pem_pk[p] = (long_D << 24) | (in.cnt[t] & in.cmask);
+            }
+            carry += tot;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(TPB) compact_kernel(const u32* __restrict__ rem_row, const u32* __restrict__ rem_col,
                                                       const u32* __restrict__ rem_count, u64 nnz, const i32* __restrict__ row_map,
                                                       u32 cmask, int renumber, const u32* __restrict__ flag,
@@ -232,6 +512,40 @@ extern "C" int cph_incidence_build(const u32* rem_row, const u32* rem_col, const
     const int renumber = col_min_sum > 0;
     const u32 cmask = packed ? CPH_CNTM : 0xffffffffu;
     WS_BEGIN(ar);
+    // ---- fast path: pem only (no CSR view) ----
+    const u32 ntiles = (u32)ceil_div(nnz > 0 ? nnz : 1, (size_t)IT_TILE);
+    u32* scal = ar.take<u32>(4);                 // [0] bad count  [3] ticket
+    u64* heads_total = ar.take<u64>(1);
+    u64* tile_state = ar.take<u64>((size_t)ntiles);
+    if (!ar.dry && indptr == nullptr) {
+        ARENA_CHECK(ar);
+        ARG_CHECK(row_map && pem_row && pem_pk && h_counts);
+        ARG_CHECK(nnz == 0 || (rem_row && rem_count));
+        h_counts[0] = h_counts[1] = 0;
+        if (nnz == 0) return CPH_OK;
+        CUDA_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
+        CUDA_TRY(cudaMemsetAsync(heads_total, 0, sizeof(u64), st));
+        CUDA_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
+        CUDA_TRY(cudaFuncSetAttribute(incidence_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ItSmem)));
+        IncIn in{rem_row, rem_count, rem_mapq, nnz, n_contigs, min_mapq, row_map, col_min_sum, cmask};
+        incidence_tile_kernel<<<ntiles, IT_THREADS, sizeof(ItSmem), st>>>(in, (unsigned long long*)tile_state, scal,
+                                                                         (unsigned long long*)heads_total, pem_row, pem_pk);
+        KERNEL_CHECK();
+        u32 hs = 0;
+        u64 last = 0, heads = 0;
+        CUDA_TRY(cudaMemcpyAsync(&hs, scal, sizeof(u32), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(&heads, heads_total, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        if (hs) {
+            cph_set_error(__FILE__, __LINE__, "an alignment count >= 2^24 cannot be represented exactly (the reference stores counts as float32)");
+            return CPH_ERR_TOO_LARGE;
+        }
+        h_counts[0] = last & IT_VAL;
+        h_counts[1] = heads;
+        return CPH_OK;
+    }
+    // ---- general path: also emits the CSR view ----
     u32* flag = ar.take<u32>(nnz);
     u64* sc = ar.take<u64>(nnz + 1);
     u64* ka = ar.take<u64>(nnz);

@@ -303,3 +303,34 @@ def test_porec_long_reads_and_tile_boundaries(api, seed):
         cols = raw.col.view(torch.int32).cpu().numpy()
         assert heads.sum() == len(np.unique(cols))
         assert np.all(heads[np.concatenate(([True], cols[1:] != cols[:-1]))])
+
+
+def test_incidence_long_hyperedges(api):
+    """hyperedges longer than the tile window (slow cooperative path) and the int8 wrap of D_e
+    (algorithms/hypergraph.py:385) -- against the oracle."""
+    ah, _, D, _ = api
+    from scipy.sparse import random as sprandom, hstack, csr_matrix as csr
+    rng = np.random.default_rng(3)
+    n = 3500
+    base = sprandom(n, 4000, density=0.001, random_state=5, format="csc")
+    base.data = rng.integers(1, 4, size=base.nnz).astype(np.float32)
+    dense_cols = []
+    for k in (1500, 3300, 130, 257):
+        col = np.zeros((n, 1), np.float32)
+        col[rng.choice(n, size=k, replace=False), 0] = rng.integers(1, 3, size=k)
+        dense_cols.append(csr(col))
+    H = hstack([base[:, :2000], dense_cols[0], dense_cols[1], base[:, 2000:], dense_cols[2], dense_cols[3]]).tocsr().astype(np.float32)
+    A = ah.HyperGraph.clique_expansion_init(H, min_weight=0)
+    ex = canon(orc.clique_expansion_exact(H, True)); ex.eliminate_zeros()
+    h = ah.device_handle(A)
+    A64 = csr((h.data64.cpu().numpy(), h.indices.cpu().numpy(), h.indptr.cpu().numpy()), shape=A.shape)
+    assert np.array_equal(canon(A64).indptr, ex.indptr) and np.array_equal(canon(A64).indices, ex.indices)
+    np.testing.assert_allclose(canon(A64).data, ex.data, rtol=1e-9)
+    # sub-incidence of the same matrix (packed input) keeps / drops hyperedges like the reference
+    idx = np.arange(0, n, 2)
+    sub, rem, kept = ah.extract_incidence_matrix2(H, idx)
+    so, ro, ko = orc.extract_incidence_matrix2(H, idx)
+    assert sub.shape == so.shape
+    for x, y in zip(canon_dup(sub), canon_dup(so)):
+        assert np.array_equal(x, y)
+    assert np.array_equal(kept, ko)
