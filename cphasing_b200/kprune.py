@@ -1,0 +1,119 @@
+"""Drop-in for ``cphasing.kprune.KPruneHyperGraph`` (reference: cphasing/kprune.py:385-552): allelic and
+cross-allelic ("weak") contig pairs read off the clique-expansion matrix A, on the device
+(csrc/kprune.cu).  ``kprune_pairs`` is the array-level entry the partition driver uses.
+"""
+from __future__ import annotations
+
+import logging
+
+import numpy as np
+import pandas as pd
+import torch
+
+from . import device as D
+from . import graphops
+from ._lib import check, lib, ptr, stream
+
+logger = logging.getLogger(__name__)
+
+
+def allele_groups(allele_pairs, n, max_alleles=1):
+    """CSR-like allele lists per contig, in allele-table order (kprune.py:437-447 keeps the first)."""
+    lists = {}
+    for a, b in allele_pairs:
+        a = int(a); b = int(b)
+        l = lists.setdefault(a, [])
+        if len(l) < max_alleles:
+            l.append(b)
+    ptr_ = np.zeros(n + 1, dtype=np.int64)
+    for a, l in lists.items():
+        if 0 <= a < n:
+            ptr_[a + 1] = len(l)
+    ptr_ = np.cumsum(ptr_)
+    idx = np.zeros(max(int(ptr_[-1]), 1), dtype=np.int32)
+    for a, l in lists.items():
+        if 0 <= a < n:
+            idx[ptr_[a]:ptr_[a] + len(l)] = l
+    return ptr_, idx
+
+
+def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False):
+    """-> (flag uint8[nnz] device, row_of int32[nnz] device[, best_with, best_all])."""
+    dev = a.indptr.device
+    n = a.n
+    pairs = np.asarray(list(allele_pairs), dtype=np.int64).reshape(-1, 2)
+    ag_ptr, ag_idx = allele_groups(pairs, n, max_alleles)
+    agp = D.to_dev(ag_ptr, torch.int64, dev); agi = D.to_dev(ag_idx, torch.int32, dev)
+    alr = D.to_dev(pairs[:, 0].copy(), torch.int64, dev); alc = D.to_dev(pairs[:, 1].copy(), torch.int64, dev)
+    row_of = torch.empty(max(a.nnz, 1), dtype=torch.int32, device=dev)
+    check(lib().cph_csr_row_ids(ptr(a.indptr), n, ptr(row_of), stream()))
+    flag = torch.empty(max(a.nnz, 1), dtype=torch.uint8, device=dev)
+    bw = torch.zeros(max(a.nnz, 1), dtype=torch.float64, device=dev) if want_scores else None
+    ba = torch.zeros(max(a.nnz, 1), dtype=torch.float64, device=dev) if want_scores else None
+    d64 = a.data64
+    d32 = a.data32 if d64 is None else None
+    check(lib().cph_kprune(ptr(a.indptr), ptr(a.indices), ptr(d32), ptr(d64), n, a.nnz, ptr(row_of), ptr(agp), ptr(agi),
+                           int(max_alleles), ptr(alr), ptr(alc), len(pairs), ptr(flag), ptr(bw), ptr(ba), stream()))
+    out = (flag[:a.nnz], row_of[:a.nnz])
+    return out + (bw[:a.nnz], ba[:a.nnz]) if want_scores else out
+
+
+def kprune_pairs(A, allele_pairs, max_alleles=1):
+    """A: scipy matrix / DeviceBackedCSR; allele_pairs: (i, j) contig-index pairs in allele-table order.
+    Returns (allelic list[(i, j)], weak list[(i, j)]), each sorted, i < j."""
+    a = graphops.upload_adjacency(A)
+    flag, row_of = kprune_device(a, allele_pairs, max_alleles)
+    cols = a.indices
+    al = torch.nonzero(flag == 1).flatten()
+    wk = torch.nonzero(flag == 2).flatten()
+    pick = lambda ix: sorted(zip(row_of[ix].cpu().numpy().tolist(), cols[ix].cpu().numpy().tolist()))
+    return pick(al), pick(wk)
+
+
+class KPruneHyperGraph:
+    """kprune.py:385-552.  `alleletable` is an object with a ``.data`` DataFrame whose columns 1 and 2 hold the
+    contig names of each allele pair (the reference's AlleleTable), or a plain sequence of (name1, name2)."""
+    AlleleHeader2 = ['idx1', 'idx2', 'contig1', 'contig2', 'mz1', 'mz2', 'mzShared', 'similarity', 'strand']
+
+    def __init__(self, alleletable, A, contig2idx, max_alleles=1):
+        self.alleletable = alleletable
+        df = alleletable.data.copy() if hasattr(alleletable, "data") else pd.DataFrame(
+            [(0, 0, a, b) for a, b in alleletable], columns=[-1, 0, 1, 2])
+        df[1] = df[1].map(contig2idx.get)
+        df[2] = df[2].map(contig2idx.get)
+        df = df.dropna(subset=[1, 2])
+        df[1] = df[1].astype(int); df[2] = df[2].astype(int)
+        self.alleletable_idx = df
+        self.A = A
+        self.contig2idx = contig2idx
+        self.max_alleles = max_alleles
+        self.allelic_prune_list = []
+        self.weak_prune_list = []
+
+    def run(self):
+        pairs = self.alleletable_idx[[1, 2]].to_numpy()
+        al, wk = kprune_pairs(self.A, pairs, self.max_alleles)
+        logger.info(f"Removed {len(al)} allelic contacts.")
+        logger.info(f"Removed {len(wk)} weak contacts with allelic.")
+        self.allelic_prune_list.extend(al)
+        self.weak_prune_list.extend(wk)
+
+    def get_prune_table(self, symmetric=False):
+        """7-column prune table: contig1 contig2 mz1 mz2 mzShared similarity type (core.py:711-723)."""
+        idx2name = {i: c for c, i in self.contig2idx.items()}
+        meta = {}
+        cols = list(self.alleletable_idx.columns)
+        for row in self.alleletable_idx.itertuples(index=False):
+            d = dict(zip(cols, row))
+            meta.setdefault((d[1], d[2]), tuple(d.get(k, 0) for k in (3, 4, 5, 6)))
+        rows = []
+        for a, b in self.allelic_prune_list:
+            mz1, mz2, sh, sim = meta.get((a, b), (0, 0, 0, 0))
+            rows.append((idx2name[a], idx2name[b], mz1, mz2, sh, sim, 0))
+        for a, b in self.weak_prune_list:
+            rows.append((idx2name[a], idx2name[b], 0, 0, 0, 0, 1))
+        res = pd.DataFrame(rows, columns=['contig1', 'contig2', 'mz1', 'mz2', 'mzShared', 'similarity', 'type'])
+        if symmetric:
+            res2 = res.rename(columns={'contig1': 'contig2', 'contig2': 'contig1', 'mz1': 'mz2', 'mz2': 'mz1'})
+            res = pd.concat([res, res2[res.columns]], axis=0)
+        return res

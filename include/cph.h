@@ -182,6 +182,21 @@ int cph_csr_scale_nodes(const int64_t* indptr, const int32_t* indices, uint32_t 
 int cph_csr_abs_degree(const int64_t* indptr, const int32_t* indices, uint32_t n, const float* data32,
                        const double* data64, int skip_diag, double* deg, double* diag, cph_stream_t stream);
 
+/* ---- stage 3: kprune on A ---------------------------------------------------------------------------
+ * Replaces KPruneHyperGraph.run (kprune.py:407-517) and the l1 x l2 decision of KPruner (kprune.py:269-335).
+ * A: CSR with sorted indices (diagonal ignored, :419).  row_of[t] = row of stored entry t (cph_csr_row_ids).
+ * ag_ptr/ag_idx: allele lists per contig (CSR-like; empty = the contig has no allele group); at most
+ * max_alleles (1..5) of them are used (1 = "first listed allele", kprune.py:437-447).
+ * al_r/al_c: allele-table pairs as contig indices, table order; only rows with al_r < al_c count (:456).
+ * flag (nnz bytes, overwritten): 1 = allelic stored upper entry (:455-468), 2 = weak / cross-allelic upper
+ * entry (:470-517), 0 otherwise.  best_with / best_all (double[nnz], may be NULL): weight of the best matching
+ * that pairs c1 with c2, and of the best matching overall, for every scored candidate. */
+int cph_csr_row_ids(const int64_t* indptr, uint32_t n, int32_t* row_of, cph_stream_t stream);
+int cph_kprune(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64, uint32_t n,
+               uint64_t nnz, const int32_t* row_of, const int64_t* ag_ptr, const int32_t* ag_idx, int max_alleles,
+               const int64_t* al_r, const int64_t* al_c, uint64_t n_al, uint8_t* flag, double* best_with,
+               double* best_all, cph_stream_t stream);
+
 /* ---- synthetic workload generators (bench infrastructure; device twin of cphasing_b200/synth.py) ---
  * Seeded, counter-based tables of the shapes BASELINE.json names, written straight to HBM.
  * cph_synth_porec_count: nrec_off (u64[m+1]) <- exclusive prefix of the records per concatemer, *h_total = N.
