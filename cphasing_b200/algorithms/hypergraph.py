@@ -336,6 +336,128 @@ class HyperGraph:
         return graphops.scale_by_node_weights(A, _node_weights_from_NW(NW))
 
 
+    # -- algorithms/hypergraph.py:486-524
+    @staticmethod
+    def _to_series_contigsizes(contigsizes, nodes):
+        import pandas as pd
+        if contigsizes is None:
+            raise ValueError("contigsizes is required")
+        if isinstance(contigsizes, dict):
+            return pd.Series(contigsizes, name="size")
+        if isinstance(contigsizes, pd.Series):
+            return contigsizes.rename("size") if contigsizes.name is None else contigsizes
+        if isinstance(contigsizes, pd.DataFrame):
+            df = contigsizes.copy()
+            cols = {str(c).lower(): c for c in df.columns}
+            if "chrom" in cols and "length" in cols:
+                df = df.rename(columns={cols["chrom"]: "contig", cols["length"]: "size"})
+            elif not ("contig" in df.columns and "size" in df.columns):
+                if df.shape[1] >= 2:
+                    df = df.iloc[:, :2].copy()
+                    df.columns = ["contig", "size"]
+                else:                                   # read_chrom_sizes: index = contig, one column = length
+                    df = df.reset_index()
+                    df.columns = ["contig", "size"]
+            return pd.Series(df["size"].values, index=df["contig"].astype(str).values, name="size")
+        raise TypeError(f"Unsupported contigsizes type: {type(contigsizes)}")
+
+    # -- algorithms/hypergraph.py:526-580: degree on the device (cph_csr_abs_degree), n-vector statistics on the host
+    @staticmethod
+    def filter_adjacency_matrix(A, nodes, contigsizes, invert=False, method="quantile", high_q=0.999, low_q=None,
+                                mad_z=3.0):
+        import pandas as pd
+        from .. import graphops
+        n = A.shape[0]
+        if A is None or n == 0 or A.nnz == 0:
+            return np.arange(n, dtype=np.int64)
+        a = graphops.upload_adjacency(A)
+        deg, _ = graphops.abs_degree(a, skip_diag=False, use32=(A.dtype == np.float32))
+        deg = deg.cpu().numpy()
+        cs = HyperGraph._to_series_contigsizes(contigsizes, nodes)
+        sizes = pd.Index(np.asarray(nodes).astype(str)).map(cs).to_numpy(dtype=np.float64)
+        sizes[~np.isfinite(sizes)] = np.nan
+        sizes[sizes <= 0] = np.nan
+        norm = deg / sizes * 10000.0
+        x = norm[np.isfinite(norm)]
+        if x.size == 0:
+            return np.arange(n, dtype=np.int64)
+        keep = np.ones(n, dtype=bool)
+        if method == "quantile":
+            if high_q is not None:
+                hi = float(np.nanquantile(x, float(high_q)))
+                keep &= ~(np.isfinite(norm) & (norm > hi))
+            if low_q is not None:
+                lo = float(np.nanquantile(x, float(low_q)))
+                keep &= ~(np.isfinite(norm) & (norm < lo))
+        elif method == "mad":
+            med = float(np.nanmedian(x))
+            mad = float(np.nanmedian(np.abs(x - med)))
+            if mad <= 0:
+                hi = float(np.nanquantile(x, 0.999))
+                keep &= ~(np.isfinite(norm) & (norm > hi))
+            else:
+                robust_z = 0.6745 * (norm - med) / mad
+                keep &= ~(np.isfinite(robust_z) & (robust_z > float(mad_z)))
+        else:
+            raise ValueError("method must be 'quantile' or 'mad'")
+        return np.where(keep)[0].astype(np.int64)
+
+    # -- algorithms/hypergraph.py:582-588
+    @staticmethod
+    def filter_by_weight(A, min_weight=0.1):
+        if min_weight > 0:
+            A = csr_matrix(A)
+            A.data[A.data < min_weight] = 0
+            A.eliminate_zeros()
+        return A
+
+    # -- algorithms/hypergraph.py:604-630
+    @staticmethod
+    def _normalize_pair_index(P):
+        if P is None:
+            return None, None
+        if isinstance(P, (tuple, list)) and len(P) == 2 and not (
+                isinstance(P[0], (tuple, list, np.ndarray)) and len(np.asarray(P[0]).shape) == 2):
+            return np.asarray(P[0], dtype=np.int64).ravel(), np.asarray(P[1], dtype=np.int64).ravel()
+        arr = np.asarray(P)
+        if arr.ndim != 2 or arr.shape[1] != 2:
+            raise ValueError(f"Invalid pair index format for P_allelic_idx: shape={arr.shape}")
+        return arr[:, 0].astype(np.int64, copy=False), arr[:, 1].astype(np.int64, copy=False)
+
+    # -- algorithms/hypergraph.py:632-709 (numeric allelic_factor <= 0: the CLI default path; the string modes and
+    #    positive factors are experimental branches no live caller selects)
+    @staticmethod
+    def reweight_adjacency_matrix(A, P_allelic_idx=None, P_weak_idx=None, allelic_factor=-1, cross_allelic_factor=0):
+        if P_allelic_idx or P_weak_idx:
+            from .. import graphops
+            return graphops.reweight_pairs(A, P_allelic_idx if P_allelic_idx else None,
+                                           P_weak_idx if P_weak_idx else None, allelic_factor, cross_allelic_factor)
+        return A
+
+    # -- algorithms/hypergraph.py:712-753 (TSV writer: host I/O)
+    @staticmethod
+    def to_contacts(A, nodes=None, NW=None, min_weight=1.0, contigsizes=None, output="hypergraph.expansion.contacts"):
+        import pandas as pd
+        Ac = A.tocoo()
+        mask = (Ac.row <= Ac.col) & (np.abs(Ac.data) >= min_weight) & np.isfinite(Ac.data)
+        r, c, d = Ac.row[mask], Ac.col[mask], Ac.data[mask]
+        if nodes is not None:
+            nodes = np.asarray(nodes)
+            df = pd.DataFrame({"0": nodes[r], "1": nodes[c], "2": d})
+            if contigsizes is not None:
+                cs = HyperGraph._to_series_contigsizes(contigsizes, nodes)
+                l0 = df["0"].map(cs).to_numpy(dtype=np.float64)
+                l1 = df["1"].map(cs).to_numpy(dtype=np.float64)
+                df["2"] = df["2"] / np.sqrt(l0 * l1)
+        else:
+            df = pd.DataFrame({"0": r, "1": c, "2": d})
+        if output:
+            df.to_csv(output, sep="\t", header=False, index=False)
+            logger.info(f"Export hypergraph into `{output}`")
+            return
+        return df
+
+
 def _node_weights_from_NW(NW):
     """The reference passes the dense outer product NW = w w^T (hyperpartition.py:568); the kernels
     take the vector.  Accept either: a vector is used as is, a matrix gives w = sqrt(diag)."""
@@ -381,3 +503,57 @@ def _kept_columns(h: D.DeviceH, idx):
     s = torch.zeros(h.n_cols, dtype=torch.int64, device=dev)
     s.index_add_(0, h.indices.long()[m], cnt[m])
     return torch.nonzero(s > 1).flatten().cpu().numpy()
+
+
+# ------------------------------------------------------------------------------------------------
+# IRMM (algorithms/hypergraph.py:1067-1399)
+# ------------------------------------------------------------------------------------------------
+def _upper_pairs_symmetric(P):
+    """igraph only ever sees triu(A) (algorithms/hypergraph.py:1178): a listed pair acts on the graph through its
+    upper-triangle entry only.  Keep the pairs listed with r < c and mirror them, so the symmetric device graph carries
+    exactly the edge weights igraph would see.  (The reference's callers pass symmetrised lists,
+    hyperpartition.py:438-441, for which this is the whole list.)"""
+    r, c = HyperGraph._normalize_pair_index(P)
+    if r is None or len(r) == 0:
+        return None
+    up = r < c
+    ru, cu = r[up], c[up]
+    if len(ru) == 0:
+        return None
+    return np.concatenate([ru, cu]), np.concatenate([cu, ru])
+
+
+def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor=-1, cross_allelic_factor=0.3,
+         resolution=1, min_weight=1, threshold=0.01, max_round=1, chunk=10000, threads=10, method="louvain",
+         outprefix="all"):
+    """Same signature and return contract as the reference: ``(raw_A, A, cluster_assignments, cluster_results)``.
+
+    Graph preparation (:1120-1178) and the clustering (:1239-1252) run on the device; ``cluster_assignments`` offers
+    ``.membership`` and iterates over groups like igraph's VertexClustering.  Deviations, all deliberate:
+      * the clustering is deterministic (no RNG), so CPHASING_RANDOM_SEED has no effect;
+      * the caller's A is NOT modified in place (the reference multiplies ``A.data`` by allelic_factor in place on every
+        call, :1160-1164, so repeated calls in the resolution search flip the sign of allelic entries when
+        allelic_factor < 0);
+      * ``max_round > 1`` (iterative hyperedge re-weighting, :1258-1397; CLI default 1) is not implemented yet.
+    """
+    from .. import community, graphops
+    if max_round > 1:
+        raise NotImplementedError("IRMM max_round > 1 (iterative re-weighting) is not on the device path yet "
+                                  "(SURVEY.md 8f rank 4; the CLI default is --max-round 1)")
+    if A is None:
+        # A = H W D_e^-1 H^T, threshold, normalise, zero diagonal (:1120-1150)
+        A = HyperGraph.clique_expansion_init(H, NW=NW, min_weight=float(min_weight) if min_weight > 0 else 0.0)
+    raw_A = A
+    a = graphops.clone_adjacency(graphops.upload_adjacency(A))
+    if P_allelic_idx or P_weak_idx:
+        Pa = _upper_pairs_symmetric(P_allelic_idx) if P_allelic_idx else None
+        Pw = _upper_pairs_symmetric(P_weak_idx) if P_weak_idx else None
+        graphops.reweight_device(a, Pa, Pw, allelic_factor, 0.0)          # :1158-1170
+    graphops.zero_diagonal(a)                                             # :1172 (kept as explicit zeros)
+    use_leiden = (isinstance(allelic_factor, (int, float)) and allelic_factor < 0) or method == "leiden"
+    mem, q, stats = community.community_device(a, float(resolution), "leiden" if use_leiden else "louvain",
+                                               n_iterations=2, use32=False)
+    cluster_assignments = community.VertexClustering(mem.cpu().numpy(), q, stats)
+    cluster_results = [set(c) for c in cluster_assignments]
+    A_out = wrap_adjacency(a, dtype=A.dtype if A.dtype in (np.float32, np.float64) else np.float32)
+    return raw_A, A_out, cluster_assignments, cluster_results

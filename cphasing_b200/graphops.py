@@ -107,3 +107,18 @@ def abs_degree(a: D.DeviceCSR, skip_diag=False, use32=False):
     check(lib().cph_csr_abs_degree(ptr(a.indptr), ptr(a.indices), a.n, ptr(d32), ptr(d64), int(skip_diag), ptr(deg),
                                    ptr(diag), stream()))
     return deg, diag
+
+
+def zero_diagonal(a: D.DeviceCSR):
+    """A.setdiag(0) on stored entries (algorithms/hypergraph.py:1172); in place."""
+    if a.nnz == 0:
+        return a
+    dev = a.indptr.device
+    row_of = torch.empty(a.nnz, dtype=torch.int32, device=dev)
+    check(lib().cph_csr_row_ids(ptr(a.indptr), a.n, ptr(row_of), stream()))
+    on_diag = row_of == a.indices
+    if a.data32 is not None:
+        a.data32.masked_fill_(on_diag, 0)
+    if a.data64 is not None:
+        a.data64.masked_fill_(on_diag, 0)
+    return a

@@ -197,6 +197,27 @@ int cph_kprune(const int64_t* indptr, const int32_t* indices, const float* data3
                const int64_t* al_r, const int64_t* al_c, uint64_t n_al, uint8_t* flag, double* best_with,
                double* best_all, cph_stream_t stream);
 
+/* ---- stage 4: Louvain / Leiden modularity clustering ---------------------------------------------------
+ * Replaces the igraph calls of IRMM (algorithms/hypergraph.py:1239-1252): community_multilevel(weights,
+ * resolution) [method 0] and community_leiden(weights, resolution_parameter, objective_function="modularity")
+ * [method 1, n_iterations passes, python-igraph default 2] on the undirected graph of A's off-diagonal entries
+ * (:1157-1244; A must be symmetric CSR, both triangles stored; the diagonal and non-finite values are ignored).
+ * Quality = sum_c [ in_c / 2m - resolution (tot_c / 2m)^2 ].  Weights may be negative (allelic_factor < 0).
+ * Deterministic: weights are converted to 64-bit fixed point, ties go to the lowest community id.
+ * n_phases (<= 0: 8) = interleaved vertex phases per local-moving sweep, max_sweeps (<= 0: 64).
+ * init_membership (device int32[n], labels in [0, n), or NULL = singletons): igraph's initial_membership (:1366-1373).
+ * membership (device int32[n], out): groups numbered 0..g-1 in order of first appearance.
+ * h_quality (host, may be NULL), h_stats (host uint32[4], may be NULL: groups, levels, sweeps, refinement rounds).
+ * Synchronises `stream`.
+ * cph_modularity: the same quality function for a given membership (labels in [0, n)). */
+int cph_community(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64, uint32_t n,
+                  uint64_t nnz, double resolution, int method, int n_iterations, int n_phases, int max_sweeps,
+                  const int32_t* init_membership, int32_t* membership, double* h_quality, uint32_t* h_stats, void* ws,
+                  size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+int cph_modularity(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64, uint32_t n,
+                   uint64_t nnz, double resolution, const int32_t* membership, double* h_quality, void* ws, size_t ws_bytes,
+                   size_t* h_ws_need, cph_stream_t stream);
+
 /* ---- synthetic workload generators (bench infrastructure; device twin of cphasing_b200/synth.py) ---
  * Seeded, counter-based tables of the shapes BASELINE.json names, written straight to HBM.
  * cph_synth_porec_count: nrec_off (u64[m+1]) <- exclusive prefix of the records per concatemer, *h_total = N.

@@ -1,0 +1,151 @@
+"""GPU parity of the stages downstream of A: kprune (kprune.py:385-552), the adjacency filters
+(algorithms/hypergraph.py:526-580), IRMM's graph preparation + clustering (:1157-1256), end to end on a
+workload-A shaped synthetic table (5 chromosomes x 4 haplotypes)."""
+import numpy as np
+import pytest
+from scipy.sparse import csr_matrix
+
+from oracle import community_oracle as co
+from oracle import hypergraph_oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def case():
+    """table -> H -> A through the device classes, plus the oracle's H and A of the same table."""
+    from cphasing_b200 import synth
+    from cphasing_b200 import hypergraph as hg
+    from cphasing_b200.algorithms import hypergraph as ah
+    g = synth.make_genome(400, 5, 4, seed=20240)
+    t = synth.porec_table(g, 120_000, seed=20240)
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes,
+                                       min_quality=1, edge_length=0)
+    HG = ah.HyperGraph(ex.edges, min_quality=1)
+    H = HG.incidence_matrix(min_contacts=25)
+    r, c, cnt, q = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=1, n_contigs=g.n)
+    rr, cc, kk, ncol = orc.hypergraph_get_data(r, c, cnt, q, 1)
+    Ho, keep_rows, _ = orc.incidence_matrix(rr, cc, kk, g.n, ncol, 25)
+    return dict(g=g, ah=ah, HG=HG, H=H, Ho=Ho, nodes=HG.nodes, alleles=synth.allele_pairs(g, seed=3))
+
+
+def _kept_index(case):
+    """allele pairs re-indexed to the rows that survived min_contacts."""
+    name2new = {nm: i for i, nm in enumerate(case["nodes"])}
+    names = sorted(case["g"].contig_idx, key=case["g"].contig_idx.get)
+    out = []
+    for a, b, *_ in case["alleles"]:
+        na, nb = names[a], names[b]
+        if na in name2new and nb in name2new:
+            out.append((name2new[na], name2new[nb]))
+    return out
+
+
+def test_kprune_matches_oracle(case):
+    from cphasing_b200 import kprune
+    ah = case["ah"]
+    A = ah.HyperGraph.clique_expansion_init(case["H"], min_weight=1.0, use_high_order=False)
+    Ao = orc.clique_expansion(case["Ho"], use_high_order=False, min_weight=1.0)
+    pairs = _kept_index(case)
+    al, wk = kprune.kprune_pairs(A, pairs)
+    al_o, wk_o = orc.kprune_hypergraph(Ao, pairs)
+    assert al == al_o
+    assert wk == wk_o
+    assert len(al) > 50 and len(wk) > 50           # the case exercises both lists
+
+
+def test_kprune_hypergraph_class_and_table(case):
+    import pandas as pd
+    from cphasing_b200 import kprune
+    ah = case["ah"]
+    A = ah.HyperGraph.clique_expansion_init(case["H"], min_weight=1.0, use_high_order=False)
+    names = list(case["nodes"])
+    c2i = {nm: i for i, nm in enumerate(names)}
+    allg = sorted(case["g"].contig_idx, key=case["g"].contig_idx.get)
+    rows = [(0, 0, allg[a], allg[b], m1, m2, sh, sim, 1) for a, b, m1, m2, sh, sim in case["alleles"]]
+    df = pd.DataFrame(rows, columns=[-1, 0, 1, 2, 3, 4, 5, 6, 7]).set_index(-1)
+
+    class AT:      # the slice of core.AlleleTable the class reads (core.py:289-300)
+        data = df
+    kp = kprune.KPruneHyperGraph(AT(), A, c2i)
+    kp.run()
+    al_o, wk_o = orc.kprune_hypergraph(orc.clique_expansion(case["Ho"], use_high_order=False, min_weight=1.0), _kept_index(case))
+    assert kp.allelic_prune_list == al_o and kp.weak_prune_list == wk_o
+    pt = kp.get_prune_table()
+    assert list(pt.columns) == ['contig1', 'contig2', 'mz1', 'mz2', 'mzShared', 'similarity', 'type']
+    assert (pt["type"] == 0).sum() == len(al_o) and (pt["type"] == 1).sum() == len(wk_o)
+    assert len(kp.get_prune_table(symmetric=True)) == 2 * len(pt)
+
+
+def test_filter_adjacency_matrix_matches_oracle(case):
+    ah = case["ah"]
+    A = ah.HyperGraph.clique_expansion_init(case["H"], min_weight=2.0)
+    Ao = orc.clique_expansion(case["Ho"], min_weight=2.0)
+    sizes = case["g"].contigsizes
+    keep = ah.HyperGraph.filter_adjacency_matrix(A, case["nodes"], sizes)
+    lengths = np.array([sizes[nm] for nm in case["nodes"]], dtype=np.float64)
+    keep_o = orc.filter_adjacency(Ao, lengths)
+    assert np.array_equal(keep, keep_o)
+    assert len(keep) < A.shape[0]
+    import pandas as pd
+    keep2 = ah.HyperGraph.filter_adjacency_matrix(A, case["nodes"], pd.DataFrame({"length": pd.Series(sizes)}))
+    assert np.array_equal(keep2, keep_o)
+
+
+@pytest.mark.parametrize("method,allelic_factor", [("louvain", 0), ("leiden", 0), ("louvain", -1)])
+def test_irmm_matches_oracle(case, method, allelic_factor):
+    """IRMM(H, A, ...) on the device vs oracle: graph preparation (irmm_graph) + sequential clustering.  The synthetic
+    genome has a clear optimum per resolution (20 haplotype groups), so the north-star bar applies."""
+    from cphasing_b200 import kprune
+    ah = case["ah"]
+    A = ah.HyperGraph.clique_expansion_init(case["H"], min_weight=2.0)
+    Ao = orc.clique_expansion(case["Ho"], min_weight=2.0)
+    pairs = _kept_index(case)
+    al, wk = orc.kprune_hypergraph(orc.clique_expansion(case["Ho"], use_high_order=False, min_weight=1.0), pairs)
+    sym = lambda L: [np.array([a for a, b in L] + [b for a, b in L]), np.array([b for a, b in L] + [a for a, b in L])]
+    Pa, Pw = sym(al), sym(wk)
+    raw_A, A2, ca, K = ah.IRMM(case["H"], A, None, Pa, Pw, allelic_factor=allelic_factor, resolution=1.0, method=method)
+    src, dst, w = orc.irmm_graph(Ao, Pa, Pw, allelic_factor)
+    n = Ao.shape[0]
+    G = csr_matrix((np.concatenate([w, w]), (np.concatenate([src, dst]), np.concatenate([dst, src]))), shape=(n, n))
+    use_leiden = method == "leiden" or allelic_factor < 0
+    mem_o, g_o = co.community(G, 1.0, "leiden" if use_leiden else "louvain")
+    mem = np.asarray(ca.membership)
+    q_o = co.modularity(G, mem_o, 1.0)
+    q_g = co.modularity(G, mem, 1.0)
+    assert abs(q_g - q_o) <= 1e-5 * abs(q_o), (q_g, q_o)
+    assert co.ari(mem, mem_o) >= 0.99
+    assert [set(c) for c in ca] == K and sum(len(k) for k in K) == n
+    # the returned A: re-weighted entries and a zero diagonal, raw_A untouched
+    A2 = csr_matrix(A2)
+    assert abs(A2.diagonal()).max() == 0
+    assert abs(csr_matrix(raw_A) - csr_matrix(A)).nnz == 0
+    if al:
+        i, j = al[0]
+        assert A2[i, j] == pytest.approx(allelic_factor * csr_matrix(A)[i, j])
+    if wk:
+        i, j = wk[0]
+        assert A2[i, j] == 0 and A2[j, i] == 0
+    # truth: every haplotype group of the synthetic genome is one cluster at resolution 1?  Not required -- but the
+    # clusters must not mix chromosomes
+    grp = case["g"].group
+    names = sorted(case["g"].contig_idx, key=case["g"].contig_idx.get)
+    name2old = {nm: i for i, nm in enumerate(names)}
+    chrom = np.array([grp[name2old[nm]] // case["g"].ploidy for nm in case["nodes"]])
+    for k in K:
+        if len(k) > 5:
+            vals, cnts = np.unique(chrom[list(k)], return_counts=True)
+            assert cnts.max() >= 0.9 * len(k)
+
+
+def test_irmm_builds_A_when_missing(case):
+    ah = case["ah"]
+    raw_A, A2, ca, K = ah.IRMM(case["H"], None, None, None, None, allelic_factor=0, resolution=1.0, min_weight=2.0)
+    Ao = orc.clique_expansion(case["Ho"], min_weight=2.0)
+    src, dst, w = orc.irmm_graph(Ao)
+    n = Ao.shape[0]
+    G = csr_matrix((np.concatenate([w, w]), (np.concatenate([src, dst]), np.concatenate([dst, src]))), shape=(n, n))
+    mem_o, _ = co.community(G, 1.0, "louvain")
+    assert co.ari(np.asarray(ca.membership), mem_o) >= 0.99
+    with pytest.raises(NotImplementedError):
+        ah.IRMM(case["H"], None, max_round=3)
