@@ -63,6 +63,7 @@ _SIGS = {
     "cph_kprune": (_I, [_P, _P, _P, _P, _U32, _U64, _P, _P, _P, _I, _P, _P, _U64, _P, _P, _P, _P]),
     "cph_community": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _I, _I, _I, _I, _P, _P, C.POINTER(_D), C.POINTER(_U32)] + _WS),
     "cph_modularity": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _P, C.POINTER(_D)] + _WS),
+    "cph_group_sums": (_I, [_P, _P, _P, _P, _U32, _U64, _P, _U32, _P, _P] + _WS),
     "cph_synth_porec_count": (_I, [_U64, _U64, _U64, _I, _P, C.POINTER(_U64)] + _WS),
     "cph_synth_porec_fill": (_I, [_U64, _U64, _U64, _I, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cph_synth_pairs": (_I, [_U64, _U64, _U64, _D, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),

@@ -374,7 +374,7 @@ class HyperGraph:
         deg, _ = graphops.abs_degree(a, skip_diag=False, use32=(A.dtype == np.float32))
         deg = deg.cpu().numpy()
         cs = HyperGraph._to_series_contigsizes(contigsizes, nodes)
-        sizes = pd.Index(np.asarray(nodes).astype(str)).map(cs).to_numpy(dtype=np.float64)
+        sizes = np.array(pd.Index(np.asarray(nodes).astype(str)).map(cs), dtype=np.float64)   # writable copy
         sizes[~np.isfinite(sizes)] = np.nan
         sizes[sizes <= 0] = np.nan
         norm = deg / sizes * 10000.0

@@ -218,6 +218,16 @@ int cph_modularity(const int64_t* indptr, const int32_t* indices, const float* d
                    uint64_t nnz, double resolution, const int32_t* membership, double* h_quality, void* ws, size_t ws_bytes,
                    size_t* h_ws_need, cph_stream_t stream);
 
+/* ---- group-level affinity sums (partition driver post-processing) ---------------------------------
+ * labels: device int32[n], group of each contig in [0, n_groups) or -1 (in no group).
+ * S (device double[n * n_groups], row-major, may be NULL) = A M: linkage of every contig to every group
+ *     (recluster_by_linkage, hyperpartition.py:2889-2892; the diagonal of A is included, as there).
+ * V (device double[n_groups * n_groups], may be NULL) = M^T A M: value_matrix of _merge (hyperpartition.py:2402-2410).
+ * Deterministic (64-bit fixed-point accumulation).  Synchronises `stream` once. */
+int cph_group_sums(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64,
+                   uint32_t n, uint64_t nnz, const int32_t* labels, uint32_t n_groups, double* S, double* V, void* ws,
+                   size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
 /* ---- synthetic workload generators (bench infrastructure; device twin of cphasing_b200/synth.py) ---
  * Seeded, counter-based tables of the shapes BASELINE.json names, written straight to HBM.
  * cph_synth_porec_count: nrec_off (u64[m+1]) <- exclusive prefix of the records per concatemer, *h_total = N.

@@ -386,3 +386,106 @@ def modularity(n, src, dst, w, membership, resolution=1.0):
     same = membership[src] == membership[dst]
     inn = np.bincount(membership[src][same], weights=w[same], minlength=nc)
     return float((inn / m - resolution * (tot / (2 * m)) ** 2).sum())
+
+
+# --------------------------------------------------------------------------------------------
+# stage 5: group post-processing of the partition driver
+# --------------------------------------------------------------------------------------------
+def merge_groups(A, K, size_db, k, allelic_idx_set=(), min_allelic_overlap=0.1, allele_use_method="conflict", method="mean"):
+    """hyperpartition.py:2288-2471 (_merge, alleletable_df=None): greedy merge of the pair of groups with the largest
+    Q_ij = V_ij - V_i. V_j. / sum(triu V), V = M^T A M (mean: divided by the size product), until k groups remain."""
+    K = [list(g) for g in K]
+    A = A.tocsr()
+    it = 0
+    while k and len(K) > k:
+        g = len(K)
+        if it > (g - k + 100):
+            break
+        Kt = [tuple(sorted(x)) for x in K]
+        glen = np.array([sum(size_db.get(c, 0.0) for c in x) for x in Kt])
+        c2g = {c: i for i, x in enumerate(Kt) for c in x}
+        flag = np.ones((g, g)); overlap = np.zeros((g, g))
+        if allelic_idx_set:
+            s1, s2 = {}, {}
+            for c1, c2 in allelic_idx_set:
+                g1, g2 = c2g.get(c1), c2g.get(c2)
+                if g1 is not None and g2 is not None and g1 != g2:
+                    if g1 > g2:
+                        g1, g2, c1, c2 = g2, g1, c2, c1
+                    s1.setdefault((g1, g2), set()).add(c1)
+                    s2.setdefault((g1, g2), set()).add(c2)
+            for (i, j), a in s1.items():
+                l1 = float(sum(size_db.get(c, 0.0) for c in a))
+                l2 = float(sum(size_db.get(c, 0.0) for c in s2.get((i, j), set())))
+                o1 = l1 / glen[i] if glen[i] > 0 else 0
+                o2 = l2 / glen[j] if glen[j] > 0 else 0
+                if o1 > min_allelic_overlap or o2 > min_allelic_overlap:
+                    flag[i, j] = 0
+                    overlap[i, j] = max(o1, o2)
+        rows = [c for x in Kt for c in x]
+        cols = [i for i, x in enumerate(Kt) for _ in x]
+        M = csr_matrix((np.ones(len(rows), dtype=np.float32), (rows, cols)), shape=(A.shape[0], g))
+        V = (M.T.dot(A).dot(M)).toarray().astype(np.float64)
+        np.fill_diagonal(V, 0)
+        if method == "mean":
+            sz = np.array([len(x) for x in Kt], dtype=np.float32)
+            so = np.outer(sz, sz); so[so == 0] = 1.0
+            V = V / so
+        total = max(np.triu(V, 1).sum(), 1e-9)
+        best, bi = None, None
+        for i in range(g):
+            vi = V[i].sum()
+            for j in range(i + 1, g):
+                raw = V[i, j] - (V[j].sum() * vi) / total
+                if flag[i, j]:
+                    q = raw
+                elif allele_use_method == "conflict":
+                    q = -2 ** 64
+                else:
+                    q = max(overlap[i, j] * raw, 0)
+                if best is None or q > best:
+                    best, bi = q, (i, j)
+        i1, i2 = bi
+        K[i1].extend(K[i2])
+        K.pop(i2)
+        it += 1
+    return K
+
+
+def recluster_by_linkage(A, K, contig_lens, min_weight, allelic_idx_set=(), min_ratio=1.5):
+    """hyperpartition.py:2860-2968 (length_norm = False branch).  Returns (new K, number of moved contigs)."""
+    A = A.tocsr()
+    n, g = A.shape[0], len(K)
+    c2g = np.full(n, -1, dtype=int)
+    rows, cols = [], []
+    for gid, grp in enumerate(K):
+        c2g[list(grp)] = gid
+        rows.extend(grp); cols.extend([gid] * len(grp))
+    look = {}
+    for c1, c2 in allelic_idx_set:
+        look.setdefault(c1, set()).add(c2)
+        look.setdefault(c2, set()).add(c1)
+    M = csr_matrix((np.ones(len(rows), dtype=np.float32), (rows, cols)), shape=(n, g))
+    S = A.dot(M).toarray()
+    best = np.argmax(S, axis=1)
+    bS = S[np.arange(n), best]
+    cur = np.zeros(n)
+    valid = c2g != -1
+    cur[valid] = S[np.where(valid)[0], c2g[valid]]
+    tot = S.sum(axis=1)
+    spec = np.divide(bS, tot, out=np.zeros(n), where=tot > 0)
+    mask = (best != c2g) & (bS > cur * min_ratio) & (spec > 0.9) & (tot > min_weight)
+    cand = sorted(np.where(mask)[0], key=lambda x: contig_lens[x], reverse=True)
+    newK = [set(x) for x in K]
+    moved = 0
+    for c in cand:
+        bg, cg = best[c], c2g[c]
+        if S[c, bg] / (tot[c] + 1e-9) < 0.25:
+            continue
+        if look.get(c, set()).isdisjoint(newK[bg]):
+            if cg != -1:
+                newK[cg].discard(c)
+            newK[bg].add(c)
+            c2g[c] = bg
+            moved += 1
+    return ([sorted(int(x) for x in s) for s in newK] if moved else [list(x) for x in K]), moved

@@ -149,3 +149,119 @@ def test_irmm_builds_A_when_missing(case):
     assert co.ari(np.asarray(ca.membership), mem_o) >= 0.99
     with pytest.raises(NotImplementedError):
         ah.IRMM(case["H"], None, max_round=3)
+
+
+# ---- partition driver post-processing (hyperpartition.py:2288-2471, 2860-2968) against the reference's own outputs
+def _groups(labels):
+    labels = np.asarray(labels)
+    return [sorted(np.where(labels == g)[0].tolist()) for g in range(int(labels.max()) + 1)]
+
+
+def _part(K):
+    return sorted(tuple(sorted(int(x) for x in g)) for g in K)
+
+
+def test_group_sums_match_scipy():
+    from helpers import csr_from, load_golden
+    from cphasing_b200 import hyperpartition as hp
+    g = load_golden("partition_post")
+    A = csr_from(g, "A").astype(np.float64)
+    K = _groups(g["K3_labels"])                      # some contigs are in no group (-1)
+    S, V = hp.group_sums(A, K, want_S=True, want_V=True)
+    n = A.shape[0]
+    rows = [c for x in K for c in x]
+    cols = [i for i, x in enumerate(K) for _ in x]
+    M = csr_matrix((np.ones(len(rows)), (rows, cols)), shape=(n, len(K)))
+    np.testing.assert_allclose(S, A.dot(M).toarray(), rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(V, M.T.dot(A).dot(M).toarray(), rtol=1e-9, atol=1e-9)
+
+
+def test_merge_and_recluster_match_reference_golden():
+    from helpers import csr_from, load_golden
+    from cphasing_b200 import hyperpartition as hp
+    import pandas as pd
+    import types
+    g = load_golden("partition_post")
+    A = csr_from(g, "A")
+    n = A.shape[0]
+    vsz = pd.DataFrame({"length": {i: int(g["lengths"][i]) for i in range(n)}})
+    K0 = _groups(g["K0_labels"])
+    G = len(set(g["group"].tolist()))
+    for method in ("mean", "sum"):
+        K1 = hp.HyperPartition._merge(A, [list(x) for x in K0], vsz, k=G, method=method)
+        assert _part(K1) == _part(_groups(g[f"merge_{method}_labels"]))
+        assert [x[0] for x in K1] == g[f"merge_{method}_order"].tolist()        # same merge order too
+    aset = set(map(tuple, g["allelic_pairs"].tolist()))
+    K2 = hp.HyperPartition._merge(A, [list(x) for x in K0], vsz, k=G, allelic_idx_set=aset, min_allelic_overlap=0.1)
+    assert _part(K2) == _part(_groups(g["merge_conflict_labels"]))
+    Ar = csr_from(g, "Ar")
+    fake = types.SimpleNamespace(K=_groups(g["K3_labels"]), allelic_idx_set=set(), min_weight=1.0, H=None,
+                                 idx_to_vertices={i: f"c{i}" for i in range(n)},
+                                 contig_sizes={f"c{i}": int(g["lengths"][i]) for i in range(n)})
+    moved = hp.HyperPartition.recluster_by_linkage(fake, A=Ar, min_ratio=1.5, iter_count=1)
+    assert moved == int(g["recluster_count"][0])
+    assert _part(fake.K) == _part(_groups(g["recluster_labels"]))
+
+
+@pytest.mark.parametrize("normalize", [False, True])
+def test_single_partition_end_to_end(case, tmp_path, normalize):
+    """table -> HyperPartition(...).single_partition(k) with the resolution auto-search: the groups are the planted
+    haplotype groups of the synthetic genome, and the oracle pipeline (H, A, IRMM graph, sequential Louvain at the
+    same resolutions, filter, merge) ends in the same partition."""
+    from cphasing_b200 import hyperpartition as hp, synth
+    from cphasing_b200 import hypergraph as hg
+    g = case["g"]
+    t = synth.porec_table(g, 120_000, seed=20240)
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes,
+                                       min_quality=1, edge_length=0)
+    P = hp.HyperPartition(ex.edges, g.contigsizes, k=[20], min_contacts=25, min_weight=2.0, min_cis_weight=20,
+                          resolution1=-1, init_resolution1=1.0, min_scaffold_length=2_000_000, allelic_factor=0,
+                          normalize=normalize, min_length=10000)
+    K = P.single_partition(k=20)
+    assert len(K) == 20
+    names = list(P.vertices)
+    old = {nm: i for i, nm in enumerate(sorted(g.contig_idx, key=g.contig_idx.get))}
+    truth = np.array([g.group[old[nm]] for nm in names])
+    mem = np.full(len(names), -1)
+    for i, grp in enumerate(K):
+        mem[grp] = i
+    inside = mem >= 0
+    assert inside.mean() > 0.95
+    assert co.ari(mem[inside], truth[inside]) >= 0.99
+    # sorted by total length, descending (:1210-1213)
+    tot = [sum(P.vertices_idx_sizes[i] for i in grp) for grp in K]
+    assert tot == sorted(tot, reverse=True)
+    out = tmp_path / "out.clusters.txt"
+    P.to_cluster(str(out))
+    lines = out.read_text().strip().split("\n")
+    assert len(lines) == 20 and lines[0].startswith("Chr01\t")
+    f = lines[3].split("\t")
+    assert int(f[1]) == len(f[2].split(" ")) == len(K[3])
+
+    # oracle pipeline at the resolutions the search visited
+    Ho = case["Ho"]
+    Ao = orc.clique_expansion(Ho, min_weight=2.0)
+    keep = np.where(Ao.diagonal() >= 20)[0]
+    if len(keep) < Ao.shape[0]:
+        Ho, _, _ = orc.extract_incidence_matrix2(Ho, keep)
+        Ao = orc.clique_expansion(Ho, min_weight=2.0)
+    assert Ao.shape[0] == len(names)
+    if normalize:
+        lens = np.array([g.contigsizes[nm] for nm in names], dtype=np.float64)
+        Ao = orc.normalize_adjacency(Ao, orc.normalize_weight_svc(Ho, lens))
+    src, dst, w = orc.irmm_graph(Ao)
+    n = Ao.shape[0]
+    Gm = csr_matrix((np.concatenate([w, w]), (np.concatenate([src, dst]), np.concatenate([dst, src]))), shape=(n, n))
+    res, glen = P.resolutions_tried[-1]
+    mem_o, _ = co.community(Gm, res, "louvain")
+    sizes = P.vertices_idx_sizes
+    Ko = [np.where(mem_o == c)[0].tolist() for c in range(mem_o.max() + 1)]
+    Ko = [x for x in Ko if sum(sizes[i] for i in x) >= 2_000_000]
+    assert len(Ko) == glen
+    if len(Ko) > 20:
+        Ko = orc.merge_groups(Ao, Ko, {i: float(s) for i, s in sizes.items()}, 20)
+    mo = np.full(n, -1)
+    for i, grp in enumerate(Ko):
+        mo[grp] = i
+    both = (mo >= 0) & (mem >= 0)
+    assert co.ari(mem[both], mo[both]) >= 0.99

@@ -87,3 +87,37 @@ def test_normalise_filter_extract(name):
     assert np.array_equal(np.asarray(kept, dtype=np.int64), g["sub_kept"])
     off = np.sort(orc.find_csr_data_offsets(A.tocsr(), g["pair_r"], g["pair_c"]))
     assert np.array_equal(off, g["pair_offsets"])
+
+
+# ---- partition post-processing: oracle restatements vs outputs of the reference's own _merge / recluster_by_linkage
+def _groups(labels):
+    labels = np.asarray(labels)
+    return [sorted(np.where(labels == g)[0].tolist()) for g in range(int(labels.max()) + 1)]
+
+
+def _same_partition(K, labels):
+    want = sorted(map(tuple, _groups(labels)))
+    got = sorted(tuple(sorted(int(x) for x in g)) for g in K)
+    return want == got
+
+
+def test_oracle_merge_and_recluster_match_reference():
+    g = load_golden("partition_post")
+    A = csr_from(g, "A")
+    n = A.shape[0]
+    sizes = {i: float(g["lengths"][i]) for i in range(n)}
+    K0 = _groups(g["K0_labels"])
+    G = len(set(g["group"].tolist()))
+    for method in ("mean", "sum"):
+        K1 = orc.merge_groups(A, K0, sizes, G, method=method)
+        assert _same_partition(K1, g[f"merge_{method}_labels"])
+        assert [x[0] for x in K1] == g[f"merge_{method}_order"].tolist()
+    aset = set(map(tuple, g["allelic_pairs"].tolist()))
+    K2 = orc.merge_groups(A, K0, sizes, G, allelic_idx_set=aset, min_allelic_overlap=0.1)
+    assert _same_partition(K2, g["merge_conflict_labels"])
+    Ar = csr_from(g, "Ar")
+    lab3 = g["K3_labels"]
+    K3 = _groups(lab3)
+    K4, moved = orc.recluster_by_linkage(Ar, K3, g["lengths"].astype(np.float32), 1.0)
+    assert moved == int(g["recluster_count"][0]) and moved > 0
+    assert _same_partition(K4, g["recluster_labels"])
