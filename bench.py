@@ -24,6 +24,8 @@ sys.path.insert(0, ROOT)
 
 # workload per GPU count: N=1 -> config C (potato-scale Pore-C, 4k contigs, 50M concatemers); N>1 -> config D's
 # genome (20k contigs) with 62.5M concatemers per GPU (500M at N=8): weak scaling over concatemer shards.
+# dram bytes per launch of the dominant kernel from the committed ncu --set full capture, keyed by (workload, m per GPU)
+NCU_TRAFFIC = {("C", 50_000_000): 2572098000 + 2290708000}
 PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight=2.0)   # cphasing/_config.py:38-45
 
 
@@ -259,9 +261,11 @@ def run_own(args):
             stages.setdefault(n1, []).append(e0.elapsed_time(e1))
     stages = {k: sum(v) / len(v) for k, v in stages.items()}
 
-    # roofline of the clique-expansion accumulate kernel (the SpGEMM): algorithmic bytes of stage 2 that this
-    # launch moves = 8 B per H entry read (row + packed count/degree) -- SURVEY.md 8(d); its share of A is written
-    # by the emit kernels.  Pair updates (the work figure) reported beside it.
+    # roofline of the DOMINANT kernel (profiles/r1d_launch_summary.txt: porec_tile_kernel = 45 % of the step on Pore-C
+    # tables; on pairs tables the expansion's expand_kernel).  ALGORITHMIC bytes:
+    #   porec_tile_kernel: 9 B per alignment record read + 8 B per surviving (read, contig) entry written
+    #   expand_kernel    : 8 B per H entry read (row + packed count/degree); its work figure is the pair REDs
+    # duration = CUDA events around the C-ABI call that launches it, averaged over the timed steps.
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -269,15 +273,25 @@ def run_own(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     nnzH, nnzA, n_rows = H.nnz, A.nnz, H.n_rows
-    bytes_acc = 8 * nnzH
     acc_ms = stages.get("accumulate", float("nan"))
+    edges_ms = stages.get("edges", float("nan"))
     stage1_bytes = 9 * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
     stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
     s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
     s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
-    roof = {"bound": "hbm", "kernel": "expand_kernel (cph_expand_accumulate)", "achieved": bytes_acc / acc_ms / 1e6,
-            "peak": peak, "unit": "GB/s", "frac": bytes_acc / acc_ms / 1e6 / peak, "traffic": None,
-            "peak_source": "MEASURED_PEAKS.json hbm_gbs" if peaks else "fallback 6650",
+    per_kernel = {"expand_kernel+diag_hist_kernel (cph_expand_accumulate + cph_diag_hist)":
+                  {"bytes": 8 * nnzH, "ms": acc_ms, "GBps": 8 * nnzH / acc_ms / 1e6, "frac": 8 * nnzH / acc_ms / 1e6 / peak}}
+    if cfg["kind"] == "pairs":
+        kname, kbytes, kms, traffic = "expand_kernel (cph_expand_accumulate)", 8 * nnzH, acc_ms, None
+    else:
+        kname, kbytes, kms = "porec_tile_kernel (cph_porec_to_edges)", 9 * n_rec + 8 * raw.nnz, edges_ms
+        # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/r1d_ncu_full_top3.txt)
+        traffic = NCU_TRAFFIC.get((name, cfg["m"]))
+        per_kernel[kname] = {"bytes": kbytes, "ms": kms, "GBps": kbytes / kms / 1e6, "frac": kbytes / kms / 1e6 / peak}
+    roof = {"bound": "hbm", "kernel": kname, "achieved": kbytes / kms / 1e6, "peak": peak, "unit": "GB/s",
+            "frac": kbytes / kms / 1e6 / peak, "traffic": traffic,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
+            "algorithmic_bytes_per_launch": kbytes, "kernel_ms": kms, "kernels": per_kernel,
             "stage1_GBps": stage1_bytes / s1_ms / 1e6 if s1_ms else None,
             "stage2_GBps": stage2_bytes / s2_ms / 1e6 if s2_ms else None}
     out = {"metric": "concatemers/sec (H build + H*W*H^T)", "value": cfg["m"] * world / (ms_step / 1e3),
