@@ -40,6 +40,7 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=10_000_000, help="concatemers in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-partition", action="store_true", help="skip the kprune + clustering tail (hyperpartition wall s)")
     return ap.parse_args()
 
 
@@ -137,24 +138,65 @@ def device_step(D, cfg, g, t, ev, world, rank):
         raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=PARAMS["min_mapq"],
                                min_order=PARAMS["min_order"], max_order=PARAMS["max_order"])
     mark("edges")
-    hook = None
-    if world > 1:
-        def hook(rs, mx):
-            dist.all_reduce(rs)          # global per-contig contact sums for the min_contacts row filter
-            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
-            return rs, mx
-    H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0, rowsum_hook=hook)
+    from cphasing_b200 import parallel as par
+    # exchange 1 (world > 1): global per-contig contact sums + largest count for the min_contacts row filter
+    H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0,
+                    rowsum_hook=par.allreduce_rowsums if world > 1 else None)
     mark("incidence")
     # the fixed-point scale derives from the (all-reduced) row sums, so every rank picks the same one
     acc = D.expand_accumulate(H, use_high_order=True)
     mark("accumulate")
     if world > 1:
-        dist.all_reduce(acc.acc)
-        dist.all_reduce(acc.diag)
-        mark("allreduce")
+        par.sum_triangle(acc.acc, acc.n)     # exchange 2: reduce-scatter over contig row blocks + all-gather (NCCL)
+        par.sum_vector(acc.diag)
+        mark("exchange")
     A = D.expand_emit(acc, min_weight=PARAMS["min_weight"], want32=True, want64=True)
     mark("emit")
     return raw, H, A
+
+
+def partition_tail(D, cfg, g, H, A, reps=3):
+    """the rest of `hyperpartition` on the device-resident H / A of the last step: unweighted expansion -> kprune
+    (allelic + cross-allelic pairs from the synthetic allele table) -> pair re-weighting -> Louvain at resolution 1.
+    Wall-clock (synchronised) per stage, best of `reps`; ARI of the clustering against the planted haplotype groups."""
+    import torch
+    from cphasing_b200 import community, graphops, kprune, synth
+    keep = H.row_keep.cpu().numpy() if H.row_keep is not None else np.ones(g.n, bool)
+    new = np.cumsum(keep) - 1
+    pairs = np.array([(new[a], new[b]) for a, b, *_ in synth.allele_pairs(g, seed=cfg["seed"] + 1) if keep[a] and keep[b]],
+                     dtype=np.int64).reshape(-1, 2)
+    best = {}
+    out = {}
+    G = g.G
+    for _ in range(reps):
+        tm = {}
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        Au, _ = D.clique_expansion(H, use_high_order=False, min_weight=1.0, want32=False, want64=True)
+        flag, row_of = kprune.kprune_device(Au, pairs, 1)
+        al = torch.nonzero(flag == 1).flatten(); wk = torch.nonzero(flag == 2).flatten()
+        Pa = (torch.cat([row_of[al], Au.indices[al]]), torch.cat([Au.indices[al], row_of[al]]))     # symmetrised, on device
+        Pw = (torch.cat([row_of[wk], Au.indices[wk]]), torch.cat([Au.indices[wk], row_of[wk]]))
+        torch.cuda.synchronize(); tm["kprune_ms"] = (time.perf_counter() - t0) * 1e3; t0 = time.perf_counter()
+        a = graphops.clone_adjacency(A)
+        graphops.reweight_device(a, Pa, Pw, 0.0, 0.0)
+        # resolution auto-search of hyperpartition.py:1049-1078: start at 1.0, +0.2 until at least G groups
+        gamma, rounds = 1.0, 0
+        while True:
+            mem, q, st = community.community_device(a, gamma, "louvain")
+            rounds += 1
+            if st["groups"] >= G or rounds >= 50:
+                break
+            gamma += 0.2
+        torch.cuda.synchronize(); tm["cluster_ms"] = (time.perf_counter() - t0) * 1e3
+        for k_, v in tm.items():
+            best[k_] = min(best.get(k_, v), v)
+        out = {"allelic_pairs": int(al.numel()), "weak_pairs": int(wk.numel()), "groups": st["groups"], "planted_groups": G,
+               "modularity": q, "resolution": round(gamma, 2), "clusterings": rounds, "cluster_ms_each": tm["cluster_ms"] / rounds}
+    from oracle import community_oracle as co          # checker only: ARI against the planted groups
+    truth = g.group[keep]
+    out["ari_vs_planted"] = float(co.ari(mem.cpu().numpy(), truth))
+    out.update(best)
+    return out
 
 
 def e2e_step(cfg, g, host, names):
@@ -303,6 +345,12 @@ def run_own(args):
                       "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
                       "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
            "stages_ms": stages, "roofline": roof, "clocks": clk}
+    if rank == 0 and world == 1 and not args.no_partition:
+        tail = partition_tail(D, cfg, g, H, A)
+        tail["wall_s"] = (ms_step + tail["kprune_ms"] + tail["cluster_ms"]) / 1e3
+        tail["what"] = ("table -> H -> A (ms_per_step) + unweighted expansion + kprune + pair re-weighting + Louvain "
+                        "inside the resolution auto-search (1.0, +0.2 until >= planted groups), device-resident")
+        out["hyperpartition"] = tail
     if rank == 0 and world == 1 and not args.no_e2e:
         import torch
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in t.items()}

@@ -1,0 +1,121 @@
+"""Multi-GPU form of stages 1-2: one process per GPU, concatemer-column shards, NCCL through
+``torch.distributed``.
+
+Why it shards: W is diagonal and column-local (``D_e`` depends only on the hyperedge's own entries,
+algorithms/hypergraph.py:385), so with rank r owning a contiguous range of concatemer ids
+
+    A = sum_r  H_r W_r H_r^T .
+
+Exchanges per pass (everything else is local):
+  1. all-reduce of the per-contig contact sums (n x int64) and of the largest count (1 x int32): the ``min_contacts`` row
+     filter (algorithms/hypergraph.py:286-300) is global, and every rank must pick the same fixed-point scale;
+     the column filter (sum of counts >= 2, :305-306) is column-local and needs nothing.
+  2. sum of the partial accumulators (packed upper triangle, 64-bit fixed point, integer => order independent and
+     bit-identical on every rank).  On NCCL this is a reduce-scatter over contiguous CONTIG ROW BLOCKS of the triangle
+     followed by an all-gather of the reduced blocks; on other backends (gloo in the CPU tests) one all-reduce.
+Clustering (stage 4) then runs replicated: the kernels are deterministic, so every rank computes the same membership
+from the same A without any exchange (n <= 2*10^4 vertices is latency-bound, SURVEY.md 8e caveat).
+
+The functions take tensors on whatever device the process group works on, so the collective logic is exercised on CPU
+with gloo (tests/test_parallel_cpu.py) and on NVLink with NCCL (bench.py --gpus N).
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def world():
+    return (dist.get_rank(), dist.get_world_size()) if dist.is_available() and dist.is_initialized() else (0, 1)
+
+
+def shard_range(m, rank, world_size):
+    """contiguous concatemer-id range [first, first + count) of `rank`; the ranges tile [0, m) exactly."""
+    base, rem = divmod(int(m), int(world_size))
+    first = rank * base + min(rank, rem)
+    return first, base + (1 if rank < rem else 0)
+
+
+def tri_offset(i, n):
+    """index of (i, i) in the packed upper triangle acc[i(2n-i+1)/2 + (j-i)]."""
+    return i * (2 * n - i + 1) // 2
+
+
+def row_blocks(n, world_size):
+    """contig row blocks [lo, hi) whose packed-triangle slices have (nearly) equal element counts: rank r reduces the
+    rows of block r.  Returns a list of (row_lo, row_hi)."""
+    total = n * (n + 1) // 2
+    cuts = [0]
+    for r in range(1, world_size):
+        target = total * r // world_size
+        # smallest i with tri_offset(i) >= target
+        lo, hi = cuts[-1], n
+        while lo < hi:
+            mid = (lo + hi) // 2
+            if tri_offset(mid, n) >= target:
+                hi = mid
+            else:
+                lo = mid + 1
+        cuts.append(lo)
+    cuts.append(n)
+    return [(cuts[r], cuts[r + 1]) for r in range(world_size)]
+
+
+def allreduce_rowsums(rowsum, max_count, group=None):
+    """exchange 1: global contact sums and largest count (used as the `rowsum_hook` of device.incidence)."""
+    if world()[1] > 1:
+        dist.all_reduce(rowsum, op=dist.ReduceOp.SUM, group=group)
+        dist.all_reduce(max_count, op=dist.ReduceOp.MAX, group=group)
+    return rowsum, max_count
+
+
+def sum_triangle(acc, n, group=None):
+    """exchange 2: acc (int64 packed upper triangle of n rows, fixed point) <- sum over ranks, in place.
+
+    NCCL: reduce-scatter over the row blocks of ``row_blocks`` (padded to equal length), then all-gather.  Each rank
+    therefore owns the reduced rows of its block between the two steps -- the hook for a row-partitioned consumer."""
+    rank, ws = world()
+    if ws == 1:
+        return acc
+    backend = dist.get_backend(group)
+    if backend != "nccl":
+        dist.all_reduce(acc, op=dist.ReduceOp.SUM, group=group)
+        return acc
+    blocks = row_blocks(n, ws)
+    offs = [tri_offset(lo, n) for lo, _ in blocks] + [n * (n + 1) // 2]
+    sizes = [offs[r + 1] - offs[r] for r in range(ws)]
+    chunk = max(sizes)
+    if all(s == chunk for s in sizes):
+        send = acc[:chunk * ws]
+    else:
+        send = torch.zeros(chunk * ws, dtype=acc.dtype, device=acc.device)
+        for r in range(ws):
+            send[r * chunk:r * chunk + sizes[r]] = acc[offs[r]:offs[r + 1]]
+    mine = torch.empty(chunk, dtype=acc.dtype, device=acc.device)
+    dist.reduce_scatter_tensor(mine, send, op=dist.ReduceOp.SUM, group=group)
+    dist.all_gather_into_tensor(send, mine, group=group)
+    if send.data_ptr() != acc.data_ptr():
+        for r in range(ws):
+            acc[offs[r]:offs[r + 1]] = send[r * chunk:r * chunk + sizes[r]]
+    return acc
+
+
+def sum_vector(v, group=None):
+    if world()[1] > 1:
+        dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)
+    return v
+
+
+def sharded_clique_expansion(raw, min_contacts=25, min_weight=2.0, use_high_order=True, node_w=None, group=None,
+                             want32=True, want64=True):
+    """stage 1c + 2 on this rank's shard `raw` (device.RawEdges of its concatemers) with the two exchanges.
+    Returns (DeviceH of the shard, DeviceCSR of the GLOBAL A, identical on every rank)."""
+    from . import device as D
+    H = D.incidence(raw, min_contacts=min_contacts, min_mapq=0,
+                    rowsum_hook=lambda rs, mx: allreduce_rowsums(rs, mx, group))
+    acc = D.expand_accumulate(H, use_high_order=use_high_order)       # scale from the all-reduced bound: same everywhere
+    sum_triangle(acc.acc, acc.n, group)
+    sum_vector(acc.diag, group)
+    A = D.expand_emit(acc, min_weight=min_weight, node_w=node_w, want32=want32, want64=want64)
+    return H, A

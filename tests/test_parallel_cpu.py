@@ -1,0 +1,107 @@
+"""World-size-2 gloo tests (CPU) of the multi-GPU host logic in cphasing_b200/parallel.py: shard ranges, row blocks,
+and that the two exchanges reproduce the single-process result.  The per-shard arithmetic here is done by the ORACLE
+(test infrastructure) -- on the GPU box the same collectives move the CUDA kernels' partial accumulators."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from cphasing_b200 import parallel as par
+
+
+def test_shard_ranges_tile_exactly():
+    for m in (0, 1, 7, 1000, 500_000_001):
+        for ws in (1, 2, 3, 8):
+            pos = 0
+            for r in range(ws):
+                first, cnt = par.shard_range(m, r, ws)
+                assert first == pos and cnt >= 0
+                pos += cnt
+            assert pos == m
+            sizes = [par.shard_range(m, r, ws)[1] for r in range(ws)]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_row_blocks_cover_and_balance():
+    for n in (1, 5, 400, 4000, 20000):
+        for ws in (1, 2, 4, 8):
+            blocks = par.row_blocks(n, ws)
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(ws - 1))
+            if n >= 400:
+                tot = n * (n + 1) // 2
+                sz = [par.tri_offset(hi, n) - par.tri_offset(lo, n) for lo, hi in blocks]
+                assert sum(sz) == tot
+                assert max(sz) - min(sz) <= 2 * n            # within one row of perfect balance
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, ws, port, m, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        from cphasing_b200 import synth
+        from oracle import hypergraph_oracle as orc
+        g = synth.make_genome(60, 3, 2, seed=11)
+        first, cnt = par.shard_range(m, rank, ws)
+        t = synth.porec_table(g, cnt, seed=12, first=first)
+        r, c, k, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=1, n_contigs=g.n)
+        # exchange 1: global row sums / max count
+        rs = torch.from_numpy(np.bincount(r, weights=k, minlength=g.n).astype(np.int64))
+        mx = torch.tensor([int(k.max()) if len(k) else 0], dtype=torch.int32)
+        par.allreduce_rowsums(rs, mx)
+        keep = rs.numpy() >= 25
+        c = c - first if len(c) else c
+        H, _, _ = orc.incidence_matrix(r, c, k, g.n, max(int(c.max()) + 1 if len(c) else 1, 1), 0)
+        H = H[keep]
+        H = H[:, np.asarray(H.sum(axis=0)).ravel() >= 2]                 # the column filter is column-local
+        n = H.shape[0]
+        C = orc.contact_counts(H).toarray().astype(np.int64)             # integer partial of this shard
+        iu = np.triu_indices(n)
+        acc = torch.from_numpy(np.ascontiguousarray(C[iu]))              # packed upper triangle, row-major
+        par.sum_triangle(acc, n)                                         # exchange 2
+        q.put((rank, rs.numpy(), int(mx.item()), n, acc.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_column_shards_reproduce_the_single_process_counts():
+    from cphasing_b200 import synth
+    from oracle import hypergraph_oracle as orc
+    m, ws = 4000, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, ws, port, m, q)) for r in range(ws)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=240) for _ in range(ws)], key=lambda x: x[0])
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    # single process
+    g = synth.make_genome(60, 3, 2, seed=11)
+    t = synth.porec_table(g, m, seed=12)
+    r, c, k, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=1, n_contigs=g.n)
+    rs = np.bincount(r, weights=k, minlength=g.n).astype(np.int64)
+    H, _, _ = orc.incidence_matrix(r, c, k, g.n, int(c.max()) + 1, 25)
+    C = orc.contact_counts(H).toarray().astype(np.int64)
+    iu = np.triu_indices(H.shape[0])
+    for rank, rs_r, mx_r, n_r, acc_r in res:
+        assert np.array_equal(rs_r, rs)
+        assert mx_r == int(k.max())
+        assert n_r == H.shape[0]
+        assert np.array_equal(acc_r, C[iu]), "summed integer partials must be bit-exact"
