@@ -136,33 +136,59 @@ __device__ __forceinline__ Best warp_best(Best b) {
     return b;
 }
 
+// group of G threads (a warp, or the whole CTA for high-degree levels) that works on one vertex at a time
+template <int G>
+__device__ __forceinline__ void group_sync() {
+    if (G == 32) __syncwarp();
+    else __syncthreads();
+}
+template <int G>
+__device__ __forceinline__ Best group_best(Best b, Best* sm) {
+    b = warp_best(b);
+    if (G == 32) return b;
+    const int w = threadIdx.x >> 5;
+    if (lane_id() == 0) sm[w] = b;
+    __syncthreads();
+    Best r = sm[0];
+#pragma unroll
+    for (int q = 1; q < G / 32; ++q) {
+        Best o = sm[q];
+        if (o.c >= 0 && (r.c < 0 || o.gain > r.gain || (o.gain == r.gain && o.c < r.c))) r = o;
+    }
+    __syncthreads();
+    return r;
+}
+
 // proposals for the vertices v = first + phase + i * n_phases (< last).  prop[v] = chosen community (or comm[v]).
-// `strip` = n_warps private rows of g.n int64 zeros (left zero again on exit).
+// `strip` = one private row of g.n int64 zeros per group (left zero again on exit).
+template <int G>
 __global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int phase, int n_phases, int first, int last,
                                                                   const i32* __restrict__ comm, const i64* __restrict__ tot,
                                                                   const i32* __restrict__ csize, const i64* __restrict__ k,
                                                                   double gamma, double m2, i64* __restrict__ strip,
                                                                   i32* __restrict__ prop) {
-    const int n_warps = gridDim.x * CM_WPB;
-    const int gw = blockIdx.x * CM_WPB + (threadIdx.x >> 5);
-    const u32 lane = lane_id();
-    i64* sc = strip + (size_t)gw * g.n;
-    for (i64 v = (i64)first + phase + (i64)gw * n_phases; v < last; v += (i64)n_warps * n_phases) {
+    __shared__ Best sm_best[CM_WPB];
+    constexpr int GPB = CM_THREADS / G;                       // groups per block
+    const int n_groups = gridDim.x * GPB;
+    const int gi = blockIdx.x * GPB + threadIdx.x / G;
+    const u32 lane = threadIdx.x % G;
+    i64* sc = strip + (size_t)gi * g.n;
+    for (i64 v = (i64)first + phase + (i64)gi * n_phases; v < last; v += (i64)n_groups * n_phases) {
         const int old = comm[v];
         const i64 kv = k[v];
         const i64 b = g.beg[v], e = g.end[v];
-        for (i64 t = b + lane; t < e; t += 32) {
+        for (i64 t = b + lane; t < e; t += G) {
             int u = g.idx[t];
             i64 w = g.w[t];
             if (u != v && w != 0) add64(&sc[comm[u]], w);
         }
-        __syncwarp();
+        group_sync<G>();
         const double stay = (double)ld_cg(&sc[old]) - pen(gamma, kv, tot[old] - kv, m2);
         const bool old_single = csize[old] == 1;
         Best best;
         best.gain = 0;
         best.c = -1;
-        for (i64 t = b + lane; t < e; t += 32) {
+        for (i64 t = b + lane; t < e; t += G) {
             int u = g.idx[t];
             i64 w = g.w[t];
             if (u == v || w == 0) continue;
@@ -175,13 +201,13 @@ __global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int 
                 best.c = c;
             }
         }
-        best = warp_best(best);
-        __syncwarp();
-        for (i64 t = b + lane; t < e; t += 32) {
+        best = group_best<G>(best, sm_best);
+        group_sync<G>();
+        for (i64 t = b + lane; t < e; t += G) {
             int u = g.idx[t];
             if (u != v) st_cg(&sc[comm[u]], 0);
         }
-        __syncwarp();
+        group_sync<G>();
         if (lane == 0) prop[v] = (best.c >= 0 && best.gain > stay) ? best.c : old;
     }
 }
@@ -558,6 +584,9 @@ int quality(State& S, const LGraph& g, const i32* comm, double* Q) {
 }
 
 int local_moving(State& S, const LGraph& g, bool* moved) {
+    // rows of >= 128 entries on average (the dense level-0 graph of a clique expansion): a CTA per vertex keeps the
+    // machine full where a warp per vertex would leave it latency bound
+    const bool cta_mode = g.w == S.w0 && S.nnz0 / (g.n > 0 ? g.n : 1) >= 128;
     TRY(totals(S, g, S.comm));
     double bestQ;
     TRY(quality(S, g, S.comm, &bestQ));
@@ -570,10 +599,16 @@ int local_moving(State& S, const LGraph& g, bool* moved) {
         for (int ph = 0; ph < P; ++ph) {
             int cnt = (g.n - ph + P - 1) / P;
             if (cnt <= 0) continue;
-            int blocks = (int)ceil_div((size_t)cnt, CM_WPB);
-            if (blocks > S.blocks) blocks = S.blocks;
-            move_propose_kernel<<<blocks, CM_THREADS, 0, S.st>>>(g, ph, P, 0, g.n, S.comm, S.tot, S.csize, S.k, S.gamma, S.m2,
-                                                                 S.strip, S.prop);
+            if (cta_mode) {          // one CTA per vertex: S.blocks * CM_WPB strips are available
+                int blocks = cnt < S.blocks * CM_WPB ? cnt : S.blocks * CM_WPB;
+                move_propose_kernel<CM_THREADS><<<blocks, CM_THREADS, 0, S.st>>>(g, ph, P, 0, g.n, S.comm, S.tot, S.csize, S.k,
+                                                                                 S.gamma, S.m2, S.strip, S.prop);
+            } else {
+                int blocks = (int)ceil_div((size_t)cnt, CM_WPB);
+                if (blocks > S.blocks) blocks = S.blocks;
+                move_propose_kernel<32><<<blocks, CM_THREADS, 0, S.st>>>(g, ph, P, 0, g.n, S.comm, S.tot, S.csize, S.k, S.gamma,
+                                                                         S.m2, S.strip, S.prop);
+            }
             KERNEL_CHECK();
             move_commit_kernel<<<tgrid(cnt), 256, 0, S.st>>>(ph, P, 0, g.n, S.comm, S.prop, S.k, S.tot, S.csize, &S.sc->moves);
             KERNEL_CHECK();

@@ -29,7 +29,8 @@ def gpu_cluster(A, gamma, method, **kw):
 
 
 @pytest.mark.parametrize("method", ["louvain", "leiden"])
-@pytest.mark.parametrize("n,g,p_in,p_out,seed", [(300, 6, 0.4, 0.01, 1), (1200, 12, 0.3, 0.005, 5), (64, 2, 0.9, 0.02, 7)])
+@pytest.mark.parametrize("n,g,p_in,p_out,seed", [(300, 6, 0.4, 0.01, 1), (1200, 12, 0.3, 0.005, 5), (64, 2, 0.9, 0.02, 7),
+                                                  (800, 4, 0.9, 0.1, 13)])     # last case: mean degree > 128 -> CTA-per-vertex path
 def test_planted_partition_matches_oracle(method, n, g, p_in, p_out, seed):
     A, truth = planted(n, g, p_in, p_out, seed)
     mem_o, g_o = co.community(A, 1.0, method)
