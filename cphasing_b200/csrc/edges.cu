@@ -242,12 +242,15 @@ __device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (co
 }
 
 struct PtSmem {
-    u32 read[PT_WIN];
-    u32 cvq[PT_WIN];
+    alignas(16) u32 read[PT_WIN];
+    alignas(16) u32 cvq[PT_WIN];
     u32 cnt[PT_WIN];
+    alignas(16) u8 mq[PT_WIN];   // raw MAPQ bytes of the window (bulk-copy staging)
+    alignas(8) unsigned long long mbar;
+    u32 ord[PT_WIN];            // at the first record of a read: number of its (read, contig) representatives
     u32 head[PT_WORDS];
     u32 rep[PT_WORDS];
-    u32 rpref[PT_WORDS + 1];
+    u32 first[PT_WORDS];        // representative with no valid record before it in its read: head of the hyperedge
     u32 keep[PT_WORDS];
     u32 kpref[PT_WORDS + 1];
     int beg, end, last;
@@ -277,25 +280,38 @@ __device__ __forceinline__ void pt_word_prefix(const u32* __restrict__ words, u3
         if (tid == 31) pref[PT_WORDS] = incl;
     }
 }
-__device__ __forceinline__ u32 pt_rank(const u32* __restrict__ words, const u32* __restrict__ pref, int x) {   // set bits in [0, x)
-    int w = x >> 5;
-    return w >= PT_WORDS ? pref[PT_WORDS] : pref[w] + __popc(words[w] & ((1u << (x & 31)) - 1u));
-}
 __device__ __forceinline__ int pt_seg_start(const u32* __restrict__ head, int i) {   // last head <= i (exists)
     int w = i >> 5;
     u32 m = head[w] & (0xffffffffu >> (31 - (i & 31)));
     while (m == 0) m = head[--w];
     return w * 32 + 31 - __clz(m);
 }
-__device__ __forceinline__ int pt_seg_end(const u32* __restrict__ head, int i, int fend) {   // first head > i, capped
-    int w = i >> 5;
-    u32 m = head[w] & ~((2u << (i & 31)) - 1u);
-    while (m == 0 && ++w < PT_WORDS) m = head[w];
-    int e = m ? w * 32 + __ffs(m) - 1 : fend;
-    return min(e, fend);
+// TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
+// signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
+__device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, u32 bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
+    u32 ok;
+    do {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok)
+                     : "r"(smem_u32(bar)), "r"(phase)
+                     : "memory");
+    } while (!ok);
 }
 
-__global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, u32 min_order, u32 max_order, u32 read_offset,
+__global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                 unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
                                                                 u32* __restrict__ rem_row, u32* __restrict__ rem_col,
                                                                 u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
@@ -308,6 +324,7 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, u32 
         S.end = 0x7fffffff;
         S.last = -1;
         S.long_order = 0;
+        if (use_tma) mbar_init(&S.mbar, 1);
     }
     __syncthreads();
     const u32 tile = S.tile;
@@ -315,11 +332,35 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, u32 
     const size_t N = in.n;
     const int own = (int)min((size_t)PT_TILE, N - lo);           // records of the tile proper
     const int wn = (int)min((size_t)PT_WIN, N - lo);             // records staged
-    for (int i = tid; i < wn; i += PT_THREADS) {
-        size_t t = lo + i;
-        S.read[i] = in.read[t];
-        S.cvq[i] = porec_cvq(in, t);
-        S.cnt[i] = 1u;
+    if (use_tma && wn == PT_WIN) {
+        // full window, 16-byte aligned columns, no edge filter: three bulk copies, then an in-place pack of
+        // (contig, mapq) -> cvq.  The tile origin lo is a multiple of PT_TILE, so every source stays aligned.
+        if (tid == 0) {
+            mbar_expect_tx(&S.mbar, PT_WIN * 9u);
+            bulk_g2s(S.read, in.read + lo, PT_WIN * 4u, &S.mbar);
+            bulk_g2s(S.cvq, in.contig + lo, PT_WIN * 4u, &S.mbar);
+            bulk_g2s(S.mq, in.mapq + lo, PT_WIN, &S.mbar);
+        }
+        for (int i = tid; i < PT_WIN; i += PT_THREADS) {
+            S.cnt[i] = 1u;
+            S.ord[i] = 0u;
+        }
+        mbar_wait(&S.mbar, 0);
+        for (int i = tid; i < PT_WIN; i += PT_THREADS) {
+            const u32 c = S.cvq[i];
+            const int8_t q = (int8_t)S.mq[i];
+            bool ok = c < in.n_contigs;
+            if (in.min_mapq > 0) ok = ok && (int)q >= in.min_mapq;                  // hypergraph.py:1774-1775
+            S.cvq[i] = ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
+        }
+    } else {
+        for (int i = tid; i < wn; i += PT_THREADS) {
+            size_t t = lo + i;
+            S.read[i] = in.read[t];
+            S.cvq[i] = porec_cvq(in, t);
+            S.cnt[i] = 1u;
+            S.ord[i] = 0u;
+        }
     }
     __syncthreads();
     const u32 prev_read = lo > 0 ? in.read[lo - 1] : 0u;
@@ -359,43 +400,51 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, u32 
             fend = S.last;            // the last read of the tile overflows the window
         }
     }
-    // P1: representative = first valid record of its (read, contig); later ones fold count / max MAPQ into it
-    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+    // P1: representative = first valid record of its (read, contig); later ones fold count / max MAPQ into it.  Each
+    // representative also bumps the order counter kept at the first record of its read.
+    const int p_end = empty ? 0 : fend;                                    // block-uniform loop bound
+    for (int i0 = 0; i0 < p_end; i0 += PT_THREADS) {
         int i = i0 + tid;
-        bool rep = false;
-        if (!empty && i >= beg && i < fend) {
+        bool rep = false, first = false;
+        if (i >= beg && i < fend) {
             const u32 x = S.cvq[i], c = x >> 8;
             if (c != PT_INVALID) {
                 rep = true;
+                first = true;
                 const int s0 = pt_seg_start(S.head, i);
-                for (int j = s0; j < i; ++j)
-                    if ((S.cvq[j] >> 8) == c) {
+                for (int j = s0; j < i; ++j) {
+                    const u32 cj = S.cvq[j] >> 8;
+                    if (cj != PT_INVALID) first = false;
+                    if (cj == c) {
                         rep = false;
                         atomicAdd(&S.cnt[j], 1u);
                         atomicMax(&S.cvq[j], x);      // same contig bits, larger MAPQ byte wins
                         break;
                     }
+                }
+                if (rep) atomicAdd(&S.ord[s0], 1u);
             }
         }
         u32 m = __ballot_sync(0xffffffffu, rep);
-        if (lane == 0) S.rep[i >> 5] = m;
+        u32 f = __ballot_sync(0xffffffffu, rep && first);
+        if (lane == 0) {
+            S.rep[i >> 5] = m;
+            S.first[i >> 5] = f;
+        }
     }
+    for (int w = (p_end + 31) / 32 + tid; w < PT_WORDS; w += PT_THREADS) S.keep[w] = 0u;
     __syncthreads();
-    pt_word_prefix(S.rep, S.rpref, tid);
-    __syncthreads();
-    // P2: distinct-contig order of the read = representatives in its segment
+    // P2: distinct-contig order of the read (hypergraph.py:1461-1468) decides which representatives survive
     u32 my_max_read = 0;
-    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+    for (int i0 = 0; i0 < p_end; i0 += PT_THREADS) {
         int i = i0 + tid;
         bool keep = false;
-        if (!empty && i >= beg && i < fend && ((S.rep[i >> 5] >> (i & 31)) & 1u)) {
-            const int s0 = pt_seg_start(S.head, i), e0 = pt_seg_end(S.head, i, fend);
-            const u32 rs = pt_rank(S.rep, S.rpref, s0);
-            const u32 order = pt_rank(S.rep, S.rpref, e0) - rs;
+        if (i >= beg && i < fend && ((S.rep[i >> 5] >> (i & 31)) & 1u)) {
+            const u32 order = S.ord[pt_seg_start(S.head, i)];
             keep = order >= min_order && order <= max_order;
             if (keep) {
                 my_max_read = S.read[i];
-                if (pt_rank(S.rep, S.rpref, i) == rs) S.cnt[i] |= CPH_HEAD;     // first entry of the hyperedge
+                if ((S.first[i >> 5] >> (i & 31)) & 1u) S.cnt[i] |= CPH_HEAD;     // first entry of the hyperedge
             }
         }
         u32 m = __ballot_sync(0xffffffffu, keep);
@@ -622,7 +671,9 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
         CUDA_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
         CUDA_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
         CUDA_TRY(cudaFuncSetAttribute(porec_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmem)));
-        porec_tile_kernel<<<ntiles, PT_THREADS, sizeof(PtSmem), st>>>(in, min_order, max_order, read_offset,
+        // bulk (TMA) window loads need 16-byte aligned columns; the edge filter reads two more columns -> plain loads
+        const int use_tma = edge_length == 0 && (((uintptr_t)read_idx | (uintptr_t)contig_idx | (uintptr_t)mapq) & 15) == 0;
+        porec_tile_kernel<<<ntiles, PT_THREADS, sizeof(PtSmem), st>>>(in, use_tma, min_order, max_order, read_offset,
                                                                      (unsigned long long*)tile_state, scal, rem_row, rem_col,
                                                                      rem_count, rem_mapq);
         KERNEL_CHECK();

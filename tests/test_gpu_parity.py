@@ -334,3 +334,26 @@ def test_incidence_long_hyperedges(api):
     for x, y in zip(canon_dup(sub), canon_dup(so)):
         assert np.array_equal(x, y)
     assert np.array_equal(kept, ko)
+
+
+def test_porec_edges_unaligned_device_columns(api):
+    """the bulk (TMA) window loads need 16-byte aligned columns; views that start 4 bytes off take the plain-load path
+    and must give the same triplets."""
+    import torch
+    _, hg, D, synth = api
+    g = synth.make_genome(150, 5, 2, seed=5)
+    t = synth.porec_table(g, 20000, seed=6)
+    exp = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=1, min_order=2, max_order=50, n_contigs=g.n)
+    dev = torch.device("cuda")
+    pad = lambda a, dt: torch.cat([torch.zeros(1, dtype=dt, device=dev), torch.from_numpy(a.view(
+        {torch.int32: np.int32, torch.int8: np.int8}[dt])).to(dev)])[1:]
+    r = pad(t["read_idx"], torch.int32).view(torch.uint32)
+    c = pad(t["contig_idx"], torch.int32).view(torch.uint32)
+    q = pad(t["mapq"], torch.int8)
+    assert r.data_ptr() % 16 != 0
+    for cols in ((r, c, q), (r.clone(), c.clone(), q.clone())):          # unaligned views, then aligned copies
+        raw = D.porec_to_edges(cols[0], cols[1], cols[2], g.n, min_mapq=1, min_order=2, max_order=50)
+        row, col, cnt, mq = D.edges_to_triplets(raw)
+        got = (row.cpu().numpy(), col.cpu().numpy(), cnt.view(torch.int32).cpu().numpy().view(np.uint32), mq.cpu().numpy())
+        for a, b in zip(got, exp):
+            assert np.array_equal(a, b)
