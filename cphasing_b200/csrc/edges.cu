@@ -220,8 +220,8 @@ __global__ void __launch_bounds__(TPB) porec_emit_kernel(KeyView kv, const u32* 
 // window is handled by a slow cooperative walk over global memory.
 // ------------------------------------------------------------------------------------------------
 constexpr int PT_THREADS = 512;
-constexpr int PT_TILE = 4096;
-constexpr int PT_HALO = 1024;
+constexpr int PT_TILE = 3584;     // + halo = 4096-record window: 70 KB of shared memory, 3 CTAs per SM
+constexpr int PT_HALO = 512;
 constexpr int PT_WIN = PT_TILE + PT_HALO;
 constexpr int PT_WORDS = PT_WIN / 32;
 constexpr u32 PT_INVALID = 0x00ffffffu;          // contig field of a filtered-out record (n_contigs < 2^23)
