@@ -200,7 +200,7 @@ def partition_tail(D, cfg, g, H, A, reps=3):
     return out
 
 
-def e2e_step(cfg, g, host, names):
+def e2e_step(cfg, g, host, names, trace=None):
     """host (pinned) buffers -> reference-facing classes -> scipy CSR of A on the host."""
     import torch
     from cphasing_b200 import hypergraph as hg
@@ -213,11 +213,20 @@ def e2e_step(cfg, g, host, names):
         ex = hg.HyperExtractor.from_arrays(host["read_idx"], host["contig_idx"], host["mapq"], idx, sizes,
                                            min_quality=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
                                            max_order=PARAMS["max_order"], edge_length=0)
+    tr = trace is not None
+    if tr:
+        torch.cuda.synchronize(); trace["extract (H2D + group-by)"] = time.perf_counter()
     HG = ah.HyperGraph(ex.edges, min_quality=PARAMS["min_mapq"], mapq_filter=False)
     H = HG.incidence_matrix(PARAMS["min_contacts"])
+    if tr:
+        torch.cuda.synchronize(); trace["incidence"] = time.perf_counter()
     A = ah.HyperGraph.clique_expansion_init(H, min_weight=PARAMS["min_weight"])
+    if tr:
+        torch.cuda.synchronize(); trace["expansion"] = time.perf_counter()
     d2h = A.data.nbytes + A.indices.nbytes + A.indptr.nbytes        # touching .data materialises the scipy CSR
     torch.cuda.synchronize()
+    if tr:
+        trace["D2H + scipy csr"] = time.perf_counter()
     return A, d2h
 
 
@@ -363,13 +372,22 @@ def run_own(args):
             Ah, d2h = e2e_step(cfg, g, host, names)
         torch.cuda.synchronize()
         t0 = time.perf_counter()
-        ne = max(2, min(args.steps, 3))
+        ne = max(2, min(args.steps, 10))
+        each = []
         for _ in range(ne):
+            t_s = time.perf_counter()
             Ah, d2h = e2e_step(cfg, g, host, names)
+            each.append((time.perf_counter() - t_s) * 1e3)
         torch.cuda.synchronize()
         dt = (time.perf_counter() - t0) / ne
+        trace = {}
+        torch.cuda.synchronize(); t1 = time.perf_counter()
+        e2e_step(cfg, g, host, names, trace)           # one extra, untimed pass with a sync after every stage
+        stages_e2e, prev = {}, t1
+        for k_, v in trace.items():
+            stages_e2e[k_] = (v - prev) * 1e3; prev = v
         out["e2e"] = {"value": cfg["m"] / dt, "unit": "concatemers/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                      "ms_per_step": dt * 1e3, "api": "HyperExtractor.from_arrays -> HyperGraph.incidence_matrix -> "
+                      "ms_per_step": dt * 1e3, "ms_each": each, "stages_ms_synchronised": stages_e2e, "api": "HyperExtractor.from_arrays -> HyperGraph.incidence_matrix -> "
                                                       "HyperGraph.clique_expansion_init -> scipy csr (host)"}
         t = {k: v.to(dev) for k, v in host.items()} if not args.no_cpu_baseline else None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

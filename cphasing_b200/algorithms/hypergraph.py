@@ -76,10 +76,7 @@ class LazyTriplets:
 
     def _arr(self):
         if self._a is None:
-            t = self._p()
-            if t.dtype == torch.uint32:
-                t = t.view(torch.int32)
-            a = t.cpu().numpy()
+            a = D.to_host(self._p())
             self._a = a.view(self.dtype) if a.dtype != self.dtype else a
             self._p = None
         return self._a
@@ -156,16 +153,16 @@ def _idx_dtype(nnz):
 
 def wrap_incidence(H: D.DeviceH):
     def load():
-        ip = H.indptr.to(_idx_dtype(H.nnz)).cpu().numpy()
-        return H.counts_f32().cpu().numpy(), H.indices.cpu().numpy(), ip
+        ip = D.to_host(H.indptr.to(_idx_dtype(H.nnz)))
+        return D.to_host(H.counts_f32()), D.to_host(H.indices), ip
     return DeviceBackedCSR(loader=load, lazy_shape=(H.n_rows, H.n_cols), handle=H)
 
 
 def wrap_adjacency(A: D.DeviceCSR, dtype=np.float32):
     def load():
-        ip = A.indptr.to(_idx_dtype(A.nnz)).cpu().numpy()
+        ip = D.to_host(A.indptr.to(_idx_dtype(A.nnz)))
         d = A.data32 if (dtype == np.float32 and A.data32 is not None) else A.data64
-        return d.cpu().numpy().astype(dtype, copy=False), A.indices.cpu().numpy(), ip
+        return D.to_host(d).astype(dtype, copy=False), D.to_host(A.indices), ip
     return DeviceBackedCSR(loader=load, lazy_shape=(A.n, A.n), handle=A)
 
 

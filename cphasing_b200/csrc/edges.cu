@@ -12,6 +12,7 @@
 // order of the read; a scan compacts the survivors.  Bytes per record (sorted input): 9 read,
 // 8+8 key write/read x2, 10 flags -> HBM bound.
 #include "common.cuh"
+#include <vector>
 
 namespace {
 
@@ -747,6 +748,108 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
     h_counts[0] = h_total;
     h_counts[1] = h_total ? (u64)h_lastcol + 1 : 0;
     return CPH_OK;
+}
+
+// Host-table variant of the fast path: the three columns live in HOST memory (pinned for full PCIe rate) and are moved
+// to caller-owned device staging columns in chunks on a private copy stream; the tile kernel for the tiles a chunk
+// completes is launched as soon as that chunk has landed, so the group-by runs under the next chunk's transfer.
+// The ticket counter and the look-back state words carry over from launch to launch, which makes the sequence of
+// launches equivalent to one launch over the whole table.  A launch may only cover tiles whose window (tile + halo)
+// has arrived AND whose last read is known to end inside the arrived prefix (the slow path walks to the end of a
+// read that overflows the window); the host read column answers that in O(1) per chunk.
+// h_counts[2] = 1 when the table turned out not to be grouped by read: the staged device columns are complete, the
+// outputs are not, and the caller re-runs cph_porec_to_edges on them (general path).
+extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_contig_idx, const int8_t* h_mapq, u32* d_read_idx,
+                                       u32* d_contig_idx, int8_t* d_mapq, u64 n_records, u32 n_contigs, int min_mapq,
+                                       u32 min_order, u32 max_order, u32 read_offset, u64 chunk_records, u32* rem_row,
+                                       u32* rem_col, u32* rem_count, int8_t* rem_mapq, u64* h_counts, void* ws, size_t ws_bytes,
+                                       size_t* h_ws_need, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const u64 N = n_records;
+    ARG_CHECK(N < (1ull << 32) - 8192);
+    ARG_CHECK(n_contigs > 0 && n_contigs < (1u << 23));
+    WS_BEGIN(ar);
+    const u32 ntiles = (u32)ceil_div(N > 0 ? N : 1, (size_t)PT_TILE);
+    u32* scal = ar.take<u32>(4);
+    u64* tile_state = ar.take<u64>((size_t)ntiles);
+    WS_QUERY_RETURN(ar);
+    ARG_CHECK(h_counts);
+    h_counts[0] = h_counts[1] = h_counts[2] = 0;
+    if (N == 0) return CPH_OK;
+    ARG_CHECK(h_read_idx && h_contig_idx && h_mapq && d_read_idx && d_contig_idx && d_mapq);
+    ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq);
+    PorecIn in{d_read_idx, d_contig_idx, d_mapq, nullptr, nullptr, nullptr, N, n_contigs, min_mapq, (i64)0};
+    u64 chunk = chunk_records ? chunk_records : (u64)(8u << 20);
+    chunk = ceil_div(chunk, (size_t)PT_TILE) * PT_TILE;
+    const u32 nchunks = (u32)ceil_div(N, chunk);
+    cudaStream_t cs = nullptr;
+    cudaEvent_t ready = nullptr;
+    std::vector<cudaEvent_t> landed(nchunks, nullptr);
+    int rc = CPH_OK;
+    auto cleanup = [&]() {
+        for (cudaEvent_t e : landed)
+            if (e) cudaEventDestroy(e);
+        if (ready) cudaEventDestroy(ready);
+        if (cs) cudaStreamDestroy(cs);
+    };
+#define HT_TRY(expr)                                                    \
+    do {                                                                \
+        cudaError_t e__ = (expr);                                       \
+        if (e__ != cudaSuccess) {                                       \
+            cph_set_error(__FILE__, __LINE__, cudaGetErrorString(e__)); \
+            cleanup();                                                  \
+            return CPH_ERR_CUDA;                                        \
+        }                                                               \
+    } while (0)
+    HT_TRY(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    HT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+    HT_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
+    HT_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
+    HT_TRY(cudaFuncSetAttribute(porec_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmem)));
+    // the staging columns may be recycled blocks with work still queued on `st`: copies start after it
+    HT_TRY(cudaEventRecord(ready, st));
+    HT_TRY(cudaStreamWaitEvent(cs, ready, 0));
+    const int use_tma = (((uintptr_t)d_read_idx | (uintptr_t)d_contig_idx | (uintptr_t)d_mapq) & 15) == 0;
+    u32 t_done = 0;
+    for (u32 c = 0; c < nchunks; ++c) {
+        const u64 lo = (u64)c * chunk, hi = lo + chunk < N ? lo + chunk : N, len = hi - lo;
+        HT_TRY(cudaMemcpyAsync(d_read_idx + lo, h_read_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
+        HT_TRY(cudaMemcpyAsync(d_contig_idx + lo, h_contig_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
+        HT_TRY(cudaMemcpyAsync(d_mapq + lo, h_mapq + lo, len, cudaMemcpyHostToDevice, cs));
+        HT_TRY(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
+        HT_TRY(cudaEventRecord(landed[c], cs));
+        u32 t_hi;
+        if (hi == N) t_hi = ntiles;
+        else {
+            t_hi = hi >= (u64)PT_HALO ? (u32)((hi - PT_HALO) / PT_TILE) : 0u;
+            while (t_hi > t_done && h_read_idx[(u64)t_hi * PT_TILE - 1] == h_read_idx[hi - 1]) --t_hi;
+        }
+        if (t_hi > t_done) {
+            HT_TRY(cudaStreamWaitEvent(st, landed[c], 0));
+            porec_tile_kernel<<<t_hi - t_done, PT_THREADS, sizeof(PtSmem), st>>>(in, use_tma, min_order, max_order, read_offset,
+                                                                                (unsigned long long*)tile_state, scal, rem_row,
+                                                                                rem_col, rem_count, rem_mapq);
+            ++g_cph_launches;
+            HT_TRY(cudaGetLastError());
+            t_done = t_hi;
+        }
+    }
+    u32 hs[2] = {0, 0};
+    u64 last = 0;
+    HT_TRY(cudaMemcpyAsync(hs, scal, 2 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    HT_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
+    HT_TRY(cudaStreamSynchronize(st));
+    HT_TRY(cudaStreamSynchronize(cs));
+#undef HT_TRY
+    cleanup();
+    if (hs[1] != 0) {
+        h_counts[2] = 1;
+        return rc;
+    }
+    const u64 total = last & ((1ull << 62) - 1);
+    h_counts[0] = total;
+    h_counts[1] = total ? (u64)hs[0] + read_offset + 1 : 0;
+    return rc;
 }
 
 extern "C" int cph_edges_to_triplets(const u32* rem_row, const u32* rem_col, const u32* rem_count, const int8_t* rem_mapq, u64 nnz,

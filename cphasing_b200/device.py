@@ -36,6 +36,25 @@ def to_dev(x, dtype, device):
     return torch.from_numpy(a).to(device, non_blocking=True)
 
 
+PINNED_D2H_MAX_BYTES = 4 << 30
+
+
+def to_host(t: torch.Tensor) -> np.ndarray:
+    """device tensor -> numpy array.  The bytes land in page-locked memory from torch's caching host allocator (full
+    PCIe rate, and no first-touch page faults on a fresh malloc for every result); the array keeps the block alive."""
+    if t.dtype == torch.uint32:
+        t = t.view(torch.int32)
+    if not t.is_cuda:
+        return t.numpy()
+    nb = t.numel() * t.element_size()
+    if nb == 0 or nb > PINNED_D2H_MAX_BYTES:
+        return t.cpu().numpy()
+    h = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+    h.copy_(t.contiguous(), non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return h.numpy()
+
+
 @dataclass
 class RawEdges:
     """RAW EDGE-MAJOR triplets (include/cph.h): the CSC view of H, hyperedge runs marked by a head bit."""
@@ -120,6 +139,13 @@ class DeviceCSR:
 def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, contig_len=None, min_mapq=1,
                    min_order=2, max_order=50, edge_length=0, read_offset=0, device=None) -> RawEdges:
     dev = _dev(device)
+    if not edge_length:
+        host = _host_columns(read_idx, contig_idx, mapq)
+        if host is not None and host[0].numel() >= STREAM_MIN_RECORDS:
+            raw, staged = _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_offset, dev)
+            if raw is not None:
+                return raw
+            read_idx, contig_idx, mapq = staged      # table not grouped by read: the columns are already on the device
     r = to_dev(read_idx, torch.uint32, dev)
     c = to_dev(contig_idx, torch.uint32, dev)
     q = to_dev(mapq, torch.int8, dev)
@@ -139,6 +165,52 @@ def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, 
             int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0,
             ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
     return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+
+
+STREAM_MIN_RECORDS = 1 << 22      # below this the chunked host path has nothing to overlap
+STREAM_CHUNK_RECORDS = 8 << 20
+
+
+def _host_columns(read_idx, contig_idx, mapq):
+    """(read u32, contig u32, mapq i8) as contiguous CPU tensors when all three are host arrays, else None."""
+    want = (torch.uint32, torch.uint32, torch.int8)
+    npw = (np.uint32, np.uint32, np.int8)
+    out = []
+    for x, td, nd in zip((read_idx, contig_idx, mapq), want, npw):
+        if isinstance(x, torch.Tensor):
+            if x.is_cuda:
+                return None
+            if x.dtype != td:
+                same_width = x.element_size() == (1 if td == torch.int8 else 4)
+                x = x.view(td) if same_width and not x.dtype.is_floating_point else x.to(td)
+            out.append(x.contiguous())
+        else:
+            a = np.ascontiguousarray(x)
+            if a.dtype != nd:
+                a = a.astype(nd)
+            out.append(torch.from_numpy(a))
+    return out
+
+
+def _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_offset, dev):
+    """chunked H2D copy overlapped with the group-by kernel (cph_porec_to_edges_host) -> (RawEdges, None), or
+    (None, staged device columns) when the table is not grouped by read."""
+    hr, hc, hq = host
+    N = hr.numel()
+    r = torch.empty(N, dtype=torch.uint32, device=dev)
+    c = torch.empty(N, dtype=torch.uint32, device=dev)
+    q = torch.empty(N, dtype=torch.int8, device=dev)
+    o_row = torch.empty(N, dtype=torch.uint32, device=dev)
+    o_col = torch.empty(N, dtype=torch.uint32, device=dev)
+    o_cnt = torch.empty(N, dtype=torch.uint32, device=dev)
+    o_mq = torch.empty(N, dtype=torch.int8, device=dev)
+    h = (C.c_uint64 * 3)()
+    call_ws("cph_porec_to_edges_host", dev, ptr(hr), ptr(hc), ptr(hq), ptr(r), ptr(c), ptr(q), N, int(n_contigs),
+            int(min_mapq), int(min_order), int(max_order), int(read_offset), int(STREAM_CHUNK_RECORDS),
+            ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    if int(h[2]):
+        return None, (r, c, q)
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed(), None
 
 
 def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig_len=None, min_mapq=1,

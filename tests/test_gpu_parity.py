@@ -357,3 +357,46 @@ def test_porec_edges_unaligned_device_columns(api):
         got = (row.cpu().numpy(), col.cpu().numpy(), cnt.view(torch.int32).cpu().numpy().view(np.uint32), mq.cpu().numpy())
         for a, b in zip(got, exp):
             assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("chunk", [3584, 3 * 3584, 1 << 20])
+@pytest.mark.parametrize("pinned", [False, True])
+def test_porec_host_streamed_chunks(api, chunk, pinned, monkeypatch):
+    """cph_porec_to_edges_host: host columns copied in chunks with the tile kernel launched per landed chunk must give
+    exactly what the one-launch device path and the oracle give -- long reads crossing chunk borders included."""
+    _, _, D, _ = api
+    import torch
+    rng = np.random.default_rng(chunk % 97 + pinned)
+    n = 200
+    lens = []
+    while sum(lens) < 50000:
+        u = rng.random()
+        lens.append(int(rng.integers(3000, 9000)) if u < 0.002 else int(rng.integers(400, 900)) if u < 0.01
+                    else int(rng.integers(1, 12)))
+    lens = np.array(lens)
+    read = np.repeat(np.arange(len(lens), dtype=np.uint32) * 2 + 1, lens)
+    ncont = np.where(lens > 60, rng.integers(2, 45, size=len(lens)), 1000)
+    contig = np.concatenate([rng.integers(0, min(n, k), size=l) for l, k in zip(lens, ncont)]).astype(np.uint32)
+    mapq = rng.choice(np.array([0, 3, 20, 60], dtype=np.int8), size=contig.size)
+    monkeypatch.setattr(D, "STREAM_MIN_RECORDS", 1)
+    monkeypatch.setattr(D, "STREAM_CHUNK_RECORDS", chunk)
+    cols = (read, contig, mapq)
+    if pinned:
+        cols = tuple(torch.from_numpy(x.view(np.int32) if x.dtype == np.uint32 else x).pin_memory() for x in cols)
+    exp = orc.porec_edges(read, contig, mapq, min_mapq=1, min_order=2, max_order=50, n_contigs=n)
+    from cphasing_b200 import _lib
+    l0 = _lib.launches()
+    raw = D.porec_to_edges(*cols, n, min_mapq=1, min_order=2, max_order=50, read_offset=3)
+    nl = _lib.launches() - l0
+    if chunk < 50000:
+        assert nl >= 2, "expected one kernel launch per landed chunk"
+    row, col, cnt, mq = D.edges_to_triplets(raw)
+    got = (row.cpu().numpy(), col.cpu().numpy() - 3, cnt.view(torch.int32).cpu().numpy().view(np.uint32), mq.cpu().numpy())
+    for a, b in zip(got, exp):
+        assert np.array_equal(a, b)
+    # a table that is NOT grouped by read falls through to the general (sorting) path on the staged columns
+    p = rng.permutation(read.size)
+    raw2 = D.porec_to_edges(read[p], contig[p], mapq[p], n, min_mapq=1, min_order=2, max_order=50, read_offset=3)
+    row2, col2, cnt2, mq2 = D.edges_to_triplets(raw2)
+    assert np.array_equal(row2.cpu().numpy(), exp[0]) and np.array_equal(col2.cpu().numpy() - 3, exp[1])
+    assert np.array_equal(cnt2.view(torch.int32).cpu().numpy().view(np.uint32), exp[2])
