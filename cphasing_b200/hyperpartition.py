@@ -1,12 +1,13 @@
 """Drop-in for the device-relevant core of ``cphasing.hyperpartition.HyperPartition``
 (reference: cphasing/hyperpartition.py).
 
-Covered: construction (filter -> H -> normalisation weights ->
-prune pairs), ``single_partition`` with the resolution auto-search, ``filter_cluster``, ``_merge``,
+Covered: construction (filter -> H -> normalisation weights -> prune pairs),
+``single_partition`` with the resolution auto-search, the two-round ``incremental_partition`` /
+``_incremental_partition`` (in-process instead of the loky fan-out), ``filter_cluster``, ``_merge``,
 ``recluster_by_linkage``, in-process kprune on A, ``to_cluster``.  All matrix arithmetic runs in libcph; this module
-is the reference's control flow over n- and g-sized host objects.  Not covered here: the second round
-(``incremental_partition``), contig splitting, ``alleles()`` (sequence similarity), ultra-complex re-partitioning,
-``raw_sort``: they either sit outside the path or are the next rows of SURVEY.md 8f.
+is the reference's control flow over n- and g-sized host objects.  Not covered: contig splitting, ``alleles()``
+(sequence k-mer similarity), ultra-complex re-partitioning, ``raw_sort`` and the optional post-passes
+(--remove-misassembly, --recluster-contigs, --refine): they sit outside the path and raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -17,14 +18,17 @@ from pathlib import Path
 import numpy as np
 import pandas as pd
 import torch
+from scipy.sparse import csr_matrix
 
 from . import device as D
 from . import graphops
 from ._lib import call_ws, ptr
 from .algorithms.hypergraph import HyperGraph, IRMM, extract_incidence_matrix2
-from .kprune import KPruneHyperGraph
+from .kprune import KPruneHyperGraph, allele_frame as _allele_frame
 
 logger = logging.getLogger(__name__)
+
+MAX_RESOLUTION = 10.0          # hyperpartition.py:80
 
 
 def group_sums(A, K, want_S=False, want_V=False):
@@ -76,6 +80,9 @@ class HyperPartition:
         self.min_allelic_overlap = min_allelic_overlap
         self.disable_merge_in_first = disable_merge_in_first
         self.merge_use_allele = merge_use_allele
+        self.exclude_group_to_second = exclude_group_to_second
+        self.exclude_group_from_first = exclude_group_from_first
+        self.allelic_positive_factor = allelic_positive_factor
         self.whitelist = whitelist
         self.blacklist = blacklist
         self.min_contacts = min_contacts
@@ -314,6 +321,325 @@ class HyperPartition:
             self.K = sorted(self.K, key=lambda x: sum(sizes[i] for i in x), reverse=True)
         logger.info(f"Hyperpartition result {len(self.K)} groups:")
         return self.K
+
+    # -- hyperpartition.py:1726-2286.  Two-round partition for autopolyploids: round 1 splits the contigs into k[0]
+    #    chromosome-level groups on the un-pruned graph; round 2 re-partitions every round-1 group into k[1] haplotype
+    #    groups on its own sub-hypergraph (`_incremental_partition`).  The reference fans round 2 out over loky worker
+    #    processes (:2181-2187); CUDA contexts do not survive fork, so the groups run in-process, one after the other, on
+    #    the same device-resident H.
+    def incremental_partition(self, k, first_cluster=None):
+        if self.split or self.fasta is not None:
+            raise NotImplementedError("split contigs / on-the-fly `alleles` (sequence k-mer similarity) are outside the "
+                                      "accelerated path; pass an allele table or a prune table")
+        k = list(k)
+        self.P_allelic_idx, self.P_weak_idx = None, None                                   # :1736
+        A = HyperGraph.clique_expansion_init(self.H, min_weight=self.min_weight)
+        retain_idx1 = np.asarray(HyperGraph.filter_adjacency_matrix(A, self.vertices, self.vertices_idx_sizes,
+                                                                    invert=True)).astype(np.int64)
+        dia = A.diagonal()
+        raw_contig_counts = A.shape[0]
+        retain_idx = np.intersect1d(np.where(dia >= self.min_cis_weight)[0], retain_idx1)
+        if len(retain_idx) < raw_contig_counts:                                            # :1763-1784
+            self.H, _, _ = extract_incidence_matrix2(self.H, retain_idx)
+            A = csr_matrix(A)[retain_idx, :][:, retain_idx]
+            if self.NW is not None:
+                self.NW = self.NW[retain_idx]
+            self.vertices = self.vertices[retain_idx]
+            logger.info(f"Removed {raw_contig_counts - len(retain_idx):,} contigs that self edge weight < "
+                        f"{self.min_cis_weight} (--min-cis-weight).")
+        vertices_idx_sizes = pd.DataFrame(self.vertices_idx_sizes, index=['length']).T
+        A = HyperGraph.normalize_adjacency_matrix(A, self.NW) if self.NW is not None else A
+        allelic_idx_set = None
+        if self.merge_use_allele:                                                          # :1794-1896 (no fasta branch)
+            if self.prune_pair_df is not None:
+                df = self.prune_pair_df
+                allelic_idx_set = set(map(tuple, df[(df['type'] == 0) & (df['similarity'] >= 0.90)]
+                                          [['contig1', 'contig2']].values))
+            elif self.alleletable is not None:
+                at_df = _allele_frame(self.alleletable)
+                at_df = at_df[(at_df['similarity'] >= 0.90) & (at_df['mzShared'] >= 100)]
+                vi = self.vertices_idx
+                c1, c2 = at_df[1].map(vi.get), at_df[2].map(vi.get)
+                ok = c1.notna() & c2.notna()
+                allelic_idx_set = set(zip(c1[ok].astype(int), c2[ok].astype(int)))
+            else:
+                allelic_idx_set = set()
+        raw_A = A
+        if allelic_idx_set and self.merge_use_allele and self.allelic_positive_factor != 1.0:   # :1903-1907
+            Pa = (list(zip(*allelic_idx_set))[0], list(zip(*allelic_idx_set))[1])
+            A = HyperGraph.reweight_adjacency_matrix(A, Pa, allelic_factor=self.allelic_positive_factor)
+        self.resolutions_tried = []
+
+        def first_irmm(res):
+            _, _A2, _, K2 = IRMM(self.H, A, self.NW, None, None, self.allelic_factor, self.cross_allelic_factor, res,
+                                 self.min_weight, self.threshold, 1, threads=self.threads, method=self.cluster_method)
+            return _A2, list(map(list, K2))
+        if not first_cluster:
+            if k[0] == 1:
+                self.K = [list(range(A.shape[0]))]
+                _A = A
+            elif self.resolution1 < 0:                                                     # :1915-1987
+                tmp_resolution = self.init_resolution1
+                _A, self.K = first_irmm(tmp_resolution)
+                self.K = self.filter_cluster(verbose=0)
+                result_K_length = len(self.K)
+                self.resolutions_tried.append((tmp_resolution, result_K_length))
+                auto_round = 2
+                if result_K_length > k[0] and not self.merge_use_allele and not self.disable_merge_in_first:
+                    tmp_resolution = self.init_resolution1 - 0.1
+                    auto_round = 1
+                    while result_K_length > k[0]:
+                        if tmp_resolution < 0.01 or auto_round > 50:
+                            break
+                        _A, new_K = first_irmm(tmp_resolution)
+                        old_K, self.K = self.K, new_K
+                        self.K = self.filter_cluster(verbose=0)
+                        self.resolutions_tried.append((tmp_resolution, len(self.K)))
+                        if len(self.K) < k[0]:
+                            self.K = old_K
+                            break
+                        result_K_length = len(self.K)
+                        tmp_resolution -= 0.1
+                        if tmp_resolution < 0.1:
+                            tmp_resolution -= 0.02
+                        auto_round += 1
+                elif result_K_length < k[0]:
+                    while result_K_length < k[0] and k[0] != 0:
+                        if tmp_resolution > MAX_RESOLUTION or auto_round > 50:
+                            break
+                        # NB the reference feeds IRMM's zero-diagonal output back in as A here (:1972); clustering
+                        # ignores the diagonal, so passing the original A gives the same groups
+                        _A, self.K = first_irmm(tmp_resolution)
+                        self.K = self.filter_cluster(verbose=0)
+                        assert len(self.K) > 0, "Couldn't run first cluster."
+                        result_K_length = len(self.K)
+                        self.resolutions_tried.append((tmp_resolution, result_K_length))
+                        tmp_resolution += 0.2
+                        auto_round += 1
+            else:
+                _A, self.K = first_irmm(self.resolution1)
+            A1 = _A
+            self.K = self.filter_cluster()
+            if k[0] and len(self.K) > k[0]:                                                # :1972-1998
+                if self.disable_merge_in_first:
+                    self.K = sorted(self.K, key=lambda x: vertices_idx_sizes.loc[x]["length"].sum(), reverse=True)[:k[0]]
+                elif allelic_idx_set is not None and self.merge_use_allele:
+                    self.K = HyperPartition._merge(A1, self.K, vertices_idx_sizes, k[0], allelic_idx_set=allelic_idx_set,
+                                                   min_allelic_overlap=0.8, allele_use_method='merge', method='sum')
+                else:
+                    self.K = HyperPartition._merge(A1, self.K, vertices_idx_sizes, k[0],
+                                                   min_allelic_overlap=self.min_allelic_overlap, method='sum')
+            self.K = sorted(self.K, key=lambda x: vertices_idx_sizes.loc[x]['length'].sum(), reverse=True)
+            reclustered_count = 1 if self.is_recluster_by_linkage else 0
+            iter_count = 0
+            while reclustered_count > 0 and iter_count < 5:
+                iter_count += 1
+                reclustered_count = self.recluster_by_linkage(A=raw_A, min_ratio=1.5, iter_count=iter_count)
+            if self.exclude_group_from_first:
+                for i in self.exclude_group_from_first:
+                    if 0 < i <= len(self.K):
+                        self.K[i - 1] = []
+                self.K = [g for g in self.K if len(g) > 0]
+            assert len(self.K) > 0, "Couldn't run first cluster."
+            self.first_K = [list(g) for g in self.K]
+            mapq_filter = True
+        else:                                                                              # :2054-2063
+            vi = self.vertices_idx
+            groups = first_cluster.data.values() if hasattr(first_cluster, "data") else first_cluster
+            self.K = [[vi[x] for x in grp if x in vi] for grp in groups]
+            self.first_K = [list(g) for g in self.K]
+            mapq_filter = False
+        logger.info("Starting second round hyperpartition ...")
+        if len(np.asarray(self.edges.mapq).shape) and self.edges.mapq.size and (self.min_quality2 > self.min_quality1) \
+                and mapq_filter:                                                           # :2075-2106
+            itv = self.idx_to_vertices
+            tmp_K = [[itv[x] for x in grp] for grp in self.K]
+            self.HG = HyperGraph(self.edges, min_quality=self.min_quality2)
+            self.filter_hypergraph()
+            self.H, self.vertices = self.get_hypergraph()
+            raw_A = HyperGraph.clique_expansion_init(self.H, min_weight=self.min_weight, use_high_order=False)
+            self.NW = self.get_normalize_weight() if self.normalize else None
+            vertices_idx_sizes = pd.DataFrame(self.vertices_idx_sizes, index=['length']).T
+            vi = self.vertices_idx
+            removed = set(self.HG.remove_contigs)
+            self.K = [[vi[y] for y in grp if y not in removed and y in vi] for grp in tmp_K]
+        if self.prunetable is not None:                                                    # :2108-2119
+            self.P_allelic_idx, self.P_weak_idx, self.prune_pair_df = self.get_prune_pairs()
+            prune_pair_df = self.prune_pair_df.reset_index().set_index(['contig1', 'contig2'])
+        else:
+            prune_pair_df = None
+        itv = self.idx_to_vertices
+        results, assignments = [], []
+        self.exclude_groups = []
+        for num, sub_k in enumerate(self.K, 1):                                            # :2150-2190, in-process
+            sub_group_number = int(k[1][num - 1]) if isinstance(k[1], dict) else int(k[1])
+            if self.exclude_group_to_second and num in self.exclude_group_to_second:
+                self.exclude_groups.append(sub_k)
+                continue
+            _, ca, new_K = HyperPartition._incremental_partition(
+                sub_k, itv, sub_group_number, self.alleletable if self.prunetable is None else None, prune_pair_df, self.H,
+                vertices_idx_sizes, self.NW, None, self.resolution2, init_resolution=self.init_resolution2,
+                min_weight=self.min_weight, min_cis_weight=self.min_cis_weight,
+                allelic_similarity=self.allelic_similarity, min_allelic_overlap=self.min_allelic_overlap,
+                allelic_factor=self.allelic_factor, cross_allelic_factor=self.cross_allelic_factor,
+                min_scaffold_length=self.min_scaffold_length, threshold=self.threshold, max_round=self.max_round, num=num,
+                threads=self.threads, cluster_method=self.cluster_method)
+            if new_K is not None:
+                results.append(new_K)
+                assignments.append(ca)
+        self.cluster_assignments = assignments
+        self.inc_chr_idx = [i for i, res in enumerate(results) for _ in res]
+        self.second_group_info = [f"{i}g{j}" for i, res in enumerate(results, 1) for j, _ in enumerate(res, 1)]
+        self.K = [list(g) for res in results for g in res]
+        self.K = self.filter_cluster()
+        if self.exclude_group_to_second:
+            self.K.extend(self.exclude_groups)
+        reclustered_count = 1 if self.is_recluster_by_linkage else 0
+        iter_count = 0
+        while reclustered_count > 0 and iter_count < 5:                                    # :2236-2242
+            iter_count += 1
+            _A2 = HyperGraph.reweight_adjacency_matrix(raw_A, P_allelic_idx=self.P_allelic_idx,
+                                                       P_weak_idx=self.P_weak_idx, allelic_factor=0)
+            reclustered_count = self.recluster_by_linkage(A=_A2, min_ratio=1.5, iter_count=iter_count)
+        logger.info(f"Second hyperpartition resulted in {len(self.K)} groups.")
+        return self.K
+
+    # -- hyperpartition.py:1239-1560: one round-1 group -> k haplotype groups.  Same positional arguments as the reference
+    #    (its loky workers receive them as a tuple, :2166-2181).  Differences: the per-group kprune runs in-process on the
+    #    unweighted sub-A (`KPruneHyperGraph`, kprune.py:385-552) instead of writing a contacts file and shelling out to
+    #    `cphasing-rs kprune` (:1331-1345; that binary is not in the reference tree); `cis_counts` is never passed by a
+    #    live caller (hyperpartition.py:350) and is ignored.
+    @staticmethod
+    def _incremental_partition(K, idx_to_vertices, k, alleletable, prune_pair_df, H, vertices_idx_sizes, NW, cis_counts,
+                               resolution, output_dir="./", init_resolution=0.8, min_weight=1, min_cis_weight=1.0,
+                               allelic_similarity=0.8, min_allelic_overlap=0.1, allelic_factor=-1,
+                               cross_allelic_factor=0.0, is_remove_misassembly=False, is_recluster_contigs=False,
+                               refine=False, collapsed_contigs_df=None, min_scaffold_length=10000, threshold=0.01,
+                               max_round=1, num=None, kprune_norm_method='cis', count_re=None, threads=1,
+                               cluster_method="louvain"):
+        if is_remove_misassembly or is_recluster_contigs or refine:
+            raise NotImplementedError("--remove-misassembly / --recluster-contigs / --refine post-passes are not implemented")
+        if k == 1:
+            return None, None, [K]
+        merge_method = "sum" if NW is not None else "mean"
+        K = np.array(list(K))
+        if len(K) == 1:
+            return None, None, [K]
+        from .algorithms.hypergraph import device_handle, upload_incidence, wrap_incidence
+        hH = device_handle(H)
+        if not isinstance(hH, D.DeviceH):
+            hH = upload_incidence(H)
+        sub = D.sub_incidence(hH, K)                                                       # extract_incidence_matrix2 (:1270)
+        # dia = sum_e count^2 per contig (:1276); contigs whose self weight is below --min-cis-weight leave the group
+        rowsq = torch.empty(max(sub.n_rows, 1), dtype=torch.int64, device=sub.device)
+        from ._lib import check, lib, stream
+        check(lib().cph_row_sq_sums(ptr(sub.indptr), ptr(sub.pk), max(sub.n_rows, 1), ptr(rowsq), stream()))
+        dia = rowsq[:sub.n_rows].cpu().numpy().astype(np.float64)
+        retain_mask = dia >= min_cis_weight
+        raw_contig_counts = len(K)
+        K = K[retain_mask]
+        if len(K) == 0:
+            return None, None, None
+        if raw_contig_counts > len(K):                                                     # :1284-1291: rows out, then only
+            sub = D.sub_incidence(sub, np.where(retain_mask)[0], col_min=1)                # the EMPTY columns go
+        sub_H = wrap_incidence(sub)
+        sub_NW = NW[K] if NW is not None else None
+        sub_old2new_idx = dict(zip(K.tolist(), range(len(K))))
+        sizes = vertices_idx_sizes['length'] if hasattr(vertices_idx_sizes, 'columns') else pd.Series(vertices_idx_sizes)
+        sub_sizes = sizes.reindex(K)
+        sub_sizes.index = range(len(K))
+        sub_size_db = sub_sizes.to_dict()
+        sub_vertices_new_idx_sizes = pd.DataFrame({'length': sub_sizes})
+        sub_vertices = np.array([idx_to_vertices[i] for i in K])
+        sub_vertices_idx = dict(zip(sub_vertices, range(len(sub_vertices))))
+        if alleletable is not None:                                                        # :1318-1345
+            at_df = _allele_frame(alleletable)
+            at_df = at_df[at_df[1].isin(sub_vertices_idx) & at_df[2].isin(sub_vertices_idx)]
+
+            class _AT:
+                data = at_df
+            _sub_A = HyperGraph.clique_expansion_init(sub_H, min_weight=min_weight, use_high_order=False)
+            kph = KPruneHyperGraph(_AT, _sub_A, sub_vertices_idx)
+            kph.run()
+            table = kph.get_prune_table()
+            sub_prune_pair_df = table.assign(contig1=table['contig1'].map(sub_vertices_idx.get),
+                                             contig2=table['contig2'].map(sub_vertices_idx.get))
+            sym = sub_prune_pair_df.rename(columns={'contig1': 'contig2', 'contig2': 'contig1', 'mz1': 'mz2', 'mz2': 'mz1'})
+            sub_prune_pair_df = pd.concat([sub_prune_pair_df, sym[sub_prune_pair_df.columns]], axis=0)
+            sub_prune_pair_df = sub_prune_pair_df.drop_duplicates(subset=['contig1', 'contig2']).reset_index(drop=True)
+        elif prune_pair_df is not None:                                                    # :1347-1365
+            K_set = set(K.tolist())
+            sub_prune_pair_df = prune_pair_df[prune_pair_df.index.get_level_values(0).isin(K_set) &
+                                              prune_pair_df.index.get_level_values(1).isin(K_set)].reset_index()
+            sub_prune_pair_df['contig1'] = sub_prune_pair_df['contig1'].map(sub_old2new_idx.get)
+            sub_prune_pair_df['contig2'] = sub_prune_pair_df['contig2'].map(sub_old2new_idx.get)
+        else:
+            sub_prune_pair_df = None
+        if sub_prune_pair_df is not None:
+            t0 = sub_prune_pair_df[sub_prune_pair_df['type'] == 0]
+            t1 = sub_prune_pair_df[sub_prune_pair_df['type'] == 1]
+            sub_P_allelic_idx = [t0['contig1'], t0['contig2']]
+            sub_P_weak_idx = [t1['contig1'], t1['contig2']]
+        else:
+            sub_P_allelic_idx = sub_P_weak_idx = None
+        sub_A = HyperGraph.clique_expansion_init(sub_H, min_weight=min_weight)             # :1372-1378
+        if sub_NW is not None:
+            sub_A = HyperGraph.normalize_adjacency_matrix(sub_A, sub_NW)
+
+        def run(res):
+            raw_A, A, ca, new_K = IRMM(sub_H, sub_A, sub_NW, sub_P_allelic_idx, sub_P_weak_idx, allelic_factor,
+                                       cross_allelic_factor, res, min_weight, threshold, max_round, threads=1,
+                                       method=cluster_method)
+            new_K = [list(x) for x in new_K if sum(sub_size_db.get(i, 0) for i in x) >= min_scaffold_length]
+            return raw_A, A, ca, new_K
+        if resolution < 0.0 and k != 0:                                                    # :1396-1480
+            tmp_resolution = init_resolution
+            raw_A, A, cluster_assignments, new_K = run(tmp_resolution)
+            result_K_length = len(new_K)
+            auto_round = 2
+            if result_K_length < k:
+                tmp_resolution += 0.2
+                while result_K_length < k:
+                    if tmp_resolution > MAX_RESOLUTION or auto_round > 50:
+                        break
+                    raw_A, A, cluster_assignments, new_K = run(tmp_resolution)
+                    tmp_resolution += 0.2
+                    result_K_length = len(new_K)
+                    auto_round += 1
+            elif result_K_length > k:
+                tmp_resolution = init_resolution - 0.1
+                auto_round = 1
+                while result_K_length > k:
+                    if tmp_resolution < 0.01 or auto_round > 50:
+                        break
+                    old_K = new_K
+                    raw_A, A, cluster_assignments, new_K = run(tmp_resolution)
+                    if len(new_K) < k:
+                        new_K = old_K
+                        break
+                    tmp_resolution -= 0.1
+                    if tmp_resolution < 0.1:
+                        tmp_resolution -= 0.02
+                    result_K_length = len(new_K)
+                    auto_round += 1
+        else:
+            raw_A, A, cluster_assignments, new_K = run(resolution)
+        if k and len(new_K) > k:                                                           # :1515-1535
+            new_K = sorted(new_K, key=lambda x: sum(sub_size_db.get(i, 0) for i in x))
+            if sub_prune_pair_df is not None:
+                df = sub_prune_pair_df
+                allelic_idx_set = set(map(tuple, df[(df['type'] == 0) & (df['similarity'] >= allelic_similarity)]
+                                          [['contig1', 'contig2']].values))
+            else:
+                allelic_idx_set = set()
+            new_K = HyperPartition._merge(A, new_K, sub_vertices_new_idx_sizes, k, allelic_idx_set=allelic_idx_set,
+                                          min_allelic_overlap=min_allelic_overlap, allele_use_method='conflict',
+                                          method=merge_method)
+        new2old = K.tolist()
+        new_K = [[new2old[y] for y in x] for x in new_K]                                   # :1554-1557
+        new_K = sorted(new_K, key=lambda x: sizes.reindex(x).dropna().sum(), reverse=True)
+        logger.info(f"Subgroup {num} result {len(new_K)} groups.")
+        return A, cluster_assignments, new_K
 
     # -- hyperpartition.py:2288-2471: greedy merge of groups down to k.  V = M^T A M comes from the device ONCE
     #    (cph_group_sums); merging two groups adds their rows and columns, which is what recomputing M^T A M gives.

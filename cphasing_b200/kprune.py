@@ -6,6 +6,8 @@ from __future__ import annotations
 
 import logging
 
+from pathlib import Path
+
 import numpy as np
 import pandas as pd
 import torch
@@ -70,6 +72,27 @@ def kprune_pairs(A, allele_pairs, max_alleles=1):
     return pick(al), pick(wk)
 
 
+def allele_frame(alleletable):
+    """allele2 table (core.py:289-300) -> DataFrame with contig names in columns 1, 2 and named mz / similarity columns.
+    Accepts the reference's AlleleTable (`.data`), a DataFrame, a path, or a sequence of (name1, name2)."""
+    if hasattr(alleletable, "data"):
+        df = alleletable.data.copy()
+    elif isinstance(alleletable, pd.DataFrame):
+        df = alleletable.copy()
+    elif isinstance(alleletable, (str, Path)):
+        df = pd.read_csv(alleletable, sep='\t', header=None, comment="#", index_col=0,
+                         names=[-1, 0, 1, 2, 'mz1', 'mz2', 'mzShared', 'similarity', 'strand'])
+    else:
+        df = pd.DataFrame([(0, a, b, 0, 0, 0, 1.0, 1) for a, b in alleletable],
+                          columns=[0, 1, 2, 'mz1', 'mz2', 'mzShared', 'similarity', 'strand'])
+    ren = {3: 'mz1', 4: 'mz2', 5: 'mzShared', 6: 'similarity', 7: 'strand'}
+    df = df.rename(columns={c: ren[c] for c in df.columns if c in ren})
+    for c, d in (('mzShared', 0), ('similarity', 1.0)):
+        if c not in df.columns:
+            df[c] = d
+    return df
+
+
 class KPruneHyperGraph:
     """kprune.py:385-552.  `alleletable` is an object with a ``.data`` DataFrame whose columns 1 and 2 hold the
     contig names of each allele pair (the reference's AlleleTable), or a plain sequence of (name1, name2)."""
@@ -77,8 +100,7 @@ class KPruneHyperGraph:
 
     def __init__(self, alleletable, A, contig2idx, max_alleles=1):
         self.alleletable = alleletable
-        df = alleletable.data.copy() if hasattr(alleletable, "data") else pd.DataFrame(
-            [(0, 0, a, b) for a, b in alleletable], columns=[-1, 0, 1, 2])
+        df = allele_frame(alleletable)
         df[1] = df[1].map(contig2idx.get)
         df[2] = df[2].map(contig2idx.get)
         df = df.dropna(subset=[1, 2])
@@ -105,7 +127,8 @@ class KPruneHyperGraph:
         cols = list(self.alleletable_idx.columns)
         for row in self.alleletable_idx.itertuples(index=False):
             d = dict(zip(cols, row))
-            meta.setdefault((d[1], d[2]), tuple(d.get(k, 0) for k in (3, 4, 5, 6)))
+            meta.setdefault((d[1], d[2]), tuple(d.get(k, d.get(nm, 0)) for k, nm in
+                                                ((3, 'mz1'), (4, 'mz2'), (5, 'mzShared'), (6, 'similarity'))))
         rows = []
         for a, b in self.allelic_prune_list:
             mz1, mz2, sh, sim = meta.get((a, b), (0, 0, 0, 0))

@@ -265,3 +265,58 @@ def test_single_partition_end_to_end(case, tmp_path, normalize):
         mo[grp] = i
     both = (mo >= 0) & (mem >= 0)
     assert co.ari(mem[both], mo[both]) >= 0.99
+
+
+@pytest.mark.parametrize("use", ["alleletable", "prunetable", "none"])
+def test_incremental_partition_two_rounds(case, use):
+    """hyperpartition.py:1726-2286 + 1239-1560: round 1 -> 5 chromosome groups (auto-search down from the initial
+    resolution, merge), round 2 -> 4 haplotype groups inside each (sub-H, cis filter, per-group kprune, IRMM with the
+    resolution search, length filter, merge).  The result must be the planted 5 x 4 structure."""
+    import pandas as pd
+    from cphasing_b200 import hyperpartition as hp, synth, kprune
+    from cphasing_b200 import hypergraph as hg
+    g = case["g"]
+    t = synth.porec_table(g, 120_000, seed=20240)
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes,
+                                       min_quality=1, edge_length=0)
+    allg = sorted(g.contig_idx, key=g.contig_idx.get)
+    rows = [(0, 0, allg[a], allg[b], m1, m2, sh, sim, 1) for a, b, m1, m2, sh, sim in case["alleles"]]
+    at = pd.DataFrame(rows, columns=[-1, 0, 1, 2, 3, 4, 5, 6, 7]).set_index(-1)
+    kw = dict(min_contacts=25, min_weight=2.0, min_cis_weight=20, resolution1=-1, resolution2=-1, init_resolution1=0.8,
+              init_resolution2=0.8, min_scaffold_length=2_000_000, allelic_factor=0, min_length=10000)
+    if use == "alleletable":
+        P = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], alleletable=at, **kw)
+    elif use == "prunetable":
+        P0 = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], alleletable=at, **kw)
+        table = P0.kprune(at)
+        assert (table["type"] == 0).sum() > 50
+        P = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], prunetable=table, **kw)
+    else:
+        P = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], **kw)
+    K = P.incremental_partition([5, 4])
+    names = list(P.vertices)
+    old = {nm: i for i, nm in enumerate(allg)}
+    truth = np.array([g.group[old[nm]] for nm in names])
+    # round 1: chromosomes
+    assert len(P.first_K) == 5
+    m1 = np.full(len(names), -1)
+    for i, grp in enumerate(P.first_K):
+        m1[grp] = i
+    in1 = m1 >= 0
+    assert in1.mean() > 0.95 and co.ari(m1[in1], truth[in1] // g.ploidy) >= 0.99
+    # round 2: haplotypes
+    assert len(K) == 20
+    assert P.second_group_info[:5] == ["1g1", "1g2", "1g3", "1g4", "2g1"]
+    mem = np.full(len(names), -1)
+    for i, grp in enumerate(K):
+        assert mem[grp].max() == -1, "a contig landed in two groups"
+        mem[grp] = i
+    inside = mem >= 0
+    assert inside.mean() > 0.95
+    assert co.ari(mem[inside], truth[inside]) >= 0.99
+    # a supplied first cluster (hyperpartition.py:2054-2063) gives the same second round
+    first = [[names[i] for i in grp] for grp in P.first_K]
+    P2 = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], alleletable=at if use == "alleletable" else None, **kw)
+    K2 = P2.incremental_partition([5, 4], first_cluster=first)
+    if use == "alleletable":
+        assert sorted(map(sorted, K2)) == sorted(map(sorted, K))
