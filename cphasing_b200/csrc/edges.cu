@@ -248,7 +248,6 @@ struct PtSmem {
     u32 cnt[PT_WIN];
     alignas(16) u8 mq[PT_WIN];   // raw MAPQ bytes of the window (bulk-copy staging)
     alignas(8) unsigned long long mbar;
-    u32 ord[PT_WIN];            // at the first record of a read: number of its (read, contig) representatives
     u32 head[PT_WORDS];
     u32 rep[PT_WORDS];
     u32 first[PT_WORDS];        // representative with no valid record before it in its read: head of the hyperedge
@@ -287,6 +286,21 @@ __device__ __forceinline__ int pt_seg_start(const u32* __restrict__ head, int i)
     while (m == 0) m = head[--w];
     return w * 32 + 31 - __clz(m);
 }
+__device__ __forceinline__ int pt_seg_end(const u32* __restrict__ head, int i, int fend) {   // first head > i, else fend
+    int w = i >> 5;
+    u32 m = head[w] & ~((2u << (i & 31)) - 1u);
+    while (m == 0 && ++w < PT_WORDS) m = head[w];
+    const int e = m ? w * 32 + __ffs(m) - 1 : fend;
+    return e < fend ? e : fend;
+}
+__device__ __forceinline__ u32 pt_range_popc(const u32* __restrict__ words, int s, int e) {   // set bits in [s, e), s < e
+    const int ws = s >> 5, we = (e - 1) >> 5;
+    const u32 ms = 0xffffffffu << (s & 31), me = 0xffffffffu >> (31 - ((e - 1) & 31));
+    if (ws == we) return __popc(words[ws] & ms & me);
+    u32 c = __popc(words[ws] & ms) + __popc(words[we] & me);
+    for (int w = ws + 1; w < we; ++w) c += __popc(words[w]);
+    return c;
+}
 // TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
 // signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
@@ -312,7 +326,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
     } while (!ok);
 }
 
-__global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
+__global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                 unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
                                                                 u32* __restrict__ rem_row, u32* __restrict__ rem_col,
                                                                 u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
@@ -344,7 +358,6 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int 
         }
         for (int i = tid; i < PT_WIN; i += PT_THREADS) {
             S.cnt[i] = 1u;
-            S.ord[i] = 0u;
         }
         mbar_wait(&S.mbar, 0);
         for (int i = tid; i < PT_WIN; i += PT_THREADS) {
@@ -360,7 +373,6 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int 
             S.read[i] = in.read[t];
             S.cvq[i] = porec_cvq(in, t);
             S.cnt[i] = 1u;
-            S.ord[i] = 0u;
         }
     }
     __syncthreads();
@@ -423,7 +435,6 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int 
                         break;
                     }
                 }
-                if (rep) atomicAdd(&S.ord[s0], 1u);
             }
         }
         u32 m = __ballot_sync(0xffffffffu, rep);
@@ -441,7 +452,7 @@ __global__ void __launch_bounds__(PT_THREADS) porec_tile_kernel(PorecIn in, int 
         int i = i0 + tid;
         bool keep = false;
         if (i >= beg && i < fend && ((S.rep[i >> 5] >> (i & 31)) & 1u)) {
-            const u32 order = S.ord[pt_seg_start(S.head, i)];
+            const u32 order = pt_range_popc(S.rep, pt_seg_start(S.head, i), pt_seg_end(S.head, i, fend));
             keep = order >= min_order && order <= max_order;
             if (keep) {
                 my_max_read = S.read[i];

@@ -98,6 +98,79 @@ __global__ void __launch_bounds__(TPB) expand_kernel(const u32* __restrict__ pem
     }
 }
 
+// Fused form of diag_hist_kernel + expand_kernel: ONE pass over the pem.  Thread per entry (grid-stride, persistent
+// CTAs): the entry adds its own c^2 term to the diagonal (shared-memory u64 bins flushed once per CTA when n fits,
+// global REDs otherwise) and owns the pairs with the later entries of its hyperedge.  The loads of the NEXT grid-stride
+// iteration are issued before the pair loop of the current one, so the DRAM latency of the coalesced pem stream hides
+// behind the RED traffic; the triangle index stays in 32-bit arithmetic when n(n+1) < 2^32.
+constexpr int XT = 512;
+template <bool SMEM_DIAG, bool IDX32>
+__global__ void __launch_bounds__(XT, 3) expand_diag_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk,
+                                                            const float* __restrict__ ew, u64 nnz, u32 n, int use_high_order,
+                                                            int frac_bits, unsigned long long* __restrict__ acc,
+                                                            unsigned long long* __restrict__ diag) {
+    extern __shared__ unsigned long long xbins[];
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    if (SMEM_DIAG)
+        for (u32 i = threadIdx.x; i < n; i += XT) xbins[i] = 0ull;
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * XT;
+    size_t a = gtid();
+    u32 ra = 0, pa = 0, rb = CPH_HEAD;
+    float wa = 1.0f;
+    if (a < nnz) {
+        ra = pem_row[a];
+        pa = pem_pk[a];
+        rb = a + 1 < nnz ? pem_row[a + 1] : CPH_HEAD;
+        if (ew) wa = ew[a];
+    }
+    const u32 two_n1 = 2u * n + 1u;
+    while (a < nnz) {
+        const size_t an = a + stride;
+        u32 ra2 = 0, pa2 = 0, rb2 = CPH_HEAD;
+        float wa2 = 1.0f;
+        if (an < nnz) {     // prefetch the next iteration's entry
+            ra2 = pem_row[an];
+            pa2 = pem_pk[an];
+            rb2 = an + 1 < nnz ? pem_row[an + 1] : CPH_HEAD;
+            if (ew) wa2 = ew[an];
+        }
+        const u32 i = ra & CPH_ROWM;
+        double sc = scale[use_high_order ? (pa >> 24) : 1u];
+        if (ew) sc *= (double)wa;
+        const double ca = (double)(pa & CPH_CNTM);
+        const double fa = ca * sc;
+        const unsigned long long dv = __double2ull_rn(fa * ca);
+        if (SMEM_DIAG) atomicAdd(&xbins[i], dv);
+        else atomicAdd(&diag[i], dv);
+        size_t b = a + 1;
+        while (!(rb & CPH_HEAD)) {
+            const u32 j = rb & CPH_ROWM;
+            const double cb = (double)(pem_pk[b] & CPH_CNTM);
+            unsigned long long v = __double2ull_rn(fa * cb);
+            const u32 lo = i < j ? i : j, hi = i < j ? j : i;
+            if (i == j) v += v;   // duplicated (row, col): both orders land on the diagonal
+            if (IDX32) atomicAdd(&acc[(lo * (two_n1 - lo)) / 2u + (hi - lo)], v);
+            else atomicAdd(&acc[tri_index(lo, hi, n)], v);
+            if (++b >= nnz) break;
+            rb = pem_row[b];
+        }
+        a = an;
+        ra = ra2;
+        pa = pa2;
+        rb = rb2;
+        wa = wa2;
+    }
+    if (SMEM_DIAG) {
+        __syncthreads();
+        for (u32 i = threadIdx.x; i < n; i += XT) {
+            const unsigned long long v = xbins[i];
+            if (v) atomicAdd(&diag[i], v);
+        }
+    }
+}
+
 struct Epi {
     const u64* acc;
     const u64* diag;
@@ -225,6 +298,37 @@ extern "C" int cph_expand_accumulate(const u32* pem_row, const u32* pem_pk, cons
     size_t want = ceil_div(nnz, TPB);
     unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
     expand_kernel<<<grid, TPB, 0, st>>>(pem_row, pem_pk, entry_w, nnz, n, use_high_order, frac_bits, (unsigned long long*)acc);
+    KERNEL_CHECK();
+    return CPH_OK;
+}
+
+extern "C" int cph_expand_accumulate_diag(const u32* pem_row, const u32* pem_pk, const float* entry_w, u64 nnz, u32 n,
+                                          int use_high_order, int frac_bits, int zero_first, u64* acc, u64* diag_fx, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(acc && diag_fx && n > 0);
+    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
+    const size_t tri = (size_t)n * ((size_t)n + 1) / 2;
+    if (zero_first) CUDA_TRY(cudaMemsetAsync(acc, 0, tri * sizeof(u64), st));
+    CUDA_TRY(cudaMemsetAsync(diag_fx, 0, (size_t)n * sizeof(u64), st));
+    if (nnz == 0) return CPH_OK;
+    ARG_CHECK(pem_row && pem_pk);
+    const bool smem_diag = n <= 4096;               // 32 KB of u64 bins, 3 CTAs of 512 threads per SM
+    const bool idx32 = n <= 46340;                  // n (n + 1) < 2^31
+    const size_t smem = smem_diag ? (size_t)n * sizeof(u64) : 0;
+    size_t want = ceil_div(nnz, (size_t)XT);
+    unsigned grid = (unsigned)(want < 148 * 3 ? want : 148 * 3);
+    unsigned long long* A = (unsigned long long*)acc;
+    unsigned long long* Dg = (unsigned long long*)diag_fx;
+#define XLAUNCH(S, I)                                                                                                          \
+    do {                                                                                                                       \
+        if (smem > 48 * 1024)                                                                                                  \
+            CUDA_TRY(cudaFuncSetAttribute(expand_diag_kernel<S, I>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   \
+        expand_diag_kernel<S, I><<<grid, XT, smem, st>>>(pem_row, pem_pk, entry_w, nnz, n, use_high_order, frac_bits, A, Dg);  \
+    } while (0)
+    if (smem_diag) XLAUNCH(true, true);
+    else if (idx32) XLAUNCH(false, true);
+    else XLAUNCH(false, false);
+#undef XLAUNCH
     KERNEL_CHECK();
     return CPH_OK;
 }

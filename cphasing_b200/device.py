@@ -386,10 +386,8 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     if acc is None:
         acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    check(lib().cph_diag_hist(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, max(n, 1), int(use_high_order),
-                              int(frac_bits), ptr(diag), stream()))
-    check(lib().cph_expand_accumulate(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, n, int(use_high_order),
-                                      int(frac_bits), int(zero), ptr(acc), stream()))
+    check(lib().cph_expand_accumulate_diag(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, max(n, 1),
+                                           int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))
     return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
 
 

@@ -166,6 +166,11 @@ int cph_diag_hist(const uint32_t* pem_row, const uint32_t* pem_pk, const float* 
                   int use_high_order, int frac_bits, uint64_t* diag_fx, cph_stream_t stream);
 int cph_expand_accumulate(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz, uint32_t n,
                           int use_high_order, int frac_bits, int zero_first, uint64_t* acc, cph_stream_t stream);
+/* cph_diag_hist + cph_expand_accumulate in ONE pass over the pem (the hot-path form): diag_fx is zeroed and filled,
+ * acc is zeroed first when zero_first != 0. */
+int cph_expand_accumulate_diag(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz,
+                               uint32_t n, int use_high_order, int frac_bits, int zero_first, uint64_t* acc,
+                               uint64_t* diag_fx, cph_stream_t stream);
 int cph_expand_count(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
                      uint64_t* h_nnz, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 int cph_expand_emit(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
