@@ -144,7 +144,7 @@ struct ItSmem {
     u32 keep[IT_WORDS];
     u32 kpref[IT_WORDS + 1];
     int beg, end, last;
-    u32 tile, base, long_k, long_res, scan[IT_THREADS / 32 + 1];
+    u32 tile, base, long_k, long_res, has_zero, scan[IT_THREADS / 32 + 1];
     unsigned long long long_end, long_sum;
 };
 
@@ -191,7 +191,7 @@ __device__ __forceinline__ u32 inc_new_row(const IncIn& in, size_t t) {   // new
     return nr >= 0 ? (u32)nr : CPH_ROWM;
 }
 
-__global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, unsigned long long* __restrict__ tile_state,
+__global__ void __launch_bounds__(IT_THREADS, 3) incidence_tile_kernel(IncIn in, unsigned long long* __restrict__ tile_state,
                                                                     u32* __restrict__ scal, unsigned long long* __restrict__ heads_total,
                                                                     u32* __restrict__ pem_row, u32* __restrict__ pem_pk) {
     extern __shared__ __align__(16) unsigned char it_raw[];
@@ -204,6 +204,7 @@ __global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, un
         S.last = -1;
         S.long_k = 0;
         S.long_sum = 0;
+        S.has_zero = 0u;
     }
     __syncthreads();
     const u32 tile = S.tile;
@@ -211,36 +212,64 @@ __global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, un
     const size_t N = in.nnz;
     const int own = (int)min((size_t)IT_TILE, N - lo);
     const int wn = (int)min((size_t)IT_WIN, N - lo);
-    // stage + heads + ok bits
-    for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS) {
-        int i = i0 + tid;
-        bool head = false, ok = false;
-        if (i < wn) {
-            size_t t = lo + i;
-            u32 r = in.row[t];
-            u32 c = in.cnt[t];
-            if (in.cmask == 0xffffffffu && c > CPH_CNTM) scal[0] = 1u;      // not representable as float32 count
-            u32 nr = inc_new_row(in, t);
-            ok = nr != CPH_ROWM;
-            S.row[i] = nr;
-            S.cnt[i] = c & in.cmask;
-            head = (r & CPH_HEAD) || t == 0;
+    // stage + heads + ok bits.  The loads of IT_LD window slices are issued together (memory-level parallelism: the
+    // kernel is latency-bound, not bandwidth-bound) before any of them is consumed.
+    constexpr int IT_LD = 5;
+    static_assert(IT_WIN % (IT_THREADS * IT_LD) == 0, "window must split into load batches");
+    bool zero_cnt = false;
+    for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS * IT_LD) {
+        u32 lr[IT_LD], lc[IT_LD];
+        int lq[IT_LD];
+#pragma unroll
+        for (int u = 0; u < IT_LD; ++u) {
+            const int i = i0 + u * IT_THREADS + tid;
+            lr[u] = 0; lc[u] = 0; lq[u] = 127;
+            if (i < wn) {
+                const size_t t = lo + i;
+                lr[u] = in.row[t];
+                lc[u] = in.cnt[t];
+                if (in.mapq) lq[u] = in.mapq[t];
+            }
         }
-        u32 mh = __ballot_sync(0xffffffffu, head), mo = __ballot_sync(0xffffffffu, ok);
-        if (lane == 0) {
-            S.head[i >> 5] = mh;
-            S.ok[i >> 5] = mo;
-            if (mh) {
-                u32 inside = (i + 32 <= own) ? mh : (i < own ? (mh & ((1u << (own - i)) - 1u)) : 0u);
-                u32 after = mh & ~inside;
-                if (inside) {
-                    atomicMin(&S.beg, i + __ffs(inside) - 1);
-                    atomicMax(&S.last, i + 31 - __clz(inside));
+        i32 lm[IT_LD];
+#pragma unroll
+        for (int u = 0; u < IT_LD; ++u) {
+            const int i = i0 + u * IT_THREADS + tid;
+            const u32 r = lr[u] & CPH_ROWM;
+            const bool in_ok = i < wn && (in.mapq == nullptr || lq[u] >= in.min_mapq) && r < in.n;
+            lm[u] = in_ok ? in.row_map[r] : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < IT_LD; ++u) {
+            const int i = i0 + u * IT_THREADS + tid;
+            bool head = false, ok = false;
+            if (i < wn) {
+                const u32 c = lc[u];
+                if (in.cmask == 0xffffffffu && c > CPH_CNTM) scal[0] = 1u;      // not representable as float32 count
+                const u32 nr = lm[u] >= 0 ? (u32)lm[u] : CPH_ROWM;
+                ok = nr != CPH_ROWM;
+                S.row[i] = nr;
+                S.cnt[i] = c & in.cmask;
+                zero_cnt |= ok && (c & in.cmask) == 0u;
+                head = (lr[u] & CPH_HEAD) || (lo + i) == 0;
+            }
+            u32 mh = __ballot_sync(0xffffffffu, head), mo = __ballot_sync(0xffffffffu, ok);
+            if (lane == 0) {
+                S.head[i >> 5] = mh;
+                S.ok[i >> 5] = mo;
+                if (mh) {
+                    u32 inside = (i + 32 <= own) ? mh : (i < own ? (mh & ((1u << (own - i)) - 1u)) : 0u);
+                    u32 after = mh & ~inside;
+                    if (inside) {
+                        atomicMin(&S.beg, i + __ffs(inside) - 1);
+                        atomicMax(&S.last, i + 31 - __clz(inside));
+                    }
+                    if (after) atomicMin(&S.end, i + __ffs(after) - 1);
                 }
-                if (after) atomicMin(&S.end, i + __ffs(after) - 1);
             }
         }
     }
+    if (zero_cnt) S.has_zero = 1u;      // explicit zero counts (host matrices): the k >= col_min_sum shortcut is off
     __syncthreads();
     const int beg = S.beg;
     const bool empty = beg == 0x7fffffff;
@@ -258,6 +287,7 @@ __global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, un
     __syncthreads();
     // per hyperedge (thread at its start): surviving entries k, their summed count -> keep, D_e
     u32 my_heads = 0;
+    const bool has_zero = S.has_zero != 0u;
     for (int i0 = 0; i0 < IT_WIN; i0 += IT_THREADS) {
         int i = i0 + tid;
         if (!empty && i >= beg && i < fend && ((S.head[i >> 5] >> (i & 31)) & 1u)) {
@@ -268,11 +298,24 @@ __global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, un
             int e = m ? w * 32 + __ffs(m) - 1 : fend;
             e = min(e, fend);
             const u32 k = it_rank(S.ok, S.opref, e) - it_rank(S.ok, S.opref, i);
-            u64 colsum = 0;
-            for (int j = i; j < e; ++j)
-                if (S.row[j] != CPH_ROWM) colsum += S.cnt[j];
-            const bool edge_keep = k > 0 && colsum >= (u64)in.col_min_sum;     // algorithms/hypergraph.py:305-306
-            S.res[i] = (edge_keep ? 1u : 0u) | (edge_degree(k) << 8);
+            // summed count >= col_min_sum (algorithms/hypergraph.py:305-306).  Every count is >= 1 unless the tile saw
+            // an explicit zero, so k >= col_min_sum already decides it; only short survivors need the real sum.
+            bool edge_keep = k > 0;
+            if (edge_keep && (k < in.col_min_sum || has_zero)) {
+                u64 colsum = 0;
+                for (int j = i; j < e; ++j)
+                    if (S.row[j] != CPH_ROWM) colsum += S.cnt[j];
+                edge_keep = colsum >= (u64)in.col_min_sum;
+            }
+            // offset of the first surviving entry (it becomes the head of the packed hyperedge)
+            u32 foff = 0;
+            if (edge_keep) {
+                int fw = i >> 5;
+                u32 fm = S.ok[fw] & ~((1u << (i & 31)) - 1u);
+                while (fm == 0) fm = S.ok[++fw];
+                foff = (u32)(fw * 32 + __ffs(fm) - 1 - i);
+            }
+            S.res[i] = (edge_keep ? 1u : 0u) | (edge_degree(k) << 8) | (foff << 16);
             my_heads += edge_keep ? 1u : 0u;
         }
     }
@@ -285,9 +328,9 @@ __global__ void __launch_bounds__(IT_THREADS) incidence_tile_kernel(IncIn in, un
             const u32 rs = S.res[s0];
             keep = rs & 1u;
             if (keep) {
-                const bool first = it_rank(S.ok, S.opref, i) == it_rank(S.ok, S.opref, s0);
+                const bool first = (u32)(i - s0) == (rs >> 16);
                 S.row[i] |= first ? CPH_HEAD : 0u;
-                S.cnt[i] |= (rs >> 8) << 24;
+                S.cnt[i] |= ((rs >> 8) & 0xffu) << 24;
             }
         }
         u32 m = __ballot_sync(0xffffffffu, keep);

@@ -400,3 +400,25 @@ def test_porec_host_streamed_chunks(api, chunk, pinned, monkeypatch):
     row2, col2, cnt2, mq2 = D.edges_to_triplets(raw2)
     assert np.array_equal(row2.cpu().numpy(), exp[0]) and np.array_equal(col2.cpu().numpy() - 3, exp[1])
     assert np.array_equal(cnt2.view(torch.int32).cpu().numpy().view(np.uint32), exp[2])
+
+
+def test_extract_rows_with_explicit_zero_counts(api):
+    """extract_incidence_matrix2 (algorithms/hypergraph.py:938-954) on a host matrix that stores explicit zeros: the
+    column test is on the SUMMED count, so a hyperedge with two surviving entries of which one is a stored 0 must go
+    (the kernel's `k >= col_min_sum` shortcut has to switch itself off for such tiles)."""
+    ah = api[0]
+    rng = np.random.default_rng(11)
+    n, m = 60, 9000
+    k = rng.integers(2, 7, size=m)
+    cols = np.repeat(np.arange(m), k)
+    rows = np.concatenate([rng.choice(n, size=x, replace=False) for x in k])
+    data = rng.integers(0, 3, size=rows.size).astype(np.float32)          # about a third explicit zeros
+    H = csr_matrix((data, (rows, cols)), shape=(n, m))
+    assert (H.data == 0).sum() > 1000                                      # zeros really are stored
+    idx = np.sort(rng.choice(n, size=25, replace=False))
+    sub, removed, kept = ah.extract_incidence_matrix2(H, idx)
+    eo, ro, ko = orc.extract_incidence_matrix2(H, idx)
+    assert np.array_equal(kept, ko) and np.array_equal(np.asarray(removed), ro)
+    assert sub.shape == eo.shape
+    for x, y in zip(canon_dup(sub), canon_dup(eo)):
+        assert np.array_equal(x, y)
