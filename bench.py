@@ -331,10 +331,10 @@ def run_own(args):
     stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
     s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
     s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
-    per_kernel = {"expand_kernel+diag_hist_kernel (cph_expand_accumulate + cph_diag_hist)":
+    per_kernel = {"expand_diag_kernel (cph_expand_accumulate_diag)":
                   {"bytes": 8 * nnzH, "ms": acc_ms, "GBps": 8 * nnzH / acc_ms / 1e6, "frac": 8 * nnzH / acc_ms / 1e6 / peak}}
     if cfg["kind"] == "pairs":
-        kname, kbytes, kms, traffic = "expand_kernel (cph_expand_accumulate)", 8 * nnzH, acc_ms, None
+        kname, kbytes, kms, traffic = "expand_diag_kernel (cph_expand_accumulate_diag)", 8 * nnzH, acc_ms, None
     else:
         kname, kbytes, kms = "porec_tile_kernel (cph_porec_to_edges)", 9 * n_rec + 8 * raw.nnz, edges_ms
         # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/r1d_ncu_full_top3.txt)

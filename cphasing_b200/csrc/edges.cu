@@ -242,18 +242,20 @@ __device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (co
     return ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
 }
 
+constexpr int PT_RPT = PT_TILE / PT_THREADS;      // reads per thread in the per-read passes (worst case: 1 record per read)
+static_assert(PT_TILE % PT_THREADS == 0, "tile must split evenly over the threads");
+
 struct PtSmem {
     alignas(16) u32 read[PT_WIN];
-    alignas(16) u32 cvq[PT_WIN];
-    u32 cnt[PT_WIN];
-    alignas(16) u8 mq[PT_WIN];   // raw MAPQ bytes of the window (bulk-copy staging)
+    alignas(16) u32 cvq[PT_WIN];   // window records, then IN PLACE the distinct-contig list of every read (slot s + d)
+    alignas(16) u8 mq[PT_WIN];     // raw MAPQ bytes of the window (bulk-copy staging)
     alignas(8) unsigned long long mbar;
+    u16 cnt[PT_WIN];               // record count of the list entry in the same slot
+    u16 rstart[PT_WIN + 1];        // window position of the r-th read start (every head of the window, halo included)
+    u16 off[PT_TILE + 1];          // per owned read: surviving entries, then their exclusive prefix
+    u16 src[PT_WIN];               // output slot -> window position of the list entry
     u32 head[PT_WORDS];
-    u32 rep[PT_WORDS];
-    u32 first[PT_WORDS];        // representative with no valid record before it in its read: head of the hyperedge
-    u32 keep[PT_WORDS];
-    u32 kpref[PT_WORDS + 1];
-    int beg, end, last;
+    u32 hpref[PT_WORDS + 1];
     u32 tile, base, long_order, scan[PT_THREADS / 32 + 1];
     unsigned long long long_end;
 };
@@ -279,27 +281,6 @@ __device__ __forceinline__ void pt_word_prefix(const u32* __restrict__ words, u3
         for (int k = 0; k < PER; ++k) pref[tid * PER + k] = ex + loc[k];
         if (tid == 31) pref[PT_WORDS] = incl;
     }
-}
-__device__ __forceinline__ int pt_seg_start(const u32* __restrict__ head, int i) {   // last head <= i (exists)
-    int w = i >> 5;
-    u32 m = head[w] & (0xffffffffu >> (31 - (i & 31)));
-    while (m == 0) m = head[--w];
-    return w * 32 + 31 - __clz(m);
-}
-__device__ __forceinline__ int pt_seg_end(const u32* __restrict__ head, int i, int fend) {   // first head > i, else fend
-    int w = i >> 5;
-    u32 m = head[w] & ~((2u << (i & 31)) - 1u);
-    while (m == 0 && ++w < PT_WORDS) m = head[w];
-    const int e = m ? w * 32 + __ffs(m) - 1 : fend;
-    return e < fend ? e : fend;
-}
-__device__ __forceinline__ u32 pt_range_popc(const u32* __restrict__ words, int s, int e) {   // set bits in [s, e), s < e
-    const int ws = s >> 5, we = (e - 1) >> 5;
-    const u32 ms = 0xffffffffu << (s & 31), me = 0xffffffffu >> (31 - ((e - 1) & 31));
-    if (ws == we) return __popc(words[ws] & ms & me);
-    u32 c = __popc(words[ws] & ms) + __popc(words[we] & me);
-    for (int w = ws + 1; w < we; ++w) c += __popc(words[w]);
-    return c;
 }
 // TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
 // signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
@@ -327,17 +308,14 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
 }
 
 __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
-                                                                unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
-                                                                u32* __restrict__ rem_row, u32* __restrict__ rem_col,
-                                                                u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
+                                                                   unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
+                                                                   u32* __restrict__ rem_row, u32* __restrict__ rem_col,
+                                                                   u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
     extern __shared__ __align__(16) unsigned char pt_raw[];
     PtSmem& S = *reinterpret_cast<PtSmem*>(pt_raw);
     const int tid = threadIdx.x, lane = tid & 31;
     if (tid == 0) {
         S.tile = atomicAdd(&scal[3], 1u);        // ticket: every lower tile has already started
-        S.beg = 0x7fffffff;
-        S.end = 0x7fffffff;
-        S.last = -1;
         S.long_order = 0;
         if (use_tma) mbar_init(&S.mbar, 1);
     }
@@ -356,9 +334,6 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
             bulk_g2s(S.cvq, in.contig + lo, PT_WIN * 4u, &S.mbar);
             bulk_g2s(S.mq, in.mapq + lo, PT_WIN, &S.mbar);
         }
-        for (int i = tid; i < PT_WIN; i += PT_THREADS) {
-            S.cnt[i] = 1u;
-        }
         mbar_wait(&S.mbar, 0);
         for (int i = tid; i < PT_WIN; i += PT_THREADS) {
             const u32 c = S.cvq[i];
@@ -372,10 +347,10 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
             size_t t = lo + i;
             S.read[i] = in.read[t];
             S.cvq[i] = porec_cvq(in, t);
-            S.cnt[i] = 1u;
         }
     }
     __syncthreads();
+    // read starts of the window as a bitmask
     const u32 prev_read = lo > 0 ? in.read[lo - 1] : 0u;
     for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
         int i = i0 + tid;
@@ -387,83 +362,86 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
             if (i < own && (lo + i) > 0 && p > r) scal[1] = 1u;   // not grouped by read (benign race)
         }
         u32 m = __ballot_sync(0xffffffffu, head);
-        if (lane == 0) {
-            S.head[i >> 5] = m;
-            if (m) {
-                u32 inside = (i + 32 <= own) ? m : (i < own ? (m & ((1u << (own - i)) - 1u)) : 0u);
-                u32 after = m & ~inside;
-                if (inside) {
-                    atomicMin(&S.beg, i + __ffs(inside) - 1);
-                    atomicMax(&S.last, i + 31 - __clz(inside));
-                }
-                if (after) atomicMin(&S.end, i + __ffs(after) - 1);
-            }
-        }
+        if (lane == 0) S.head[i >> 5] = m;
     }
     __syncthreads();
-    const int beg = S.beg;
-    const bool empty = beg == 0x7fffffff;    // a longer read covers the whole tile: its owner emits it
+    pt_word_prefix(S.head, S.hpref, tid);
+    __syncthreads();
+    // a tile OWNS the reads that start inside it (positions < own); the first head at or after `own` ends the last one
+    const int nh_total = (int)S.hpref[PT_WORDS];
+    const int nr_own = (int)(S.hpref[own >> 5] + __popc(S.head[own >> 5] & ((1u << (own & 31)) - 1u)));
+    const bool empty = nr_own == 0;          // a longer read covers the whole tile: its owner emits it
     bool is_long = false;
-    int fend = 0;
+    int nfast = 0;
     if (!empty) {
-        if (S.end != 0x7fffffff) fend = S.end;
-        else if (lo + wn == N) fend = wn;
-        else {
-            is_long = true;
-            fend = S.last;            // the last read of the tile overflows the window
+        if (nh_total > nr_own) nfast = nr_own;
+        else if (lo + wn == N) {
+            nfast = nr_own;
+            if (tid == 0) S.rstart[nr_own] = (u16)wn;
+        } else {
+            is_long = true;                  // the last read of the tile overflows the window: slow path
+            nfast = nr_own - 1;
         }
     }
-    // P1: representative = first valid record of its (read, contig); later ones fold count / max MAPQ into it.  Each
-    // representative also bumps the order counter kept at the first record of its read.
-    const int p_end = empty ? 0 : fend;                                    // block-uniform loop bound
-    for (int i0 = 0; i0 < p_end; i0 += PT_THREADS) {
-        int i = i0 + tid;
-        bool rep = false, first = false;
-        if (i >= beg && i < fend) {
-            const u32 x = S.cvq[i], c = x >> 8;
-            if (c != PT_INVALID) {
-                rep = true;
-                first = true;
-                const int s0 = pt_seg_start(S.head, i);
-                for (int j = s0; j < i; ++j) {
-                    const u32 cj = S.cvq[j] >> 8;
-                    if (cj != PT_INVALID) first = false;
-                    if (cj == c) {
-                        rep = false;
-                        atomicAdd(&S.cnt[j], 1u);
-                        atomicMax(&S.cvq[j], x);      // same contig bits, larger MAPQ byte wins
-                        break;
-                    }
-                }
-            }
-        }
-        u32 m = __ballot_sync(0xffffffffu, rep);
-        u32 f = __ballot_sync(0xffffffffu, rep && first);
-        if (lane == 0) {
-            S.rep[i >> 5] = m;
-            S.first[i >> 5] = f;
-        }
+    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
+        const int i = i0 + tid;
+        const u32 w = S.head[i >> 5];
+        if ((w >> (i & 31)) & 1u) S.rstart[S.hpref[i >> 5] + __popc(w & ((1u << (i & 31)) - 1u))] = (u16)i;
     }
-    for (int w = (p_end + 31) / 32 + tid; w < PT_WORDS; w += PT_THREADS) S.keep[w] = 0u;
     __syncthreads();
-    // P2: distinct-contig order of the read (hypergraph.py:1461-1468) decides which representatives survive
+    const int fend = empty ? 0 : (int)S.rstart[is_long ? nr_own - 1 : nr_own];
+    // one THREAD per read (hypergraph.py:1461-1477): walk its records once, keeping the distinct contigs in place at the
+    // front of the read's own span (slot s + d holds the d-th distinct contig in first-seen order, its record count and
+    // its largest MAPQ).  The number of distinct contigs is the read's order; reads outside [min_order, max_order] emit
+    // nothing.  No atomics, no per-record segment searches; consecutive threads own consecutive reads.
     u32 my_max_read = 0;
-    for (int i0 = 0; i0 < p_end; i0 += PT_THREADS) {
-        int i = i0 + tid;
-        bool keep = false;
-        if (i >= beg && i < fend && ((S.rep[i >> 5] >> (i & 31)) & 1u)) {
-            const u32 order = pt_range_popc(S.rep, pt_seg_start(S.head, i), pt_seg_end(S.head, i, fend));
-            keep = order >= min_order && order <= max_order;
-            if (keep) {
-                my_max_read = S.read[i];
-                if ((S.first[i >> 5] >> (i & 31)) & 1u) S.cnt[i] |= CPH_HEAD;     // first entry of the hyperedge
+    for (int r = tid; r < nfast; r += PT_THREADS) {
+        const int s = S.rstart[r], e = S.rstart[r + 1];
+        int nd = 0;
+        for (int j = s; j < e; ++j) {
+            const u32 x = S.cvq[j], c = x >> 8;
+            if (c == PT_INVALID) continue;
+            int f = 0;
+            while (f < nd && (S.cvq[s + f] >> 8) != c) ++f;
+            if (f == nd) {
+                S.cvq[s + nd] = x;
+                S.cnt[s + nd] = 1;
+                ++nd;
+            } else {
+                S.cnt[s + f] += 1;
+                if (x > S.cvq[s + f]) S.cvq[s + f] = x;      // same contig bits, larger MAPQ byte wins
             }
         }
-        u32 m = __ballot_sync(0xffffffffu, keep);
-        if (lane == 0) S.keep[i >> 5] = m;
+        const bool keep = (u32)nd >= min_order && (u32)nd <= max_order;
+        S.off[r] = keep ? (u16)nd : (u16)0;
+        if (keep) my_max_read = max(my_max_read, S.read[s]);
     }
     __syncthreads();
-    pt_word_prefix(S.keep, S.kpref, tid);
+    // exclusive prefix of the per-read output counts (each thread scans PT_RPT consecutive reads)
+    u32 fast_total = 0;
+    {
+        u32 v[PT_RPT], sum = 0;
+#pragma unroll
+        for (int k = 0; k < PT_RPT; ++k) {
+            const int r = tid * PT_RPT + k;
+            v[k] = r < nfast ? (u32)S.off[r] : 0u;
+            sum += v[k];
+        }
+        u32 ex = block_excl_scan<u32, PT_THREADS>(sum, S.scan, &fast_total);
+#pragma unroll
+        for (int k = 0; k < PT_RPT; ++k) {
+            const int r = tid * PT_RPT + k;
+            if (r < nfast) S.off[r] = (u16)ex;
+            ex += v[k];
+        }
+        if (tid == 0) S.off[nfast] = (u16)fast_total;
+    }
+    __syncthreads();
+    // output slot -> window position, so that the global stores below are coalesced
+    for (int r = tid; r < nfast; r += PT_THREADS) {
+        const int o = S.off[r], nd = (int)S.off[r + 1] - o, s = S.rstart[r];
+        for (int d = 0; d < nd; ++d) S.src[o + d] = (u16)(s + d);
+    }
     // slow path, part 1: order of the read that starts at `fend` and runs past the window
     u32 long_kept = 0;
     size_t ls = 0, le = 0;
@@ -493,11 +471,9 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
         const u32 order = S.long_order;
         if (order >= min_order && order <= max_order) {
             long_kept = order;
-            my_max_read = rid;
+            my_max_read = max(my_max_read, rid);
         }
     }
-    __syncthreads();
-    const u32 fast_total = empty ? 0u : S.kpref[PT_WORDS];
     const u32 total = fast_total + long_kept;
     // decoupled look-back (warp 0): exclusive prefix of the tile totals
     if (tid < 32) {
@@ -528,18 +504,14 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
     }
     __syncthreads();
     const u32 base = S.base;
-    if (!empty) {
-        for (int i = beg + tid; i < fend; i += PT_THREADS) {
-            u32 w = S.keep[i >> 5];
-            if ((w >> (i & 31)) & 1u) {
-                u32 p = base + S.kpref[i >> 5] + __popc(w & ((1u << (i & 31)) - 1u));
-                u32 a = S.cnt[i], x = S.cvq[i];
-                rem_row[p] = (x >> 8) | (a & CPH_HEAD);
-                rem_col[p] = S.read[i] + read_offset;             // generate_edges :1871-1875
-                rem_count[p] = a & CPH_ROWM;
-                rem_mapq[p] = (int8_t)((int)(x & 0xffu) - 128);
-            }
-        }
+    for (u32 p = tid; p < fast_total; p += PT_THREADS) {
+        const int pos = S.src[p];
+        const u32 x = S.cvq[pos];
+        const bool first = (S.head[pos >> 5] >> (pos & 31)) & 1u;             // slot s: first entry of the hyperedge
+        rem_row[base + p] = (x >> 8) | (first ? CPH_HEAD : 0u);
+        rem_col[base + p] = S.read[pos] + read_offset;                      // generate_edges :1871-1875
+        rem_count[base + p] = (u32)S.cnt[pos];
+        rem_mapq[base + p] = (int8_t)((int)(x & 0xffu) - 128);
     }
     if (long_kept) {     // slow path, part 2: emit the long read after the tile's fast entries
         u32 carry = 0;
