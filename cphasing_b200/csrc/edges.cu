@@ -242,7 +242,7 @@ __device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (co
     return ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
 }
 
-constexpr int PT_RPT = PT_TILE / PT_THREADS;      // reads per thread in the per-read passes (worst case: 1 record per read)
+constexpr int PT_RPT = PT_TILE / PT_THREADS;      // records of the tile per thread: thread t owns the reads that start in its slice
 static_assert(PT_TILE % PT_THREADS == 0, "tile must split evenly over the threads");
 
 struct PtSmem {
@@ -251,8 +251,7 @@ struct PtSmem {
     alignas(16) u8 mq[PT_WIN];     // raw MAPQ bytes of the window (bulk-copy staging)
     alignas(8) unsigned long long mbar;
     u16 cnt[PT_WIN];               // record count of the list entry in the same slot
-    u16 rstart[PT_WIN + 1];        // window position of the r-th read start (every head of the window, halo included)
-    u16 off[PT_TILE + 1];          // per owned read: surviving entries, then their exclusive prefix
+    u16 rn[PT_WIN];                // at a read start: number of entries the read emits (0 = filtered out)
     u16 src[PT_WIN];               // output slot -> window position of the list entry
     u32 head[PT_WORDS];
     u32 hpref[PT_WORDS + 1];
@@ -281,6 +280,22 @@ __device__ __forceinline__ void pt_word_prefix(const u32* __restrict__ words, u3
         for (int k = 0; k < PER; ++k) pref[tid * PER + k] = ex + loc[k];
         if (tid == 31) pref[PT_WORDS] = incl;
     }
+}
+__device__ __forceinline__ int pt_next_head(const u32* __restrict__ head, int i) {   // first head >= i, PT_WIN if none
+    if (i >= PT_WIN) return PT_WIN;
+    int w = i >> 5;
+    u32 m = head[w] & ~((1u << (i & 31)) - 1u);
+    while (m == 0) {
+        if (++w >= PT_WORDS) return PT_WIN;
+        m = head[w];
+    }
+    return w * 32 + __ffs(m) - 1;
+}
+__device__ __forceinline__ int pt_prev_head(const u32* __restrict__ head, int i) {   // last head <= i (must exist)
+    int w = i >> 5;
+    u32 m = head[w] & (0xffffffffu >> (31 - (i & 31)));
+    while (m == 0) m = head[--w];
+    return w * 32 + 31 - __clz(m);
 }
 // TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
 // signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
@@ -371,38 +386,29 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
     const int nh_total = (int)S.hpref[PT_WORDS];
     const int nr_own = (int)(S.hpref[own >> 5] + __popc(S.head[own >> 5] & ((1u << (own & 31)) - 1u)));
     const bool empty = nr_own == 0;          // a longer read covers the whole tile: its owner emits it
-    bool is_long = false;
-    int nfast = 0;
-    if (!empty) {
-        if (nh_total > nr_own) nfast = nr_own;
-        else if (lo + wn == N) {
-            nfast = nr_own;
-            if (tid == 0) S.rstart[nr_own] = (u16)wn;
-        } else {
-            is_long = true;                  // the last read of the tile overflows the window: slow path
-            nfast = nr_own - 1;
-        }
-    }
-    for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
-        const int i = i0 + tid;
-        const u32 w = S.head[i >> 5];
-        if ((w >> (i & 31)) & 1u) S.rstart[S.hpref[i >> 5] + __popc(w & ((1u << (i & 31)) - 1u))] = (u16)i;
-    }
-    __syncthreads();
-    const int fend = empty ? 0 : (int)S.rstart[is_long ? nr_own - 1 : nr_own];
-    // one THREAD per read (hypergraph.py:1461-1477): walk its records once, keeping the distinct contigs in place at the
-    // front of the read's own span (slot s + d holds the d-th distinct contig in first-seen order, its record count and
-    // its largest MAPQ).  The number of distinct contigs is the read's order; reads outside [min_order, max_order] emit
-    // nothing.  No atomics, no per-record segment searches; consecutive threads own consecutive reads.
-    u32 my_max_read = 0;
-    for (int r = tid; r < nfast; r += PT_THREADS) {
-        const int s = S.rstart[r], e = S.rstart[r + 1];
-        int nd = 0;
+    // the last read of the tile overflows the window (no later head, table not finished): slow path below
+    const bool is_long = !empty && nh_total == nr_own && lo + wn != N;
+    const int long_s = is_long ? pt_prev_head(S.head, own - 1) : PT_WIN;
+    const int fend = long_s;                 // only meaningful when is_long
+    // One THREAD per read (hypergraph.py:1461-1477).  Thread t owns the reads that start inside its PT_RPT-record slice
+    // of the tile -- their records add up to about PT_RPT whatever the read lengths are, so the pass is balanced by
+    // construction.  It walks each read once, keeping the distinct contigs IN PLACE at the front of the read's own span
+    // (slot s + d: d-th distinct contig in first-seen order, its record count and its largest MAPQ).  The number of
+    // distinct contigs is the read's order; reads outside [min_order, max_order] emit nothing.  No atomics.
+    const int sl_lo = tid * PT_RPT, sl_hi = min(sl_lo + PT_RPT, own);
+    u32 my_max_read = 0, my_out = 0;
+    for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s;) {
+        const int e = min(pt_next_head(S.head, s + 1), wn);
+        int nd = 0, lf = 0;
+        u32 lc = PT_INVALID;
         for (int j = s; j < e; ++j) {
             const u32 x = S.cvq[j], c = x >> 8;
             if (c == PT_INVALID) continue;
-            int f = 0;
-            while (f < nd && (S.cvq[s + f] >> 8) != c) ++f;
+            int f = lf;
+            if (c != lc) {               // (the previous record's contig is the likeliest match: adjacent duplicates)
+                f = 0;
+                while (f < nd && (S.cvq[s + f] >> 8) != c) ++f;
+            }
             if (f == nd) {
                 S.cvq[s + nd] = x;
                 S.cnt[s + nd] = 1;
@@ -411,36 +417,28 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
                 S.cnt[s + f] += 1;
                 if (x > S.cvq[s + f]) S.cvq[s + f] = x;      // same contig bits, larger MAPQ byte wins
             }
+            lc = c;
+            lf = f;
         }
         const bool keep = (u32)nd >= min_order && (u32)nd <= max_order;
-        S.off[r] = keep ? (u16)nd : (u16)0;
-        if (keep) my_max_read = max(my_max_read, S.read[s]);
+        S.rn[s] = keep ? (u16)nd : (u16)0;
+        if (keep) {
+            my_out += (u32)nd;
+            my_max_read = max(my_max_read, S.read[s]);
+        }
+        s = e;
     }
-    __syncthreads();
-    // exclusive prefix of the per-read output counts (each thread scans PT_RPT consecutive reads)
+    // exclusive prefix of the per-thread output counts
     u32 fast_total = 0;
-    {
-        u32 v[PT_RPT], sum = 0;
-#pragma unroll
-        for (int k = 0; k < PT_RPT; ++k) {
-            const int r = tid * PT_RPT + k;
-            v[k] = r < nfast ? (u32)S.off[r] : 0u;
-            sum += v[k];
-        }
-        u32 ex = block_excl_scan<u32, PT_THREADS>(sum, S.scan, &fast_total);
-#pragma unroll
-        for (int k = 0; k < PT_RPT; ++k) {
-            const int r = tid * PT_RPT + k;
-            if (r < nfast) S.off[r] = (u16)ex;
-            ex += v[k];
-        }
-        if (tid == 0) S.off[nfast] = (u16)fast_total;
-    }
-    __syncthreads();
+    const u32 my_ex = block_excl_scan<u32, PT_THREADS>(my_out, S.scan, &fast_total);
     // output slot -> window position, so that the global stores below are coalesced
-    for (int r = tid; r < nfast; r += PT_THREADS) {
-        const int o = S.off[r], nd = (int)S.off[r + 1] - o, s = S.rstart[r];
-        for (int d = 0; d < nd; ++d) S.src[o + d] = (u16)(s + d);
+    {
+        u32 o = my_ex;
+        for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s; s = pt_next_head(S.head, s + 1)) {
+            const int nd = S.rn[s];
+            for (int d = 0; d < nd; ++d) S.src[o + d] = (u16)(s + d);
+            o += nd;
+        }
     }
     // slow path, part 1: order of the read that starts at `fend` and runs past the window
     u32 long_kept = 0;
