@@ -220,9 +220,9 @@ __global__ void __launch_bounds__(TPB) porec_emit_kernel(KeyView kv, const u32* 
 // HBM traffic: 9 B per record + 13 B per surviving entry.  The one read per tile that can overflow the
 // window is handled by a slow cooperative walk over global memory.
 // ------------------------------------------------------------------------------------------------
-constexpr int PT_THREADS = 512;
-constexpr int PT_TILE = 3584;     // + halo = 4096-record window: 70 KB of shared memory, 3 CTAs per SM
-constexpr int PT_HALO = 512;
+constexpr int PT_THREADS = 256;
+constexpr int PT_TILE = 1792;     // + halo = 2048-record window: 31 KB of shared memory, 6 CTAs of 256 threads per SM
+constexpr int PT_HALO = 256;
 constexpr int PT_WIN = PT_TILE + PT_HALO;
 constexpr int PT_WORDS = PT_WIN / 32;
 constexpr u32 PT_INVALID = 0x00ffffffu;          // contig field of a filtered-out record (n_contigs < 2^23)
@@ -322,7 +322,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
     } while (!ok);
 }
 
-__global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
+__global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                    unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
                                                                    u32* __restrict__ rem_row, u32* __restrict__ rem_col,
                                                                    u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
@@ -397,21 +397,52 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
     // distinct contigs is the read's order; reads outside [min_order, max_order] emit nothing.  No atomics.
     const int sl_lo = tid * PT_RPT, sl_hi = min(sl_lo + PT_RPT, own);
     u32 my_max_read = 0, my_out = 0;
-    for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s;) {
-        const int e = min(pt_next_head(S.head, s + 1), wn);
-        int nd = 0, lf = 0;
-        u32 lc = PT_INVALID;
-        for (int j = s; j < e; ++j) {
+    {
+        // ONE flat loop over the records of the slice's reads (a nested read / record loop makes the lanes of a warp
+        // drift apart at every read boundary).  The first four distinct contigs of the current read live in registers,
+        // so the usual order <= 4 never searches the list in shared memory.
+        int j = pt_next_head(S.head, sl_lo);
+        int jend = j;
+        if (j < sl_hi && j != long_s) {
+            jend = min(pt_next_head(S.head, sl_hi), wn);              // end of the last read that starts in the slice
+            if (is_long && jend > long_s) jend = long_s;              // ... the overflowing read is not ours to walk
+        }
+        int s = j, nd = 0, lf = 0;
+        u32 c0 = PT_INVALID, c1 = PT_INVALID, c2 = PT_INVALID, c3 = PT_INVALID, lc = PT_INVALID;
+        auto finish = [&]() {
+            const bool keep = (u32)nd >= min_order && (u32)nd <= max_order;
+            S.rn[s] = keep ? (u16)nd : (u16)0;
+            if (keep) {
+                my_out += (u32)nd;
+                my_max_read = max(my_max_read, S.read[s]);
+            }
+        };
+        for (; j < jend; ++j) {
+            if (j != s && ((S.head[j >> 5] >> (j & 31)) & 1u)) {      // next read of the slice starts here
+                finish();
+                s = j;
+                nd = 0;
+                lc = c0 = c1 = c2 = c3 = PT_INVALID;
+            }
             const u32 x = S.cvq[j], c = x >> 8;
             if (c == PT_INVALID) continue;
-            int f = lf;
-            if (c != lc) {               // (the previous record's contig is the likeliest match: adjacent duplicates)
-                f = 0;
+            int f;
+            if (c == lc) f = lf;                                      // adjacent duplicate: the likeliest case
+            else if (c == c0) f = 0;
+            else if (c == c1) f = 1;
+            else if (c == c2) f = 2;
+            else if (c == c3) f = 3;
+            else {
+                f = nd < 4 ? nd : 4;
                 while (f < nd && (S.cvq[s + f] >> 8) != c) ++f;
             }
             if (f == nd) {
                 S.cvq[s + nd] = x;
                 S.cnt[s + nd] = 1;
+                if (nd == 0) c0 = c;
+                else if (nd == 1) c1 = c;
+                else if (nd == 2) c2 = c;
+                else if (nd == 3) c3 = c;
                 ++nd;
             } else {
                 S.cnt[s + f] += 1;
@@ -420,13 +451,7 @@ __global__ void __launch_bounds__(PT_THREADS, 3) porec_tile_kernel(PorecIn in, i
             lc = c;
             lf = f;
         }
-        const bool keep = (u32)nd >= min_order && (u32)nd <= max_order;
-        S.rn[s] = keep ? (u16)nd : (u16)0;
-        if (keep) {
-            my_out += (u32)nd;
-            my_max_read = max(my_max_read, S.read[s]);
-        }
-        s = e;
+        if (jend > s) finish();
     }
     // exclusive prefix of the per-thread output counts
     u32 fast_total = 0;
