@@ -456,15 +456,6 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
     // exclusive prefix of the per-thread output counts
     u32 fast_total = 0;
     const u32 my_ex = block_excl_scan<u32, PT_THREADS>(my_out, S.scan, &fast_total);
-    // output slot -> window position, so that the global stores below are coalesced
-    {
-        u32 o = my_ex;
-        for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s; s = pt_next_head(S.head, s + 1)) {
-            const int nd = S.rn[s];
-            for (int d = 0; d < nd; ++d) S.src[o + d] = (u16)(s + d);
-            o += nd;
-        }
-    }
     // slow path, part 1: order of the read that starts at `fend` and runs past the window
     u32 long_kept = 0;
     size_t ls = 0, le = 0;
@@ -524,6 +515,16 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
             if (lane == 0) atomicExch(&tile_state[tile], PT_INCL | (running + total));
         }
         if (lane == 0) S.base = base;
+    }
+    // output slot -> window position, so that the global stores below are coalesced (warps 1.. do this while
+    // warp 0 is still looking back)
+    {
+        u32 o = my_ex;
+        for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s; s = pt_next_head(S.head, s + 1)) {
+            const int nd = S.rn[s];
+            for (int d = 0; d < nd; ++d) S.src[o + d] = (u16)(s + d);
+            o += nd;
+        }
     }
     __syncthreads();
     const u32 base = S.base;
