@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 # concatemer-column shards; N=1 is exactly the named config).  `--workload D` runs config D's genome (20k contigs) with
 # 62.5M concatemers per GPU (the named 500M at N=8); its numbers are recorded in profiles/ and DESIGN.md.
 # dram bytes per launch of the dominant kernel from the committed ncu --set full capture, keyed by (workload, m per GPU)
-NCU_TRAFFIC = {("C", 50_000_000): 2572098000 + 2290708000}
+NCU_TRAFFIC = {("C", 50_000_000): 2721182000 + 2306597000}      # profiles/r1j_ncu_full_top3.txt
 PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight=2.0)   # cphasing/_config.py:38-45
 
 
@@ -313,10 +313,10 @@ def run_own(args):
             stages.setdefault(n1, []).append(e0.elapsed_time(e1))
     stages = {k: sum(v) / len(v) for k, v in stages.items()}
 
-    # roofline of the DOMINANT kernel (profiles/r1d_launch_summary.txt: porec_tile_kernel = 45 % of the step on Pore-C
-    # tables; on pairs tables the expansion's expand_kernel).  ALGORITHMIC bytes:
+    # roofline of the DOMINANT kernel (profiles/r1j_launch_summary.txt: porec_tile_kernel = 42 % of the step on Pore-C
+    # tables; on pairs tables the expansion's expand_diag_kernel).  ALGORITHMIC bytes:
     #   porec_tile_kernel: 9 B per alignment record read + 8 B per surviving (read, contig) entry written
-    #   expand_kernel    : 8 B per H entry read (row + packed count/degree); its work figure is the pair REDs
+    #   expand_diag_kernel: 8 B per H entry read (row + packed count/degree); its work figure is the pair REDs
     # duration = CUDA events around the C-ABI call that launches it, averaged over the timed steps.
     peaks = {}
     try:
@@ -337,7 +337,7 @@ def run_own(args):
         kname, kbytes, kms, traffic = "expand_diag_kernel (cph_expand_accumulate_diag)", 8 * nnzH, acc_ms, None
     else:
         kname, kbytes, kms = "porec_tile_kernel (cph_porec_to_edges)", 9 * n_rec + 8 * raw.nnz, edges_ms
-        # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/r1d_ncu_full_top3.txt)
+        # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/r1j_ncu_full_top3.txt)
         traffic = NCU_TRAFFIC.get((name, cfg["m"]))
         per_kernel[kname] = {"bytes": kbytes, "ms": kms, "GBps": kbytes / kms / 1e6, "frac": kbytes / kms / 1e6 / peak}
     roof = {"bound": "hbm", "kernel": kname, "achieved": kbytes / kms / 1e6, "peak": peak, "unit": "GB/s",
