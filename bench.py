@@ -390,6 +390,40 @@ def run_own(args):
                       "ms_per_step": dt * 1e3, "ms_each": each, "stages_ms_synchronised": stages_e2e, "api": "HyperExtractor.from_arrays -> HyperGraph.incidence_matrix -> "
                                                       "HyperGraph.clique_expansion_init -> scipy csr (host)"}
         t = {k: v.to(dev) for k, v in host.items()} if not args.no_cpu_baseline else None
+    if world > 1 and not args.no_e2e:
+        # every rank feeds its own shard from pinned host memory through the device-module API (chunked H2D under the
+        # group-by kernel, the two NCCL exchanges, CSR emit) and rank 0 reads A back; max over ranks
+        import torch
+        from cphasing_b200 import device as Dm
+        host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in t.items()}
+        h2d = sum(v.numel() * v.element_size() for v in host.values())
+        del t, raw, H, A
+        _lib.release_workspace(); torch.cuda.empty_cache()
+
+        def e2e_multi():
+            evs = []
+            _, _, A2 = device_step(D, cfg, g, host, evs, world, rank)
+            nb = 0
+            if rank == 0:
+                parts = [Dm.to_host(A2.indptr), Dm.to_host(A2.indices), Dm.to_host(A2.data32)]
+                nb = sum(x.nbytes for x in parts)
+            torch.cuda.synchronize()
+            return nb
+        for _ in range(2):
+            e2e_multi()
+        ne = max(2, min(args.steps, 10))
+        barrier(); t0 = time.perf_counter()
+        for _ in range(ne):
+            d2h = e2e_multi()
+        barrier()
+        dtm = torch.tensor([(time.perf_counter() - t0) / ne], dtype=torch.float64, device=dev)
+        dist.all_reduce(dtm, op=dist.ReduceOp.MAX)
+        dt = float(dtm.item())
+        out["e2e"] = {"value": cfg["m"] * world / dt, "unit": "concatemers/s", "h2d_bytes_per_step": h2d * world,
+                      "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3,
+                      "api": "per rank: device.porec_to_edges(host columns) -> device.incidence (row-sum all-reduce) -> "
+                             "device.expand_accumulate -> triangle reduce-scatter/all-gather -> device.expand_emit; "
+                             "rank 0 reads CSR(A) back"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cb, _ = cpu_baseline(cfg, g, t, args.cpu_sample)
         out["cpu_baseline"] = cb
