@@ -428,7 +428,7 @@ def run_own(args):
         cb, _ = cpu_baseline(cfg, g, t, args.cpu_sample)
         out["cpu_baseline"] = cb
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -526,8 +526,18 @@ def run_reference(args):
                       "e2e": {"value": v, "unit": "concatemers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def _json_only_stdout():
+    """stdout must carry exactly ONE JSON line: libraries that write banners to fd 1 (NCCL's version line, torchrun
+    notices) are sent to stderr; the JSON line goes to the saved descriptor."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(saved, "w")
+
+
 if __name__ == "__main__":
     a = parse()
+    _json_only_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
