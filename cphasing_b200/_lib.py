@@ -67,6 +67,13 @@ _SIGS = {
     "cph_community": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _I, _I, _I, _I, _P, _P, C.POINTER(_D), C.POINTER(_U32)] + _WS),
     "cph_modularity": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _P, C.POINTER(_D)] + _WS),
     "cph_group_sums": (_I, [_P, _P, _P, _P, _U32, _U64, _P, _U32, _P, _P] + _WS),
+    "cph_irmm_edge_weights": (_I, [_P, _P, _U64, _P, _U32, _P, _P, _P, _P]),
+    "cph_expand_full": (_I, [_P, _P, _P, _P, _U64, _U32, _I, _P, _P]),
+    "cph_dense_from_csr": (_I, [_P, _P, _P, _P, _U32, _P, _P]),
+    "cph_irmm_blend": (_I, [_P, _I, _D, _P, _U32, _D, _P, _P]),
+    "cph_dense_scale_pairs": (_I, [_P, _U32, _P, _P, _U64, _D, _P]),
+    "cph_dense_to_csr_count": (_I, [_P, _U32, _I, C.POINTER(_U64)] + _WS),
+    "cph_dense_to_csr_emit": (_I, [_P, _U32, _I, _P, _P, _P, _P, _P, _P]),
     "cph_synth_porec_count": (_I, [_U64, _U64, _U64, _I, _P, C.POINTER(_U64)] + _WS),
     "cph_synth_porec_fill": (_I, [_U64, _U64, _U64, _I, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cph_synth_pairs": (_I, [_U64, _U64, _U64, _D, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),

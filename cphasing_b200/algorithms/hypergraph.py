@@ -531,13 +531,12 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
       * the caller's A is NOT modified in place (the reference multiplies ``A.data`` by allelic_factor in place on every
         call, :1160-1164, so repeated calls in the resolution search flip the sign of allelic entries when
         allelic_factor < 0);
-      * ``max_round > 1`` (iterative hyperedge re-weighting, :1258-1397; CLI default 1) is not implemented yet.
+      * ``max_round > 1`` (iterative hyperedge re-weighting, :1258-1397; CLI default 1) keeps W, the suppressed
+        monomers and A on the device between rounds (csrc/irmm.cu); the matrix arithmetic of rounds >= 2 is fp64, as
+        in the reference (its A_new is a float64 product).
     """
     from .. import community, graphops
-    if max_round > 1:
-        raise NotImplementedError("IRMM max_round > 1 (iterative re-weighting) is not on the device path yet "
-                                  "(SURVEY.md 8f rank 4; the CLI default is --max-round 1)")
-    if A is None:
+    if A is None or max_round > 1:        # :1120 -- with max_round > 1 the reference rebuilds A from H as well
         # A = H W D_e^-1 H^T, threshold, normalise, zero diagonal (:1120-1150)
         A = HyperGraph.clique_expansion_init(H, NW=NW, min_weight=float(min_weight) if min_weight > 0 else 0.0)
     raw_A = A
@@ -552,5 +551,51 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
                                                n_iterations=2, use32=False)
     cluster_assignments = community.VertexClustering(mem.cpu().numpy(), q, stats)
     cluster_results = [set(c) for c in cluster_assignments]
+    if max_round > 1:
+        return _irmm_rounds(H, raw_A, a, NW, P_allelic_idx, P_weak_idx, allelic_factor, resolution, min_weight, threshold,
+                            max_round, use_leiden, cluster_assignments)
     A_out = wrap_adjacency(a, dtype=A.dtype if A.dtype in (np.float32, np.float64) else np.float32)
+    return raw_A, A_out, cluster_assignments, cluster_results
+
+
+def _irmm_rounds(H, raw_A, a, NW, P_allelic_idx, P_weak_idx, allelic_factor, resolution, min_weight, threshold, max_round,
+                 use_leiden, cluster_assignments):
+    """Rounds 2.. of IRMM (:1258-1397): per-hyperedge re-weighting from the current clusters, damped update of A,
+    re-clustering (Leiden starts from the previous membership, :1368-1373), until the partition is stable (ARI > 0.99),
+    the weights stop moving or max_round is reached.  All matrix work in csrc/irmm.cu; n-sized decisions here."""
+    from .. import community, irmm
+    dH = device_handle(H)
+    if not isinstance(dH, D.DeviceH):
+        dH = upload_incidence(H)
+    R = irmm.Rounds(dH, a, node_w=_node_weights_from_NW(NW) if NW is not None else None, P_allelic=P_allelic_idx,
+                    P_weak=P_weak_idx, allelic_factor=allelic_factor, min_weight=float(min_weight) if min_weight > 0 else 0.0)
+    membership = np.asarray(cluster_assignments.membership)
+    iter_round, diff_value, previous = 1, 1.0, None
+    history = []
+    while diff_value > threshold:
+        if iter_round >= max_round:
+            break
+        c = len(cluster_assignments)
+        diff_value = R.reweight(membership, c)
+        R.blend(0.5)
+        g = R.to_csr(1)
+        mem, q, stats = community.community_device(g, float(resolution), "leiden" if use_leiden else "louvain",
+                                                   n_iterations=2, initial_membership=membership if use_leiden else None,
+                                                   use32=False)
+        cluster_assignments = community.VertexClustering(mem.cpu().numpy(), q, stats)
+        membership = np.asarray(cluster_assignments.membership)
+        score = None
+        if previous is not None:
+            score = irmm.ari(previous, membership)
+        history.append({"round": iter_round, "max_dW": diff_value, "masked": R.masked_entries(), "ari": score,
+                        "groups": stats["groups"]})
+        if score is not None and score > 0.99:
+            logger.info("[IRMM] Converged early due to stable partitioning.")
+            break
+        previous = membership.copy()
+        iter_round += 1
+    cluster_results = [set(c) for c in cluster_assignments]
+    A_out = wrap_adjacency(R.to_csr(0), dtype=np.float64)
+    A_out._irmm_history = history
+    A_out._irmm_state = R
     return raw_A, A_out, cluster_assignments, cluster_results

@@ -264,6 +264,32 @@ int cph_synth_pairs(uint64_t seed, uint64_t first, uint64_t m, double intra, uin
                     const int64_t* length, uint32_t* chrom1, uint32_t* chrom2, uint32_t* pos1, uint32_t* pos2,
                     int8_t* mapq, cph_stream_t stream);
 
+/* ---- IRMM rounds 2.. : iterative hyperedge re-weighting (algorithms/hypergraph.py:1258-1397) ------------------
+ * cph_irmm_edge_weights: per hyperedge, from the cluster labels of its contigs (labels[n], n_clusters = c):
+ *     K_el over the ORIGINAL entries (:1282), e_c over the entries not yet masked (:1283), w_new (:1285-1289),
+ *     purity rules (:1291-1313; suppressed entries get mask = 1), W update (:1316-1317).  mask (u8) and entry_w
+ *     (float, constant inside a hyperedge) are per-pem-entry state carried from round to round (start: 0 / 1.0f).
+ * cph_expand_full: A_new = H' W D_e^-1 H^T (:1321) into a FULL n x n fixed-point matrix (zeroed first); the entry of
+ *     the LEFT factor must be unmasked, so the result is not symmetric -- as in the reference.
+ * cph_dense_from_csr: CSR(A) -> dense fp64 n x n.   cph_irmm_blend: A <- (1-damping) A + damping thr(A_new), optional
+ *     w_i w_j normalisation, zero diagonal (:1322-1329).   cph_dense_scale_pairs: A[r,c] *= factor (0 -> exact 0) for a
+ *     DEDUPLICATED pair list (:1330-1349).   cph_dense_to_csr_count/emit: dense -> CSR; mode 0 = A as is, mode 1 = the
+ *     undirected graph igraph builds from triu(A) (:1351-1366), mirrored into both triangles. */
+int cph_irmm_edge_weights(const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, const int32_t* labels,
+                          uint32_t n_clusters, uint8_t* mask, float* entry_w, uint64_t* n_suppressed, cph_stream_t stream);
+int cph_expand_full(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, const uint8_t* mask,
+                    uint64_t nnz, uint32_t n, int frac_bits, uint64_t* acc_full, cph_stream_t stream);
+int cph_dense_from_csr(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64,
+                       uint32_t n, double* dense, cph_stream_t stream);
+int cph_irmm_blend(const uint64_t* acc_full, int frac_bits, double min_weight, const double* node_w, uint32_t n,
+                   double damping, double* dense, cph_stream_t stream);
+int cph_dense_scale_pairs(double* dense, uint32_t n, const int64_t* rows, const int64_t* cols, uint64_t n_pairs,
+                          double factor, cph_stream_t stream);
+int cph_dense_to_csr_count(const double* dense, uint32_t n, int mode, uint64_t* h_nnz, void* ws, size_t ws_bytes,
+                           size_t* h_ws_need, cph_stream_t stream);
+int cph_dense_to_csr_emit(const double* dense, uint32_t n, int mode, const void* ws, int64_t* indptr, int32_t* indices,
+                          float* data32, double* data64, cph_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

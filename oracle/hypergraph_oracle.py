@@ -489,3 +489,123 @@ def recluster_by_linkage(A, K, contig_lens, min_weight, allelic_idx_set=(), min_
             c2g[c] = bg
             moved += 1
     return ([sorted(int(x) for x in s) for s in newK] if moved else [list(x) for x in K]), moved
+
+
+# --------------------------------------------------------------------------------------------
+# IRMM rounds 2.. (algorithms/hypergraph.py:1258-1397) -- restated line by line; the clustering itself is passed in
+# --------------------------------------------------------------------------------------------
+def irmm_reweight_round(H, H_T, W, D_e_inv, membership, n_clusters):
+    """One pass of :1270-1317.  H: current (re-weighted) csr float32, H_T: the ORIGINAL transpose, W: float32 vector
+    (W.data[0] of the dia matrix), membership: int[n].  Returns (H_new csr, W_new float32 vector)."""
+    n_contigs, n_hyperedges = H.shape
+    c = int(n_clusters)
+    C = csr_matrix((np.ones(n_contigs, dtype=np.float32), (np.arange(n_contigs), np.asarray(membership))),
+                   shape=(n_contigs, c))
+    K = (H_T @ C).toarray()
+    e_c = np.array(H.sum(axis=0)).flatten()
+    w_prev = W
+    inv_k = 1.0 / (1.0 + K)
+    inv_k_sum = inv_k.sum(axis=1)
+    denom = np.maximum(e_c * 2.0, 1.0)
+    w_new = inv_k_sum * (e_c + c) / denom
+    max_cluster_counts = K.max(axis=1)
+    purity = max_cluster_counts / np.maximum(e_c, 1.0)
+    noisy = (purity >= 0.75) & (e_c > max_cluster_counts) & (e_c >= 3)
+    if np.any(noisy):
+        pure = np.where(noisy)[0]
+        maj = K[pure].argmax(axis=1)
+        read_to_maj = np.full(n_hyperedges, -1, dtype=np.int32)
+        read_to_maj[pure] = maj
+        Hr = H.tocoo()
+        mono = np.asarray(membership, dtype=np.int32)[Hr.row]
+        exp = read_to_maj[Hr.col]
+        noise = (exp >= 0) & (mono != exp)
+        if np.any(noise):
+            Hr.data[noise] = 0.0
+            Hr.eliminate_zeros()
+        H = Hr.tocsr()
+    w_new = w_new * np.where((e_c >= 4) & (purity < 0.4), 0.1, 1.0)
+    w_updated = 0.5 * (w_new + w_prev)
+    W_out = np.where(e_c >= 2, w_updated, w_prev).astype(np.float32)
+    return H, W_out
+
+
+def irmm_rounds(H, cluster_fn, NW=None, P_allelic=None, P_weak=None, allelic_factor=-1.0, resolution=1.0,
+                min_weight=1.0, threshold=0.01, max_round=3):
+    """IRMM with max_round > 1 (:1120-1150 setup, :1157-1256 first clustering, :1258-1397 rounds).
+    cluster_fn(A_upper_symmetric csr, resolution, initial_membership or None) -> membership int[n].
+    NW: the VECTOR w (NW matrix = float32 outer(w, w)).  Returns (raw_A, A, membership, history) where history holds
+    per round (W, H.nnz, ari_to_previous)."""
+    from scipy.sparse import dia_matrix, diags, triu as _triu
+    H = H.tocsr().astype(np.float32)
+    n, m = H.shape
+    W = np.ones(m, dtype=np.float32)
+    with np.errstate(over="ignore"):
+        D_e_num = H.getnnz(axis=0).astype(ORDER_DTYPE) - ORDER_DTYPE(1)
+    d = 1.0 / np.maximum(D_e_num, 1)
+    H_T = H.T.tocsr()
+
+    def nw_scale(A):
+        if NW is None:
+            return A
+        A = A.tocoo()
+        nwm = np.outer(NW, NW).astype(np.float32)
+        A.data = A.data * nwm[A.row, A.col]
+        return A.tocsr()
+
+    def prep(A):
+        A = A.tocsr().copy()
+        if P_allelic is not None and len(P_allelic[0]):
+            off = np.unique(find_csr_data_offsets(A, np.asarray(P_allelic[0]), np.asarray(P_allelic[1])))
+            A.data[off] *= allelic_factor
+        if P_weak is not None and len(P_weak[0]):
+            off = np.unique(find_csr_data_offsets(A, np.asarray(P_weak[0]), np.asarray(P_weak[1])))
+            A.data[off] = 0
+        A.setdiag(0)
+        return A
+
+    def graph(A):
+        U = _triu(A, format="csr")
+        U.eliminate_zeros()
+        return (U + U.T).tocsr()
+
+    A = (H @ diags(W.astype(np.float64) * d) @ H_T).tocsr()
+    if min_weight > 0:
+        A.data[A.data < min_weight] = 0
+        A.eliminate_zeros()
+    A = nw_scale(A)
+    A.setdiag(0)
+    A.eliminate_zeros()
+    raw_A = A.copy()
+    A = prep(A)
+    membership = np.asarray(cluster_fn(graph(A), resolution, None))
+    hist = []
+    W_prev = W.copy()
+    it, diff, prev_mem = 1, 1.0, None
+    while diff > threshold:
+        if it >= max_round:
+            break
+        c = int(membership.max()) + 1
+        H, W = irmm_reweight_round(H, H_T, W, d, membership, c)
+        A_new = (H @ diags(W.astype(np.float64) * d) @ H_T).tocsr()
+        if min_weight > 0:
+            A_new.data[A_new.data < min_weight] = 0
+            A_new.eliminate_zeros()
+        A = (A * 0.5 + A_new * 0.5).tocsr()
+        A = nw_scale(A)
+        A.setdiag(0)
+        A.eliminate_zeros()
+        A = prep(A)
+        membership = np.asarray(cluster_fn(graph(A), resolution, membership))
+        a = None
+        if prev_mem is not None:
+            from oracle.community_oracle import ari as _ari
+            a = _ari(prev_mem, membership)
+        hist.append((W.copy(), H.nnz, a))
+        if a is not None and a > 0.99:
+            break
+        prev_mem = membership.copy()
+        diff = float(np.max(np.abs(W - W_prev)))
+        W_prev = W.copy()
+        it += 1
+    return raw_A, A, membership, hist

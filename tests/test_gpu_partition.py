@@ -147,8 +147,6 @@ def test_irmm_builds_A_when_missing(case):
     G = csr_matrix((np.concatenate([w, w]), (np.concatenate([src, dst]), np.concatenate([dst, src]))), shape=(n, n))
     mem_o, _ = co.community(G, 1.0, "louvain")
     assert co.ari(np.asarray(ca.membership), mem_o) >= 0.99
-    with pytest.raises(NotImplementedError):
-        ah.IRMM(case["H"], None, max_round=3)
 
 
 # ---- partition driver post-processing (hyperpartition.py:2288-2471, 2860-2968) against the reference's own outputs
@@ -320,3 +318,77 @@ def test_incremental_partition_two_rounds(case, use):
     K2 = P2.incremental_partition([5, 4], first_cluster=first)
     if use == "alleletable":
         assert sorted(map(sorted, K2)) == sorted(map(sorted, K))
+
+
+def test_irmm_reweight_round_matches_oracle(case):
+    """One round of IRMM's iterative re-weighting (algorithms/hypergraph.py:1270-1329) with the SAME membership on both
+    sides: per-hyperedge weights W, the suppressed monomers of H_reweighted, and the damped, asymmetric A."""
+    import torch
+    from cphasing_b200 import community, graphops, irmm
+    ah = case["ah"]
+    H, Ho = case["H"], case["Ho"].astype(np.float32)
+    A = ah.HyperGraph.clique_expansion_init(H, min_weight=2.0)
+    a = graphops.clone_adjacency(graphops.upload_adjacency(A))
+    graphops.zero_diagonal(a)
+    mem, _, st = community.community_device(a, 1.0, "louvain")
+    membership = mem.cpu().numpy()
+    c = int(membership.max()) + 1
+    assert 2 <= c < 100
+    R = irmm.Rounds(ah.device_handle(H), a, min_weight=2.0)
+    A0 = csr_matrix((a.data64.cpu().numpy(), a.indices.cpu().numpy(), a.indptr.cpu().numpy()), shape=A.shape).toarray()
+    dW = R.reweight(membership, c)
+    # oracle
+    with np.errstate(over="ignore"):
+        d = 1.0 / np.maximum(Ho.getnnz(axis=0).astype(np.int8) - np.int8(1), 1)
+    H_T = Ho.T.tocsr()
+    Hn, Wn = orc.irmm_reweight_round(Ho, H_T, np.ones(Ho.shape[1], np.float32), d, membership, c)
+    Wd = R.edge_weights().cpu().numpy()
+    assert Wd.shape == Wn.shape
+    np.testing.assert_allclose(Wd, Wn, rtol=2e-6)
+    assert R.masked_entries() == Ho.nnz - Hn.nnz and R.masked_entries() > 0
+    assert abs(dW - np.abs(Wn - 1.0).max()) < 1e-5
+    R.blend(0.5)
+    from scipy.sparse import diags
+    A_new = (Hn.astype(np.float64) @ diags(Wn.astype(np.float64) * d) @ H_T.astype(np.float64)).toarray()
+    edge = np.abs(A_new - 2.0) < 2e-5        # within float32 rounding of W of the threshold: may fall on either side
+    assert edge.sum() < 1000                 # of 160 000
+    A_new[A_new < 2.0] = 0
+    want = 0.5 * A0 + 0.5 * A_new
+    np.fill_diagonal(want, 0)
+    got = R.dense.cpu().numpy()
+    assert not np.allclose(want, want.T)                  # the reference's product really is asymmetric
+    np.testing.assert_allclose(got[~edge], want[~edge], rtol=1e-6, atol=1e-9)
+    # CSR views: mode 0 = A, mode 1 = mirrored upper triangle (what igraph clusters)
+    g0, g1 = R.to_csr(0), R.to_csr(1)
+    M0 = csr_matrix((g0.data64.cpu().numpy(), g0.indices.cpu().numpy(), g0.indptr.cpu().numpy()), shape=A.shape).toarray()
+    M1 = csr_matrix((g1.data64.cpu().numpy(), g1.indices.cpu().numpy(), g1.indptr.cpu().numpy()), shape=A.shape).toarray()
+    assert np.array_equal(M0, got)
+    U = np.triu(got, 1)
+    assert np.array_equal(M1, U + U.T)
+
+
+@pytest.mark.parametrize("method,allelic_factor", [("louvain", 0), ("leiden", -1)])
+def test_irmm_multi_round_end_to_end(case, method, allelic_factor):
+    """IRMM(max_round=4) on the planted 5 x 4 genome: device loop against the oracle's restatement of the same loop
+    driven by the sequential C clustering; both must land on the planted haplotype groups."""
+    ah, g = case["ah"], case["g"]
+    res = 2.0
+    raw_A, A, ca, K = ah.IRMM(case["H"], None, None, None, None, allelic_factor, 0.3, res, 2.0, 0.01, 4, method=method)
+    hist = A._irmm_history
+    assert 1 <= len(hist) <= 3 and hist[0]["masked"] > 0
+    mem = np.asarray(ca.membership)
+    assert len(mem) == case["H"].shape[0] and sorted(map(sorted, K)) == sorted(sorted(c) for c in ca)
+    names = list(case["nodes"])
+    old = {nm: i for i, nm in enumerate(sorted(g.contig_idx, key=g.contig_idx.get))}
+    truth = np.array([g.group[old[nm]] for nm in names])
+
+    def cl(G, resolution, init):
+        m, _ = co.community(G, resolution, "leiden" if (allelic_factor < 0 or method == "leiden") else "louvain",
+                            initial=init if (allelic_factor < 0 or method == "leiden") else None)
+        return m
+    _, Ao, mo, ho = orc.irmm_rounds(case["Ho"], cl, allelic_factor=allelic_factor, resolution=res, min_weight=2.0,
+                                    threshold=0.01, max_round=4)
+    assert co.ari(mem, truth) >= 0.99 and co.ari(mo, truth) >= 0.99
+    assert co.ari(mem, mo) >= 0.99
+    # the first round's weights do not depend on later clustering differences: same number of suppressed monomers
+    assert hist[0]["masked"] == case["Ho"].nnz - ho[0][1]
