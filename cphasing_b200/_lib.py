@@ -67,8 +67,8 @@ _SIGS = {
     "cph_community": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _I, _I, _I, _I, _P, _P, C.POINTER(_D), C.POINTER(_U32)] + _WS),
     "cph_modularity": (_I, [_P, _P, _P, _P, _U32, _U64, _D, _P, C.POINTER(_D)] + _WS),
     "cph_group_sums": (_I, [_P, _P, _P, _P, _U32, _U64, _P, _U32, _P, _P] + _WS),
-    "cph_irmm_edge_weights": (_I, [_P, _P, _U64, _P, _U32, _P, _P, _P, _P]),
-    "cph_expand_full": (_I, [_P, _P, _P, _P, _U64, _U32, _I, _P, _P]),
+    "cph_irmm_edge_weights": (_I, [_P, _P, _U64, _P, _U32, _P, _P, _I, _P, _P, _P]),
+    "cph_expand_full": (_I, [_P, _P, _P, _P, _P, _U64, _U32, _I, _P, _P]),
     "cph_dense_from_csr": (_I, [_P, _P, _P, _P, _U32, _P, _P]),
     "cph_irmm_blend": (_I, [_P, _I, _D, _P, _U32, _D, _P, _P]),
     "cph_dense_scale_pairs": (_I, [_P, _U32, _P, _P, _U64, _D, _P]),

@@ -25,7 +25,8 @@ __device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.
 // one thread per hyperedge (at its head entry)
 __global__ void __launch_bounds__(TPB) irmm_edge_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
                                                         const i32* __restrict__ label, u32 n_clusters, u8* __restrict__ mask,
-                                                        float* __restrict__ w, unsigned long long* __restrict__ n_suppressed) {
+                                                        u8* __restrict__ maskT, int alias, float* __restrict__ w,
+                                                        unsigned long long* __restrict__ n_suppressed) {
     const size_t t = gtid();
     if (t >= nnz) return;
     if (!(pem_row[t] & CPH_HEAD)) return;
@@ -35,7 +36,8 @@ __global__ void __launch_bounds__(TPB) irmm_edge_kernel(const u32* __restrict__ 
     double ec = 0.0;      // column sum of the CURRENT (re-weighted) H  (:1283)
     for (size_t j = t; j < e; ++j)
         if (!mask[j]) ec += (double)(pem_pk[j] & CPH_CNTM);
-    // K_el over the ORIGINAL entries (:1282 uses H_T, which is never re-weighted)
+    // K_el over the entries of H_T (:1282).  H_T shares H's data array until H is rebuilt (:1298-1310), so it carries
+    // the zeros of the FIRST suppression round and none of the later ones: maskT.
     int nd = 0, maj = 0x7fffffff;
     double inv = 0.0, maxK = -1.0;
     for (size_t j = t; j < e; ++j) {
@@ -49,7 +51,7 @@ __global__ void __launch_bounds__(TPB) irmm_edge_kernel(const u32* __restrict__ 
         if (!first) continue;
         double K = 0.0;
         for (size_t q = j; q < e; ++q)
-            if (label[pem_row[q] & CPH_ROWM] == l) K += (double)(pem_pk[q] & CPH_CNTM);
+            if (label[pem_row[q] & CPH_ROWM] == l && !maskT[q]) K += (double)(pem_pk[q] & CPH_CNTM);
         ++nd;
         inv += 1.0 / (1.0 + K);
         if (K > maxK || (K == maxK && l < maj)) {      // np.argmax: first (lowest) cluster among ties
@@ -65,6 +67,7 @@ __global__ void __launch_bounds__(TPB) irmm_edge_kernel(const u32* __restrict__ 
         for (size_t j = t; j < e; ++j)
             if (!mask[j] && label[pem_row[j] & CPH_ROWM] != maj) {
                 mask[j] = 1;
+                if (alias) maskT[j] = 1;
                 ++hit;
             }
         if (hit && n_suppressed) atomicAdd(n_suppressed, 1ull);
@@ -77,8 +80,9 @@ __global__ void __launch_bounds__(TPB) irmm_edge_kernel(const u32* __restrict__ 
 
 // thread per entry a: ordered pairs with the later entries b of its hyperedge, into the FULL matrix
 __global__ void __launch_bounds__(TPB) expand_full_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk,
-                                                          const float* __restrict__ w, const u8* __restrict__ mask, u64 nnz, u32 n,
-                                                          int frac_bits, unsigned long long* __restrict__ acc) {
+                                                          const float* __restrict__ w, const u8* __restrict__ maskL,
+                                                          const u8* __restrict__ maskT, u64 nnz, u32 n, int frac_bits,
+                                                          unsigned long long* __restrict__ acc) {
     __shared__ double scale[128];
     for (int d = threadIdx.x; d < 128; d += TPB) scale[d] = d ? ldexp(1.0, frac_bits) / (double)d : 0.0;
     __syncthreads();
@@ -90,16 +94,19 @@ __global__ void __launch_bounds__(TPB) expand_full_kernel(const u32* __restrict_
         if (rb & CPH_HEAD) continue;
         const u32 pa = pem_pk[a];
         const u64 i = pem_row[a] & CPH_ROWM;
-        const bool ma = mask && mask[a];
-        double sc = scale[pa >> 24];
-        if (w) sc *= (double)w[a];
-        const double fa = (double)(pa & CPH_CNTM) * sc;
+        const bool mla = maskL && maskL[a], mta = maskT && maskT[a];
+        const double sc = scale[pa >> 24];
+        const float wa = w ? w[a] : 1.0f;
+        const float ca = (float)(pa & CPH_CNTM);
+        // `H @ W @ D_e_inv @ H_T` runs left to right: (H @ W) is a float32 product, the rest float64 (:1321)
+        const double fa = (double)(ca * wa) * sc;
         for (;;) {
             const u64 j = rb & CPH_ROWM;
-            const unsigned long long v = __double2ull_rn(fa * (double)(pem_pk[b] & CPH_CNTM));
+            const float cb = (float)(pem_pk[b] & CPH_CNTM);
             if (i != j) {                                   // the diagonal is zeroed afterwards (:1329)
-                if (!ma) atomicAdd(&acc[i * n + j], v);     // H'[i,e] w d H[j,e]
-                if (!(mask && mask[b])) atomicAdd(&acc[j * n + i], v);
+                // A_new[i,j] += H'[i,e] w_e d_e H_T[e,j] : left factor from the re-weighted H, right one from H_T
+                if (!mla && !(maskT && maskT[b])) atomicAdd(&acc[i * n + j], __double2ull_rn(fa * (double)cb));
+                if (!(maskL && maskL[b]) && !mta) atomicAdd(&acc[j * n + i], __double2ull_rn((double)(cb * wa) * sc * (double)ca));
             }
             if (++b >= nnz) break;
             rb = pem_row[b];
@@ -190,18 +197,18 @@ __global__ void __launch_bounds__(TPB) dense_row_emit_kernel(const double* __res
 }  // namespace
 
 extern "C" int cph_irmm_edge_weights(const u32* pem_row, const u32* pem_pk, u64 nnz, const i32* labels, u32 n_clusters, u8* mask,
-                                     float* entry_w, u64* n_suppressed, void* stream) {
+                                     u8* mask_t, int alias, float* entry_w, u64* n_suppressed, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (nnz == 0) return CPH_OK;
-    ARG_CHECK(pem_row && pem_pk && labels && mask && entry_w && n_clusters > 0);
-    irmm_edge_kernel<<<grid_for(nnz, TPB), TPB, 0, st>>>(pem_row, pem_pk, nnz, labels, n_clusters, mask, entry_w,
+    ARG_CHECK(pem_row && pem_pk && labels && mask && mask_t && entry_w && n_clusters > 0);
+    irmm_edge_kernel<<<grid_for(nnz, TPB), TPB, 0, st>>>(pem_row, pem_pk, nnz, labels, n_clusters, mask, mask_t, alias, entry_w,
                                                          (unsigned long long*)n_suppressed);
     KERNEL_CHECK();
     return CPH_OK;
 }
 
-extern "C" int cph_expand_full(const u32* pem_row, const u32* pem_pk, const float* entry_w, const u8* mask, u64 nnz, u32 n,
-                               int frac_bits, u64* acc_full, void* stream) {
+extern "C" int cph_expand_full(const u32* pem_row, const u32* pem_pk, const float* entry_w, const u8* mask, const u8* mask_t,
+                               u64 nnz, u32 n, int frac_bits, u64* acc_full, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     ARG_CHECK(acc_full && n > 0);
     ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
@@ -210,7 +217,8 @@ extern "C" int cph_expand_full(const u32* pem_row, const u32* pem_pk, const floa
     ARG_CHECK(pem_row && pem_pk);
     size_t want = ceil_div(nnz, (size_t)TPB);
     unsigned grid = (unsigned)(want < 148 * 8 ? want : 148 * 8);
-    expand_full_kernel<<<grid, TPB, 0, st>>>(pem_row, pem_pk, entry_w, mask, nnz, n, frac_bits, (unsigned long long*)acc_full);
+    expand_full_kernel<<<grid, TPB, 0, st>>>(pem_row, pem_pk, entry_w, mask, mask_t, nnz, n, frac_bits,
+                                             (unsigned long long*)acc_full);
     KERNEL_CHECK();
     return CPH_OK;
 }

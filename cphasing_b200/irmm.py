@@ -1,7 +1,7 @@
 """IRMM rounds 2.. on the device (reference: cphasing/algorithms/hypergraph.py:1258-1397).
 
-State carried from round to round: a per-pem-entry mask (the zeroed monomers of ``H_reweighted``), a per-pem-entry
-weight (``W``, constant inside a hyperedge) and the dense fp64 ``A``.  Kernels: csrc/irmm.cu.
+State carried from round to round: two per-pem-entry masks (the zeroed monomers of ``H_reweighted`` and the subset
+that also reached ``H_T`` through the reference's shared data array), a per-pem-entry weight (``W``, constant inside a hyperedge) and the dense fp64 ``A``.  Kernels: csrc/irmm.cu.
 """
 from __future__ import annotations
 
@@ -49,7 +49,9 @@ class Rounds:
         self.n = dH.n_rows
         dev = dH.device
         self.dev = dev
-        self.mask = torch.zeros(max(dH.nnz, 1), dtype=torch.uint8, device=dev)
+        self.mask = torch.zeros(max(dH.nnz, 1), dtype=torch.uint8, device=dev)       # zeros of H_reweighted
+        self.mask_t = torch.zeros(max(dH.nnz, 1), dtype=torch.uint8, device=dev)     # zeros that reached H_T (aliasing)
+        self.alias = True           # H still is the object H_T was taken from (:1135, 1298-1310)
         self.w = torch.ones(max(dH.nnz, 1), dtype=torch.float32, device=dev)
         self.dense = torch.empty((self.n, self.n), dtype=torch.float64, device=dev)
         check(lib().cph_dense_from_csr(ptr(a.indptr), ptr(a.indices), ptr(a.data32) if a.data64 is None else None,
@@ -67,16 +69,20 @@ class Rounds:
         """:1270-1317 -> updates mask and w; returns max |W - W_prev| (:1389)."""
         lab = D.to_dev(np.asarray(membership, dtype=np.int32), torch.int32, self.dev)
         w_prev = self.w.clone()
+        self.suppressed.zero_()
         check(lib().cph_irmm_edge_weights(ptr(self.H.pem_row), ptr(self.H.pem_pk), self.H.nnz, ptr(lab), int(n_clusters),
-                                          ptr(self.mask), ptr(self.w), ptr(self.suppressed), stream()))
+                                          ptr(self.mask), ptr(self.mask_t), int(self.alias), ptr(self.w),
+                                          ptr(self.suppressed), stream()))
+        if self.alias and int(self.suppressed.item()) > 0:
+            self.alias = False
         return float((self.w - w_prev).abs().max().item()) if self.H.nnz else 0.0
 
     def blend(self, damping=0.5):
         """:1321-1349: A_new = H' W D_e^-1 H^T, threshold, A <- (1-d) A + d A_new, normalise, zero diagonal, pairs."""
         wmax = float(self.w.max().item()) if self.H.nnz else 1.0
         fb = D.frac_bits_for(int(self._bound * max(1.0, np.ceil(wmax))))
-        check(lib().cph_expand_full(ptr(self.H.pem_row), ptr(self.H.pem_pk), ptr(self.w), ptr(self.mask), self.H.nnz,
-                                    self.n, fb, ptr(self.accF), stream()))
+        check(lib().cph_expand_full(ptr(self.H.pem_row), ptr(self.H.pem_pk), ptr(self.w), ptr(self.mask), ptr(self.mask_t),
+                                    self.H.nnz, self.n, fb, ptr(self.accF), stream()))
         check(lib().cph_irmm_blend(ptr(self.accF), fb, self.min_weight, ptr(self.node_w), self.n, float(damping),
                                    ptr(self.dense), stream()))
         if self.Pa is not None:

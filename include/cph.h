@@ -269,16 +269,22 @@ int cph_synth_pairs(uint64_t seed, uint64_t first, uint64_t m, double intra, uin
  *     K_el over the ORIGINAL entries (:1282), e_c over the entries not yet masked (:1283), w_new (:1285-1289),
  *     purity rules (:1291-1313; suppressed entries get mask = 1), W update (:1316-1317).  mask (u8) and entry_w
  *     (float, constant inside a hyperedge) are per-pem-entry state carried from round to round (start: 0 / 1.0f).
- * cph_expand_full: A_new = H' W D_e^-1 H^T (:1321) into a FULL n x n fixed-point matrix (zeroed first); the entry of
- *     the LEFT factor must be unmasked, so the result is not symmetric -- as in the reference.
+ *     Two masks, because of an aliasing effect in the reference: `H_T = H.T` (:1135) and `H.tocoo()` (:1298) share H's
+ *     data array, so the zeros of the FIRST suppression round also land in H_T; after that H gets fresh arrays (:1308-1310)
+ *     and H_T stays as it is.  mask = zeros of H (all rounds), mask_t = zeros of H_T; `alias` != 0 while no suppression has
+ *     happened yet (the caller clears it after the first call that reports n_suppressed > 0).  K_el reads H_T (mask_t).
+ * cph_expand_full: A_new = H' W D_e^-1 H_T (:1321) into a FULL n x n fixed-point matrix (zeroed first): the left factor
+ *     of a term must be unmasked in `mask`, the right one in `mask_t`, (H' W) is rounded to float32 as in the reference.
  * cph_dense_from_csr: CSR(A) -> dense fp64 n x n.   cph_irmm_blend: A <- (1-damping) A + damping thr(A_new), optional
  *     w_i w_j normalisation, zero diagonal (:1322-1329).   cph_dense_scale_pairs: A[r,c] *= factor (0 -> exact 0) for a
  *     DEDUPLICATED pair list (:1330-1349).   cph_dense_to_csr_count/emit: dense -> CSR; mode 0 = A as is, mode 1 = the
  *     undirected graph igraph builds from triu(A) (:1351-1366), mirrored into both triangles. */
 int cph_irmm_edge_weights(const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, const int32_t* labels,
-                          uint32_t n_clusters, uint8_t* mask, float* entry_w, uint64_t* n_suppressed, cph_stream_t stream);
+                          uint32_t n_clusters, uint8_t* mask, uint8_t* mask_t, int alias, float* entry_w,
+                          uint64_t* n_suppressed, cph_stream_t stream);
 int cph_expand_full(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, const uint8_t* mask,
-                    uint64_t nnz, uint32_t n, int frac_bits, uint64_t* acc_full, cph_stream_t stream);
+                    const uint8_t* mask_t, uint64_t nnz, uint32_t n, int frac_bits, uint64_t* acc_full,
+                    cph_stream_t stream);
 int cph_dense_from_csr(const int64_t* indptr, const int32_t* indices, const float* data32, const double* data64,
                        uint32_t n, double* dense, cph_stream_t stream);
 int cph_irmm_blend(const uint64_t* acc_full, int frac_bits, double min_weight, const double* node_w, uint32_t n,

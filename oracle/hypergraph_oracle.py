@@ -494,9 +494,13 @@ def recluster_by_linkage(A, K, contig_lens, min_weight, allelic_idx_set=(), min_
 # --------------------------------------------------------------------------------------------
 # IRMM rounds 2.. (algorithms/hypergraph.py:1258-1397) -- restated line by line; the clustering itself is passed in
 # --------------------------------------------------------------------------------------------
-def irmm_reweight_round(H, H_T, W, D_e_inv, membership, n_clusters):
-    """One pass of :1270-1317.  H: current (re-weighted) csr float32, H_T: the ORIGINAL transpose, W: float32 vector
-    (W.data[0] of the dia matrix), membership: int[n].  Returns (H_new csr, W_new float32 vector)."""
+def irmm_reweight_round(H, H_T, W, membership, n_clusters, alias):
+    """One pass of :1270-1317.  H: current (re-weighted) csr float32; H_T: the transpose IRMM keeps from its set-up
+    (:1135); W: float32 vector (W.data[0] of the dia matrix); membership: int[n].
+    Aliasing, restated explicitly: `H_T = H.T` (:1135) and `H.tocoo()` (:1298) both SHARE H's data array, so the first
+    time monomers are zeroed (:1307) the zeros land in H_T as well; `eliminate_zeros()` + `tocsr()` (:1308-1310) then give
+    H fresh arrays and later rounds leave H_T alone.  `alias` says whether H still is the set-up object.
+    Returns (H_new, H_T_new, W_new, alias_new); nothing is modified in place."""
     n_contigs, n_hyperedges = H.shape
     c = int(n_clusters)
     C = csr_matrix((np.ones(n_contigs, dtype=np.float32), (np.arange(n_contigs), np.asarray(membership))),
@@ -516,18 +520,25 @@ def irmm_reweight_round(H, H_T, W, D_e_inv, membership, n_clusters):
         maj = K[pure].argmax(axis=1)
         read_to_maj = np.full(n_hyperedges, -1, dtype=np.int32)
         read_to_maj[pure] = maj
-        Hr = H.tocoo()
+        Hr = H.tocoo(copy=True)
         mono = np.asarray(membership, dtype=np.int32)[Hr.row]
         exp = read_to_maj[Hr.col]
         noise = (exp >= 0) & (mono != exp)
         if np.any(noise):
+            if alias:        # the same zeros appear in H_T (stored explicitly there, which changes no product)
+                T = H_T.tocoo(copy=True)
+                exp_t = read_to_maj[T.row]
+                T.data[(exp_t >= 0) & (np.asarray(membership, dtype=np.int32)[T.col] != exp_t)] = 0.0
+                T.eliminate_zeros()
+                H_T = T.tocsr()
             Hr.data[noise] = 0.0
             Hr.eliminate_zeros()
         H = Hr.tocsr()
+        alias = False
     w_new = w_new * np.where((e_c >= 4) & (purity < 0.4), 0.1, 1.0)
     w_updated = 0.5 * (w_new + w_prev)
     W_out = np.where(e_c >= 2, w_updated, w_prev).astype(np.float32)
-    return H, W_out
+    return H, H_T, W_out, alias
 
 
 def irmm_rounds(H, cluster_fn, NW=None, P_allelic=None, P_weak=None, allelic_factor=-1.0, resolution=1.0,
@@ -543,7 +554,6 @@ def irmm_rounds(H, cluster_fn, NW=None, P_allelic=None, P_weak=None, allelic_fac
     with np.errstate(over="ignore"):
         D_e_num = H.getnnz(axis=0).astype(ORDER_DTYPE) - ORDER_DTYPE(1)
     d = 1.0 / np.maximum(D_e_num, 1)
-    H_T = H.T.tocsr()
 
     def nw_scale(A):
         if NW is None:
@@ -569,7 +579,16 @@ def irmm_rounds(H, cluster_fn, NW=None, P_allelic=None, P_weak=None, allelic_fac
         U.eliminate_zeros()
         return (U + U.T).tocsr()
 
-    A = (H @ diags(W.astype(np.float64) * d) @ H_T).tocsr()
+    from scipy.sparse import identity
+
+    def product(Hc, Wv, HTc):
+        # `H @ W @ D_e_inv @ H_T` exactly as written (:1136-1141, 1321): identity(float32) with W on its diagonal, a float64
+        # dia_matrix, left to right -- the float64 sums then run in scipy's own order, which decides exact threshold ties
+        Wm = identity(m, dtype=np.float32)
+        Wm.data[0] = Wv
+        return (Hc @ Wm @ dia_matrix((d, [0]), shape=(m, m)) @ HTc).tocsr()
+    H_T = H.T                      # csc sharing H's arrays, as in the reference (never modified in place here)
+    A = product(H, W, H_T)
     if min_weight > 0:
         A.data[A.data < min_weight] = 0
         A.eliminate_zeros()
@@ -582,12 +601,14 @@ def irmm_rounds(H, cluster_fn, NW=None, P_allelic=None, P_weak=None, allelic_fac
     hist = []
     W_prev = W.copy()
     it, diff, prev_mem = 1, 1.0, None
+    alias = True
     while diff > threshold:
         if it >= max_round:
             break
         c = int(membership.max()) + 1
-        H, W = irmm_reweight_round(H, H_T, W, d, membership, c)
-        A_new = (H @ diags(W.astype(np.float64) * d) @ H_T).tocsr()
+        H, H_T, W, alias = irmm_reweight_round(H, H_T, W, membership, c, alias)
+        # `H @ W @ D_e_inv @ H_T` (:1321) runs left to right: H @ W is a float32 product, D_e_inv is float64
+        A_new = product(H, W, H_T)
         if min_weight > 0:
             A_new.data[A_new.data < min_weight] = 0
             A_new.eliminate_zeros()

@@ -341,7 +341,8 @@ def test_irmm_reweight_round_matches_oracle(case):
     with np.errstate(over="ignore"):
         d = 1.0 / np.maximum(Ho.getnnz(axis=0).astype(np.int8) - np.int8(1), 1)
     H_T = Ho.T.tocsr()
-    Hn, Wn = orc.irmm_reweight_round(Ho, H_T, np.ones(Ho.shape[1], np.float32), d, membership, c)
+    Hn, HTn, Wn, alias = orc.irmm_reweight_round(Ho, H_T, np.ones(Ho.shape[1], np.float32), membership, c, True)
+    assert not alias and HTn.nnz == Hn.nnz          # first suppression round: the zeros reach H_T as well
     Wd = R.edge_weights().cpu().numpy()
     assert Wd.shape == Wn.shape
     np.testing.assert_allclose(Wd, Wn, rtol=2e-6)
@@ -349,14 +350,14 @@ def test_irmm_reweight_round_matches_oracle(case):
     assert abs(dW - np.abs(Wn - 1.0).max()) < 1e-5
     R.blend(0.5)
     from scipy.sparse import diags
-    A_new = (Hn.astype(np.float64) @ diags(Wn.astype(np.float64) * d) @ H_T.astype(np.float64)).toarray()
+    A_new = ((Hn @ diags(Wn)).astype(np.float32) @ diags(d) @ HTn).toarray()
     edge = np.abs(A_new - 2.0) < 2e-5        # within float32 rounding of W of the threshold: may fall on either side
     assert edge.sum() < 1000                 # of 160 000
     A_new[A_new < 2.0] = 0
     want = 0.5 * A0 + 0.5 * A_new
     np.fill_diagonal(want, 0)
     got = R.dense.cpu().numpy()
-    assert not np.allclose(want, want.T)                  # the reference's product really is asymmetric
+    assert not R.alias and int(R.mask_t.sum().item()) == R.masked_entries()
     np.testing.assert_allclose(got[~edge], want[~edge], rtol=1e-6, atol=1e-9)
     # CSR views: mode 0 = A, mode 1 = mirrored upper triangle (what igraph clusters)
     g0, g1 = R.to_csr(0), R.to_csr(1)
@@ -392,3 +393,31 @@ def test_irmm_multi_round_end_to_end(case, method, allelic_factor):
     assert co.ari(mem, mo) >= 0.99
     # the first round's weights do not depend on later clustering differences: same number of suppressed monomers
     assert hist[0]["masked"] == case["Ho"].nnz - ho[0][1]
+
+
+@pytest.mark.parametrize("name", ["louvain", "leiden"])
+@pytest.mark.parametrize("max_round", [1, 4])
+def test_irmm_against_reference_run(name, max_round):
+    """Device IRMM against the REFERENCE's own IRMM run (tests/golden/ref_irmm_rounds.npz: the reference's code, igraph's
+    clustering answered by oracle/community.c): same partition after every round, same returned A."""
+    import cphasing_b200.algorithms.hypergraph as ah
+    from helpers import load_golden, csr_from
+    g = load_golden("irmm_rounds")
+    H = csr_from(g, "H")
+    res, mw, thr = g["params"]
+    tag = f"{name}_r{max_round}"
+    leiden = name == "leiden"
+    P = [g["allelic_pairs"][:, 0], g["allelic_pairs"][:, 1]] if leiden else None
+    raw_A, A, ca, K = ah.IRMM(H, None, None, P, None, -1 if leiden else 0, 0.3, float(res), float(mw), float(thr),
+                              max_round, method=name)
+    mem = np.asarray(ca.membership)
+    assert co.ari(mem, g[tag + "_membership"]) >= 0.99
+    if max_round > 1:
+        hist = A._irmm_history
+        assert len(hist) == int(g[tag + "_ncalls"][0]) - 1
+    if co.ari(mem, g[tag + "_membership"]) == 1.0:
+        Aref = csr_from(g, tag + "_A").toarray()
+        Ag = csr_matrix(A).toarray()
+        np.fill_diagonal(Ag, 0); np.fill_diagonal(Aref, 0)
+        close = np.isclose(Ag, Aref, rtol=2e-5, atol=1e-9)
+        assert (~close).sum() <= 40, (~close).sum()          # threshold ties of A_new (0.5 / 0.25 steps after damping)
