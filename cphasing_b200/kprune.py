@@ -62,14 +62,43 @@ def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False
 
 def kprune_pairs(A, allele_pairs, max_alleles=1):
     """A: scipy matrix / DeviceBackedCSR; allele_pairs: (i, j) contig-index pairs in allele-table order.
-    Returns (allelic list[(i, j)], weak list[(i, j)]), each sorted, i < j."""
+    Returns (allelic list[(i, j)], weak list[(i, j)]), each sorted, i < j -- plus the (c, c) entries the reference's weak
+    list carries (see `_self_pairs`)."""
     a = graphops.upload_adjacency(A)
     flag, row_of = kprune_device(a, allele_pairs, max_alleles)
     cols = a.indices
     al = torch.nonzero(flag == 1).flatten()
     wk = torch.nonzero(flag == 2).flatten()
     pick = lambda ix: sorted(zip(row_of[ix].cpu().numpy().tolist(), cols[ix].cpu().numpy().tolist()))
-    return pick(al), pick(wk)
+    allelic, weak = pick(al), pick(wk)
+    if max_alleles == 1:
+        weak = sorted(weak + _self_pairs(a, allele_pairs))
+    return allelic, weak
+
+
+def _self_pairs(a: D.DeviceCSR, allele_pairs):
+    """The reference's `A.setdiag(0)` (kprune.py:419) stores an explicit zero on every diagonal cell and `triu(A)` keeps
+    stored zeros (:427), so every (c, c) is a candidate pair as well.  Its 2x2 block is [c, al] x [c, al]: the straight
+    matching scores 0, the crossed one A[c, al] + A[al, c] (minus the allelic zeroing of the upper triangle, :466), so
+    (c, c) lands in the weak list exactly when c has an allele group and a stored non-zero contact with it.  n look-ups."""
+    first = {}
+    for x, y in allele_pairs:
+        x = int(x); y = int(y)
+        if x not in first:
+            first[x] = y
+    cs = np.array([c for c, al in first.items() if al in first and 0 <= c < a.n and 0 <= al < a.n and c != al],
+                  dtype=np.int64)
+    if cs.size == 0:
+        return []
+    als = np.array([first[int(c)] for c in cs], dtype=np.int64)
+    lo, hi = np.minimum(cs, als), np.maximum(cs, als)
+    off = graphops.find_pairs(a, hi, lo)                      # the LOWER entry is never zeroed by remove_allelic
+    d = a.data64 if a.data64 is not None else a.data32
+    ok = off >= 0
+    val = torch.zeros(off.numel(), dtype=d.dtype, device=d.device)
+    val[ok] = d[off[ok]]
+    hit = (val != 0).cpu().numpy()
+    return [(int(c), int(c)) for c in cs[hit]]
 
 
 def allele_frame(alleletable):

@@ -281,7 +281,7 @@ def kprune_hypergraph(A, allele_pairs):
     allele-table order.  Returns (allelic list[(i,j)], weak list[(i,j)]) each sorted.
 
     allelic (:455-468) = allele pairs i<j that are stored non-zeros of triu(A); they are zeroed.
-    weak (:470-517): for every remaining stored (c1<c2 or c1==c2 excluded) pair of triu(A) whose
+    weak (:470-517): for every remaining stored pair of triu(A) (the diagonal included, see below) whose
     two contigs both have an allele group, score the 2x2 block [c1,al1]x[c2,al2] on A and call
     the pair weak unless the max-weight perfect matching pairs c1 with c2.
     Tie rule (igraph's choice on equal sums is unspecified): a tie counts as strong.
@@ -298,6 +298,10 @@ def kprune_hypergraph(A, allele_pairs):
     D = L.todok()
     pairs -= set(al)
     grp = allele_group_first(allele_pairs)
+    # `self.A.setdiag(0)` (:419) stores an explicit zero on EVERY diagonal cell and triu(A) keeps stored zeros, so every
+    # (c, c) is a candidate pair too (:427).  Its 2x2 block is [c, al] x [c, al]: straight = 0, cross = A[c,al] + A[al,c]
+    # after the allelic zeroing of the upper triangle -- the reference lists (c, c) as weak whenever c touches its allele.
+    pairs |= {(i, i) for i in range(A.shape[0])}
     weak = []
     for c1, c2 in sorted(pairs):
         if c1 not in grp or c2 not in grp:

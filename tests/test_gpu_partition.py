@@ -421,3 +421,26 @@ def test_irmm_against_reference_run(name, max_round):
         np.fill_diagonal(Ag, 0); np.fill_diagonal(Aref, 0)
         close = np.isclose(Ag, Aref, rtol=2e-5, atol=1e-9)
         assert (~close).sum() <= 40, (~close).sum()          # threshold ties of A_new (0.5 / 0.25 steps after damping)
+
+
+def test_kprune_against_reference_run():
+    """KPruneHyperGraph on the device against the lists of the REFERENCE's own KPruneHyperGraph.run()
+    (tests/golden/ref_kprune.npz), identical including the (c, c) entries of the weak list."""
+    import pandas as pd
+    from cphasing_b200 import kprune
+    from helpers import load_golden, csr_from
+    g = load_golden("kprune")
+    A = csr_from(g, "A")
+    n = A.shape[0]
+    names = [f"c{i}" for i in range(n)]
+    rows = [(0, 0, names[a], names[b], *m, 1) for (a, b), m in zip(g["allele_pairs"], g["allele_meta"])]
+    df = pd.DataFrame(rows, columns=[-1, 0, 1, 2, 3, 4, 5, 6, 7]).set_index(-1)
+
+    class AT:
+        data = df
+    kp = kprune.KPruneHyperGraph(AT(), A, {nm: i for i, nm in enumerate(names)})
+    kp.run()
+    assert kp.allelic_prune_list == [tuple(x) for x in g["allelic"]]
+    assert kp.weak_prune_list == [tuple(x) for x in g["weak"]]
+    pt = kp.get_prune_table()
+    assert len(pt) == len(g["allelic"]) + len(g["weak"])

@@ -121,3 +121,16 @@ def test_oracle_merge_and_recluster_match_reference():
     K4, moved = orc.recluster_by_linkage(Ar, K3, g["lengths"].astype(np.float32), 1.0)
     assert moved == int(g["recluster_count"][0]) and moved > 0
     assert _same_partition(K4, g["recluster_labels"])
+
+
+def test_kprune_oracle_matches_reference_run():
+    """oracle kprune_hypergraph against the lists of the REFERENCE's own KPruneHyperGraph.run() (tests/golden/
+    make_golden_kprune.py: the reference class with igraph's 2x2 matching answered by a stand-in)."""
+    g = load_golden("kprune")
+    A = csr_from(g, "A")
+    al, wk = orc.kprune_hypergraph(A, [tuple(x) for x in g["allele_pairs"]])
+    assert al == [tuple(x) for x in g["allelic"]]
+    assert wk == [tuple(x) for x in g["weak"]]
+    assert sum(1 for a, b in wk if a == b) > 100          # the (c, c) entries of the reference's weak list
+    grp = orc.allele_group_first([tuple(x) for x in g["allele_pairs"]])
+    assert sorted(grp.items()) == [tuple(x) for x in g["allele_group"]]
