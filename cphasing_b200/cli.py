@@ -1,0 +1,197 @@
+"""Command-line face of the drop-in for the three commands on the hot path (reference: cphasing/cli.py):
+
+    python -m cphasing_b200 hypergraph     <table[.gz]> <contigsizes> <out.hg> [--pairs] ...     (cli.py:3709-3941)
+    python -m cphasing_b200 hyperpartition <in.hg|table> <contigsizes> <out.clusters.txt> ...    (cli.py:3945-5360)
+    python -m cphasing_b200 kprune         <alleletable> <in.hg> <contigsizes> <out.prune.table> (cli.py:3525-3669)
+
+Same positional arguments, option names and defaults (cphasing/_config.py:30-55) for the options that belong to the
+accelerated path; the reference's other ~60 options steer stages that are out of scope (splitting, HCR, fasta alleles,
+plotting) and are not accepted here.  This is a thin argparse layer over HyperExtractor / Extractor / HyperPartition.
+"""
+from __future__ import annotations
+
+import argparse
+import logging
+import re
+import sys
+
+import msgspec
+import pandas as pd
+
+logger = logging.getLogger("cphasing_b200")
+
+MIN_CONTACTS, MIN_CIS_WEIGHT, MIN_WEIGHT = 25, 20, 2.0            # _config.py:43-45
+MIN_SCAFFOLD_LENGTH, MIN_LENGTH, MAX_ORDER = 2e6, 10_000, 50       # _config.py:38, 54-55
+
+
+def _size(s):
+    """'5m' / '500k' / '2e6' -> int (cli.py humanized sizes)."""
+    s = str(s).strip().lower()
+    mult = {"k": 1e3, "m": 1e6, "g": 1e9}.get(s[-1])
+    return int(float(s[:-1]) * mult) if mult else int(float(s))
+
+
+def read_contigsizes(path):
+    """two-column `contig<TAB>length` file -> DataFrame indexed by contig (utilities.read_chrom_sizes)."""
+    df = pd.read_csv(path, sep="\t", header=None, index_col=0, names=["contig", "length"], usecols=[0, 1], comment="#")
+    df.index = df.index.astype(str)
+    return df
+
+
+def load_hg(path):
+    from .algorithms.hypergraph import HyperEdges, numpy_dec_hook
+    with open(path, "rb") as fh:
+        e = msgspec.msgpack.decode(fh.read(), type=HyperEdges, dec_hook=numpy_dec_hook)
+    e.to_numpy()
+    return e
+
+
+def _extract(args, sizes):
+    from . import hypergraph as hg
+    idx = {c: i for i, c in enumerate(sizes.index)}
+    sz = sizes["length"].to_dict()
+    el = _size(args.edge_length) if args.edge_length else 0
+    if args.pairs:
+        return hg.Extractor([args.table], idx, sz, min_quality=args.min_quality, edge_length=el, threads=args.threads)
+    return hg.HyperExtractor([args.table], idx, sz, min_order=args.min_order, max_order=args.max_order,
+                             min_quality=args.min_quality, edge_length=el, threads=args.threads)
+
+
+def cmd_hypergraph(args):
+    sizes = read_contigsizes(args.contigsizes)
+    ex = _extract(args, sizes)
+    ex.save(args.output)
+    return 0
+
+
+def _allele_table(path):
+    from .kprune import allele_frame
+
+    class AT:
+        data = allele_frame(path)
+        filename = path
+    return AT()
+
+
+def cmd_hyperpartition(args):
+    from .hyperpartition import HyperPartition
+    sizes = read_contigsizes(args.contigsizes)
+    if args.porec or args.pairs:
+        args.table = args.hypergraph
+        edges = _extract(args, sizes).edges
+    else:
+        edges = load_hg(args.hypergraph)
+    n = [int(x) if x else 0 for x in re.split(r":|x|\|", args.n)] if args.n else None      # cli.py:4637
+    read_list = lambda p: [l.strip().split()[0] for l in open(p) if l.strip()] if p else None
+    at = _allele_table(args.alleletable) if args.alleletable else None
+    mode = args.mode
+    if mode is None:
+        mode = "phasing" if (n and len(n) > 1 and n[1] and n[1] > 1) else ("basal_withprune" if (at or args.prunetable)
+                                                                          else "basal")
+    if not n and args.resolution1 < 0:
+        args.resolution1 = args.init_resolution1          # no group number to search for: one clustering at the start value
+    hp = HyperPartition(edges, sizes, k=n, alleletable=at, prunetable=args.prunetable, normalize=args.normalize,
+                        allelic_factor=args.allelic_factor, cross_allelic_factor=args.cross_allelic_factor,
+                        allelic_similarity=args.allelic_similarity, min_allelic_overlap=args.min_allelic_overlap,
+                        disable_merge_in_first=args.disable_merge_in_first, whitelist=read_list(args.whitelist),
+                        blacklist=read_list(args.blacklist), min_contacts=args.min_contacts,
+                        min_length=_size(args.min_length), resolution1=args.resolution1, resolution2=args.resolution2,
+                        init_resolution1=args.init_resolution1, init_resolution2=args.init_resolution2,
+                        min_weight=args.min_weight, min_cis_weight=args.min_cis_weight,
+                        cluster_method=args.cluster_method, min_quality1=args.min_quality1,
+                        min_quality2=args.min_quality2, min_scaffold_length=_size(args.min_scaffold_length),
+                        threshold=args.threshold, max_round=args.max_round, threads=args.threads)
+    if mode == "phasing":                                                                   # cli.py:5334-5346
+        first = None
+        if args.first_cluster:
+            first = [l.rstrip("\n").split("\t")[2].split(" ") for l in open(args.first_cluster) if l.strip()]
+        hp.incremental_partition(n, first_cluster=first)
+    else:                                                                                    # cli.py:5347-5352
+        hp.single_partition(k=n[0] if n else None, is_kprune=(mode == "basal_withprune" and at is not None))
+    hp.to_cluster(args.output)
+    return 0
+
+
+def cmd_kprune(args):
+    from .algorithms.hypergraph import HyperGraph
+    from .kprune import KPruneHyperGraph
+    sizes = read_contigsizes(args.contigsizes)
+    edges = load_hg(args.hypergraph)
+    HG = HyperGraph(edges, min_quality=args.min_quality, mapq_filter=False)
+    H = HG.incidence_matrix(args.min_contacts)
+    A = HyperGraph.clique_expansion_init(H, min_weight=args.min_weight, use_high_order=False)    # hyperpartition.py:1566
+    kp = KPruneHyperGraph(_allele_table(args.alleletable), A, {c: i for i, c in enumerate(HG.nodes)})
+    kp.run()
+    kp.get_prune_table().to_csv(args.output, sep="\t", header=None, index=None)              # core.py:711-723
+    logger.info(f"Wrote {len(kp.allelic_prune_list)} allelic and {len(kp.weak_prune_list)} cross-allelic pairs "
+                f"to `{args.output}`.")
+    return 0
+
+
+def build_parser():
+    ap = argparse.ArgumentParser(prog="cphasing_b200", description=__doc__.split("\n\n")[0])
+    sub = ap.add_subparsers(dest="command", required=True)
+
+    def extract_opts(p):
+        p.add_argument("-prs", "--pairs", action="store_true", help="input is a 4DN pairs file")
+        p.add_argument("-pct", "--porec", action="store_true", help="input is a Pore-C table (default for `hypergraph`)")
+        p.add_argument("-e", "--edge-length", default="5m")
+        p.add_argument("--min-order", type=int, default=2)
+        p.add_argument("--max-order", type=int, default=MAX_ORDER)
+        p.add_argument("-q", "--min-quality", type=int, default=1)
+        p.add_argument("-t", "--threads", type=int, default=4)
+
+    g = sub.add_parser("hypergraph", aliases=["hg"])
+    g.add_argument("table"); g.add_argument("contigsizes"); g.add_argument("output")
+    extract_opts(g)
+    g.set_defaults(fn=cmd_hypergraph)
+
+    h = sub.add_parser("hyperpartition", aliases=["hp"])
+    h.add_argument("hypergraph"); h.add_argument("contigsizes"); h.add_argument("output")
+    extract_opts(h)
+    h.add_argument("--mode", choices=["basal", "haploid", "phasing", "basal_withprune"], default=None)
+    h.add_argument("-n", default=None, help="group numbers, e.g. 12 or 12:4")
+    h.add_argument("-at", "--alleletable", default=None)
+    h.add_argument("-pt", "--prunetable", default=None)
+    h.add_argument("-norm", "--normalize", action="store_true")
+    h.add_argument("-af", "--allelic-factor", type=float, default=0)
+    h.add_argument("-caf", "--cross-allelic-factor", type=float, default=0)
+    h.add_argument("-as", "--allelic-similarity", type=float, default=0.85)
+    h.add_argument("-mao", "--min-allelic-overlap", type=float, default=0.3)
+    h.add_argument("-fc", "--first-cluster", default=None)
+    h.add_argument("--disable-merge-in-first", action="store_true")
+    h.add_argument("-wl", "--whitelist", default=None)
+    h.add_argument("-bl", "--blacklist", default=None)
+    h.add_argument("-mc", "--min-contacts", type=int, default=MIN_CONTACTS)
+    h.add_argument("-ml", "--min-length", default=str(MIN_LENGTH))
+    h.add_argument("-r1", "--resolution1", type=float, default=-1.0)
+    h.add_argument("-r2", "--resolution2", type=float, default=-1.0)
+    h.add_argument("-ir1", "--init-resolution1", type=float, default=1.0)
+    h.add_argument("-ir2", "--init-resolution2", type=float, default=1.0)
+    h.add_argument("-mw", "--min-weight", type=float, default=MIN_WEIGHT)
+    h.add_argument("-mcw", "--min-cis-weight", type=float, default=MIN_CIS_WEIGHT)
+    h.add_argument("-q1", "--min-quality1", type=int, default=1)
+    h.add_argument("-q2", "--min-quality2", type=int, default=1)
+    h.add_argument("-ms", "--min-scaffold-length", default=str(MIN_SCAFFOLD_LENGTH))
+    h.add_argument("--cluster-method", choices=["louvain", "leiden"], default="louvain")
+    h.add_argument("--threshold", type=float, default=0.01)
+    h.add_argument("--max-round", type=int, default=1)
+    h.set_defaults(fn=cmd_hyperpartition)
+
+    k = sub.add_parser("kprune")
+    k.add_argument("alleletable"); k.add_argument("hypergraph"); k.add_argument("contigsizes"); k.add_argument("output")
+    k.add_argument("-mc", "--min-contacts", type=int, default=MIN_CONTACTS)
+    k.add_argument("-mw", "--min-weight", type=float, default=1.0)
+    k.add_argument("-q", "--min-quality", type=int, default=1)
+    k.set_defaults(fn=cmd_kprune)
+    return ap
+
+
+def main(argv=None):
+    logging.basicConfig(level=logging.INFO, format="%(asctime)s %(name)s %(levelname)s %(message)s", stream=sys.stderr)
+    args = build_parser().parse_args(argv)
+    return args.fn(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

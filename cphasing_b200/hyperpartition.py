@@ -758,12 +758,25 @@ class HyperPartition:
             self.K = [sorted(int(x) for x in g) for g in new_K]
         return count
 
-    # -- hyperpartition.py:4238-4296 (first-round / basal output: `ChrNN\t<count>\t<contigs>`)
+    # -- hyperpartition.py:4238-4296: `ChrNN\t<count>\t<contigs>` after one round, `ChrNNgH` after the second round
     def to_cluster(self, output, merge=True):
         itv = self.idx_to_vertices
         clusters = [[itv[x] for x in grp] for grp in self.K]
-        clusters = [c for c in clusters if c]
+        inc = getattr(self, "inc_chr_idx", None)
         with open(output, 'w') as out:
-            for i, group in enumerate(clusters, 1):
-                print(f'Chr{i:0>2}\t{len(group)}\t{" ".join(group)}', file=out)
+            if inc is not None:
+                n = min(len(inc), len(clusters))
+                tail = [c for c in clusters[n:] if c]
+                pairs = [(c, i) for c, i in zip(clusters[:n], inc[:n]) if c]
+                hap = defaultdict(lambda: 1)
+                last = 0
+                for group, chr_idx in pairs:
+                    print(f'Chr{chr_idx + 1:0>2}g{hap[chr_idx]}\t{len(group)}\t{" ".join(group)}', file=out)
+                    hap[chr_idx] += 1
+                    last = chr_idx + 1
+                for i, group in enumerate(tail):
+                    print(f'Chr{i + 1 + last:0>2}\t{len(group)}\t{" ".join(group)}', file=out)
+            else:
+                for i, group in enumerate([c for c in clusters if c], 1):
+                    print(f'Chr{i:0>2}\t{len(group)}\t{" ".join(group)}', file=out)
         logger.info(f"Successful output hyperpartition results in `{output}`.")

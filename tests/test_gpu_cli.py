@@ -1,0 +1,63 @@
+"""The command-line face (cphasing_b200/cli.py; reference cli.py:3525-5360) end to end on files: Pore-C table (TSV.gz) ->
+`hypergraph` -> .hg (the reference's msgpack layout) -> `hyperpartition -n 5:4 -at ...` -> clusters file, and `kprune`."""
+import gzip
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import community_oracle as co
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def run(*args):
+    r = subprocess.run([sys.executable, "-m", "cphasing_b200", *args], cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return r
+
+
+def test_cli_files_end_to_end(tmp_path):
+    from cphasing_b200 import synth
+    g = synth.make_genome(400, 5, 4, seed=20240)
+    t = synth.porec_table(g, 120_000, seed=20240)
+    names = np.array(g.names)
+    table = tmp_path / "reads.porec.gz"
+    with gzip.open(table, "wt") as fh:      # the 11 columns of a Pore-C table; the path reads 0, 5, 6, 7, 8 (hypergraph.py:1706-1717)
+        for r, c, s, e, q in zip(t["read_idx"], t["contig_idx"], t["start"], t["end"], t["mapq"]):
+            fh.write(f"{r}\t100\t0\t90\t+\t{names[c]}\t{s}\t{e}\t{q}\t0.9\tread{r}\n")
+    sizes = tmp_path / "contigs.sizes"
+    sizes.write_text("".join(f"{n}\t{l}\n" for n, l in zip(g.names, g.length)))
+    at = tmp_path / "allele.table"
+    with open(at, "w") as fh:
+        for i, (a, b, m1, m2, sh, sim) in enumerate(synth.allele_pairs(g, seed=3)):
+            fh.write(f"{i}\t{i}\t{names[a]}\t{names[b]}\t{m1}\t{m2}\t{sh}\t{sim:.4f}\t1\n")
+    hgf = tmp_path / "reads.hg"
+    run("hypergraph", str(table), str(sizes), str(hgf), "-e", "0")
+    assert hgf.stat().st_size > 100_000
+    out = tmp_path / "out.clusters.txt"
+    run("hyperpartition", str(hgf), str(sizes), str(out), "-n", "5:4", "-at", str(at), "-ir1", "0.8", "-ir2", "0.8")
+    lines = out.read_text().strip().split("\n")
+    assert len(lines) == 20
+    assert [l.split("\t")[0] for l in lines[:5]] == ["Chr01g1", "Chr01g2", "Chr01g3", "Chr01g4", "Chr02g1"]
+    truth = {n: int(x) for n, x in zip(g.names, g.group)}
+    lab, tru = [], []
+    for i, l in enumerate(lines):
+        f = l.split("\t")
+        members = f[2].split(" ")
+        assert int(f[1]) == len(members)
+        lab += [i] * len(members); tru += [truth[m] for m in members]
+    assert len(lab) > 0.95 * g.n and co.ari(lab, tru) >= 0.99
+    # one round straight from the table, no .hg in between (cli.py --porec)
+    out1 = tmp_path / "basal.clusters.txt"
+    run("hyperpartition", str(table), str(sizes), str(out1), "--porec", "-e", "0", "-n", "20")
+    l1 = out1.read_text().strip().split("\n")
+    assert len(l1) == 20 and l1[0].startswith("Chr01\t")
+    # kprune: 7-column prune table (core.py:711-723)
+    pt = tmp_path / "prune.table"
+    run("kprune", str(at), str(hgf), str(sizes), str(pt))
+    rows = [l.split("\t") for l in pt.read_text().strip().split("\n")]
+    assert all(len(r) == 7 for r in rows) and {r[6] for r in rows} == {"0", "1"}
