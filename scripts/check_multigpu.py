@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Multi-GPU parity check, run under torchrun with one rank per GPU:
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 scripts/check_multigpu.py
+
+Every rank generates its concatemer-column shard of one synthetic Pore-C table, runs stage 1 + the sharded expansion
+(row-sum all-reduce, triangle reduce-scatter + all-gather over NCCL) and rank 0 compares the result with the
+single-GPU run over the whole table: the integer contact-count matrix must be BIT-EXACT, the weighted A equal to
+1e-9 relative (fixed-point sums are order-free, so they are in fact identical), H shards must tile the global H.
+Prints one JSON line on rank 0 and exits non-zero on any mismatch."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device(f"cuda:{local}")
+    dist.init_process_group("nccl", device_id=dev)
+    from cphasing_b200 import device as D, parallel as par, synth
+    n, m = 3000, 4_000_000
+    g = synth.make_genome(n, 10, 4, seed=77)
+    first, count = par.shard_range(m, rank, world)
+    t = synth.porec_table_device(g, count, 78, law="poisson", first=first, device=dev)
+    raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=1)
+    out = {"world": world, "n": n, "m": m}
+    ok = True
+    for use_high_order, mw in ((False, 0.0), (True, 2.0)):
+        H, A = par.sharded_clique_expansion(raw, min_contacts=25, min_weight=mw, use_high_order=use_high_order)
+        nnz_h = torch.tensor([H.nnz], dtype=torch.int64, device=dev)
+        dist.all_reduce(nnz_h)
+        if rank == 0:
+            tf = synth.porec_table_device(g, m, 78, law="poisson", first=0, device=dev)
+            rawf = D.porec_to_edges(tf["read_idx"], tf["contig_idx"], tf["mapq"], g.n, min_mapq=1)
+            Hf = D.incidence(rawf, min_contacts=25, min_mapq=0)
+            Af, _ = D.clique_expansion(Hf, use_high_order=use_high_order, min_weight=mw)
+            same_pattern = bool(torch.equal(A.indptr, Af.indptr) and torch.equal(A.indices, Af.indices))
+            if use_high_order:
+                close = same_pattern and bool(torch.allclose(A.data64, Af.data64, rtol=1e-9, atol=0))
+                exact = same_pattern and bool(torch.equal(A.data64, Af.data64))
+                out["weighted"] = {"same_pattern": same_pattern, "rtol_1e-9": close, "bit_identical": exact,
+                                   "nnz_A": int(Af.nnz)}
+                ok &= close
+            else:
+                exact = same_pattern and bool(torch.equal(A.data64, Af.data64))
+                out["contact_counts"] = {"bit_exact": exact, "nnz_A": int(Af.nnz),
+                                         "sum": float(Af.data64.sum().item())}
+                ok &= exact
+            out["H_shards_tile_global_H"] = bool(int(nnz_h.item()) == Hf.nnz)
+            ok &= out["H_shards_tile_global_H"]
+            del tf, rawf, Hf, Af
+        dist.barrier()
+    if rank == 0:
+        out["ok"] = bool(ok)
+        print(json.dumps(out), flush=True)
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.broadcast(flag, 0)
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) else 1)
+
+
+if __name__ == "__main__":
+    main()
