@@ -156,7 +156,7 @@ def device_step(D, cfg, g, t, ev, world, rank):
     return raw, H, A
 
 
-def partition_tail(D, cfg, g, H, A, reps=3):
+def partition_tail(D, cfg, g, H, A, reps=3, world=1, rank=0):
     """the rest of `hyperpartition` on the device-resident H / A of the last step: unweighted expansion -> kprune
     (allelic + cross-allelic pairs from the synthetic allele table) -> pair re-weighting -> Louvain at resolution 1.
     Wall-clock (synchronised) per stage, best of `reps`; ARI of the clustering against the planted haplotype groups."""
@@ -172,7 +172,17 @@ def partition_tail(D, cfg, g, H, A, reps=3):
     for _ in range(reps):
         tm = {}
         torch.cuda.synchronize(); t0 = time.perf_counter()
-        Au, _ = D.clique_expansion(H, use_high_order=False, min_weight=1.0, want32=False, want64=True)
+        if world > 1:       # H is this rank's column shard: the unweighted counts need the same exchange as A
+            from cphasing_b200 import parallel as par
+            accu = D.expand_accumulate(H, use_high_order=False)
+            par.sum_triangle(accu.acc, accu.n)
+            par.sum_vector(accu.diag)
+            Au = D.expand_emit(accu, min_weight=1.0, want32=False, want64=True)
+            del accu
+            if rank != 0:   # kprune and the clustering run on one GPU (latency-bound at n <= 2e4)
+                continue
+        else:
+            Au, _ = D.clique_expansion(H, use_high_order=False, min_weight=1.0, want32=False, want64=True)
         flag, row_of = kprune.kprune_device(Au, pairs, 1)
         al = torch.nonzero(flag == 1).flatten(); wk = torch.nonzero(flag == 2).flatten()
         Pa = (torch.cat([row_of[al], Au.indices[al]]), torch.cat([Au.indices[al], row_of[al]]))     # symmetrised, on device
@@ -193,6 +203,8 @@ def partition_tail(D, cfg, g, H, A, reps=3):
             best[k_] = min(best.get(k_, v), v)
         out = {"allelic_pairs": int(al.numel()), "weak_pairs": int(wk.numel()), "groups": st["groups"], "planted_groups": G,
                "modularity": q, "resolution": round(gamma, 2), "clusterings": rounds, "cluster_ms_each": tm["cluster_ms"] / rounds}
+    if rank != 0:
+        return None
     from oracle import community_oracle as co          # checker only: ARI against the planted groups
     truth = g.group[keep]
     out["ari_vs_planted"] = float(co.ari(mem.cpu().numpy(), truth))
@@ -355,8 +367,10 @@ def run_own(args):
                       "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
                       "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
            "stages_ms": stages, "roofline": roof, "clocks": clk}
-    if rank == 0 and world == 1 and not args.no_partition:
-        tail = partition_tail(D, cfg, g, H, A)
+    if not args.no_partition:
+        tail = partition_tail(D, cfg, g, H, A, world=world, rank=rank)
+        barrier()
+    if rank == 0 and not args.no_partition:
         tail["wall_s"] = (ms_step + tail["kprune_ms"] + tail["cluster_ms"]) / 1e3
         tail["what"] = ("table -> H -> A (ms_per_step) + unweighted expansion + kprune + pair re-weighting + Louvain "
                         "inside the resolution auto-search (1.0, +0.2 until >= planted groups), device-resident")
