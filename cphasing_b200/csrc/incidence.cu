@@ -25,25 +25,26 @@ __device__ __forceinline__ bool entry_ok(const int8_t* mapq, int min_mapq, size_
 }
 
 // per-contig sum of counts; shared-memory privatised histogram, one flush per CTA
-__global__ void __launch_bounds__(TPB) row_sums_kernel(const u32* __restrict__ rem_row, const u32* __restrict__ rem_count,
+__global__ void __launch_bounds__(1024) row_sums_kernel(const u32* __restrict__ rem_row, const u32* __restrict__ rem_count,
                                                        const int8_t* __restrict__ rem_mapq, u64 nnz, u32 n, int min_mapq,
-                                                       const u8* __restrict__ row_drop, u32 cmask, int use_smem,
-                                                       unsigned long long* __restrict__ rowsum, u32* __restrict__ max_count) {
+                                                       const u8* __restrict__ row_drop, u32 cmask, int use_smem, u32 chunk,
+                                                       u32 bin_limit, unsigned long long* __restrict__ rowsum,
+                                                       u32* __restrict__ max_count) {
     extern __shared__ u32 bins[];
     if (use_smem) {
-        for (u32 i = threadIdx.x; i < n; i += TPB) bins[i] = 0;
+        for (u32 i = threadIdx.x; i < n; i += blockDim.x) bins[i] = 0;
         __syncthreads();
     }
-    const size_t lo = (size_t)blockIdx.x * RS_CHUNK;
-    const size_t hi = min((size_t)nnz, lo + RS_CHUNK);
+    const size_t lo = (size_t)blockIdx.x * chunk;
+    const size_t hi = min((size_t)nnz, lo + chunk);
     u32 mx = 0;
-    for (size_t t = lo + threadIdx.x; t < hi; t += TPB) {
+    for (size_t t = lo + threadIdx.x; t < hi; t += blockDim.x) {
         if (!entry_ok(rem_mapq, min_mapq, t)) continue;
         u32 r = rem_row[t] & CPH_ROWM;
         if (r >= n || (row_drop && row_drop[r])) continue;
         u32 c = rem_count[t] & cmask;
         mx = max(mx, c);
-        if (use_smem && c < 65536u) atomicAdd(&bins[r], c);
+        if (use_smem && c < bin_limit) atomicAdd(&bins[r], c);       // chunk * bin_limit < 2^32: a bin cannot overflow
         else atomicAdd(&rowsum[r], (unsigned long long)c);
     }
     if (max_count) {
@@ -53,7 +54,7 @@ __global__ void __launch_bounds__(TPB) row_sums_kernel(const u32* __restrict__ r
     }
     if (use_smem) {
         __syncthreads();
-        for (u32 i = threadIdx.x; i < n; i += TPB) {
+        for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
             u32 v = bins[i];
             if (v) atomicAdd(&rowsum[i], (unsigned long long)v);
         }
@@ -538,9 +539,13 @@ extern "C" int cph_row_sums(const u32* rem_row, const u32* rem_count, const int8
     const int use_smem = n_contigs <= RS_MAX_SMEM_BINS;
     const size_t smem = use_smem ? (size_t)n_contigs * sizeof(u32) : 0;
     if (smem > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(row_sums_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    row_sums_kernel<<<grid_for(nnz, RS_CHUNK), TPB, smem, st>>>(rem_row, rem_count, rem_mapq, nnz, n_contigs, min_mapq, row_drop,
-                                                               packed ? CPH_CNTM : 0xffffffffu, use_smem,
-                                                               (unsigned long long*)rowsum, max_count);
+    // many bins: a CTA must see enough entries to pay for flushing n bins (8 x larger chunks, 4 x smaller bin limit)
+    const u32 chunk = n_contigs > 8192 ? RS_CHUNK * 8 : RS_CHUNK;
+    const u32 bin_limit = n_contigs > 8192 ? 16384u : 65536u;
+    const int rs_threads = n_contigs > 8192 ? 1024 : TPB;      // 80+ KB of bins per CTA: fill the SM with two big CTAs
+    row_sums_kernel<<<grid_for(nnz, chunk), rs_threads, smem, st>>>(rem_row, rem_count, rem_mapq, nnz, n_contigs, min_mapq, row_drop,
+                                                            packed ? CPH_CNTM : 0xffffffffu, use_smem, chunk, bin_limit,
+                                                            (unsigned long long*)rowsum, max_count);
     KERNEL_CHECK();
     return CPH_OK;
 }
