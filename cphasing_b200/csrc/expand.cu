@@ -13,6 +13,7 @@
 //
 // Roofline: HBM.  Algorithmic bytes per call: 8 nnz(H) read + 12 nnz(A) + 16 (n+1) written
 // (SURVEY.md 8d); the work figure is sum_e k_e (k_e - 1) / 2 REDs.
+#include <cstdlib>
 #include "common.cuh"
 
 namespace {
@@ -57,10 +58,10 @@ __global__ void __launch_bounds__(TPB) diag_kernel(const i64* __restrict__ indpt
     u64 s = 0;
     for (i64 t = indptr[row] + lane, e = indptr[row + 1]; t < e; t += 32) {
         u32 p = pk[t];
-        double c = (double)(p & CPH_CNTM);
+        u64 c = p & CPH_CNTM;
         double sc = scale[use_high_order ? (p >> 24) : 1u];
         if (ew) sc *= (double)ew[t];
-        s += __double2ull_rn((c * sc) * c);
+        s += __double2ull_rn((double)(c * c) * sc);
     }
     s = warp_sum(s);
     if (lane == 0) diag[row] = s;
@@ -83,11 +84,11 @@ __global__ void __launch_bounds__(TPB) expand_kernel(const u32* __restrict__ pem
         const u64 i = pem_row[a] & CPH_ROWM;
         double sc = scale[use_high_order ? (pa >> 24) : 1u];
         if (ew) sc *= (double)ew[a];
-        const double fa = (double)(pa & CPH_CNTM) * sc;
+        const u64 ca = pa & CPH_CNTM;
         for (;;) {
             const u64 j = rb & CPH_ROWM;
-            const double cb = (double)(pem_pk[b] & CPH_CNTM);
-            unsigned long long v = __double2ull_rn(fa * cb);
+            const u64 cb = pem_pk[b] & CPH_CNTM;
+            unsigned long long v = __double2ull_rn((double)(ca * cb) * sc);
             u64 lo = i < j ? i : j, hi = i < j ? j : i;
             if (i == j) v += v;   // duplicated (row, col): both orders land on the diagonal
             atomicAdd(&acc[tri_index(lo, hi, n)], v);
@@ -139,16 +140,16 @@ __global__ void __launch_bounds__(XT, 3) expand_diag_kernel(const u32* __restric
         const u32 i = ra & CPH_ROWM;
         double sc = scale[use_high_order ? (pa >> 24) : 1u];
         if (ew) sc *= (double)wa;
-        const double ca = (double)(pa & CPH_CNTM);
-        const double fa = ca * sc;
-        const unsigned long long dv = __double2ull_rn(fa * ca);
+        const u64 ca = pa & CPH_CNTM;
+        // integer product first (exact, < 2^48), then ONE rounding: every kernel that forms a term does it this way
+        const unsigned long long dv = __double2ull_rn((double)(ca * ca) * sc);
         if (SMEM_DIAG) atomicAdd(&xbins[i], dv);
         else atomicAdd(&diag[i], dv);
         size_t b = a + 1;
         while (!(rb & CPH_HEAD)) {
             const u32 j = rb & CPH_ROWM;
-            const double cb = (double)(pem_pk[b] & CPH_CNTM);
-            unsigned long long v = __double2ull_rn(fa * cb);
+            const u64 cb = pem_pk[b] & CPH_CNTM;
+            unsigned long long v = __double2ull_rn((double)(ca * cb) * sc);
             const u32 lo = i < j ? i : j, hi = i < j ? j : i;
             if (i == j) v += v;   // duplicated (row, col): both orders land on the diagonal
             if (IDX32) atomicAdd(&acc[(lo * (two_n1 - lo)) / 2u + (hi - lo)], v);
@@ -169,6 +170,126 @@ __global__ void __launch_bounds__(XT, 3) expand_diag_kernel(const u32* __restric
             if (v) atomicAdd(&diag[i], v);
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Binned expansion for accumulators that do not fit in L2 (n > ~5.6k; config D: n = 20k, 1.6 GB triangle).
+// A RED into an HBM-resident accumulator is a random 32-byte read-modify-write in DRAM.  Here the pairs are first
+// written out grouped by accumulator BLOCK (contig-block pair (I, J), Bs x Bs cells <= 48 MB), then applied block after
+// block, so that while one block is being updated its cells stay in L2.  The accumulator layout does not change -- only
+// the order of the (order-free, exact) integer additions does, so the result is bit-identical to the direct kernel.
+//   bin_count_kernel : CTA per chunk of XB_CHUNK entries; pairs per block -> cnt[bin * grid + cta]; diagonal terms
+//   (scan of cnt: exclusive offsets, bin-major, so every CTA knows where its records of every bin go -- no global atomics)
+//   bin_fill_kernel  : same enumeration, writes one 8-byte record per pair
+//   bin_apply_kernel : streams the records bin by bin, one RED each
+// record = [63:41] cell index inside the block (li * Bs + lj) | [40:34] D_e | [33:0] c_a * c_b ; pairs whose count product
+// needs more than 34 bits are added directly.  Scratch: 8 B per pair.
+// ------------------------------------------------------------------------------------------------
+constexpr int XB_T = 256;
+constexpr u32 XB_CHUNK = 8192;
+constexpr u32 XB_BS_MAX = 2508;           // 2508^2 x 8 B = 50 MB; the record's cell field (23 bits) allows 2896
+constexpr u32 XB_MAXNB = 46;              // n <= 115368 at the default block size
+constexpr int XB_MAXBINS = XB_MAXNB * (XB_MAXNB + 1) / 2;   // 1081
+constexpr u64 XB_PROD_MAX = (1ull << 34) - 1;
+
+struct BinGeom {
+    u32 n, bs, nb, nbins;
+};
+__device__ __forceinline__ u32 bin_of(const BinGeom& g, u32 I, u32 J) { return I * (2u * g.nb - I + 1u) / 2u + (J - I); }   // I <= J
+
+// enumerate the pairs owned by the entries [lo, hi) of this CTA: f(i, j, ca, cb, D) with i = row of the owning entry
+template <class F>
+__device__ __forceinline__ void xb_for_pairs(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz, size_t lo,
+                                             size_t hi, F f) {
+    for (size_t a = lo + threadIdx.x; a < hi; a += XB_T) {
+        size_t b = a + 1;
+        if (b >= nnz) break;
+        u32 rb = pem_row[b];
+        if (rb & CPH_HEAD) continue;
+        const u32 pa = pem_pk[a];
+        const u32 i = pem_row[a] & CPH_ROWM;
+        for (;;) {
+            f(i, rb & CPH_ROWM, (u64)(pa & CPH_CNTM), (u64)(pem_pk[b] & CPH_CNTM), pa >> 24);
+            if (++b >= nnz) break;
+            rb = pem_row[b];
+            if (rb & CPH_HEAD) break;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(XB_T) bin_count_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
+                                                         BinGeom g, int use_high_order, int frac_bits, u64* __restrict__ cnt,
+                                                         unsigned long long* __restrict__ diag) {
+    __shared__ u32 c[XB_MAXBINS];
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    for (int k = threadIdx.x; k < XB_MAXBINS; k += XB_T) c[k] = 0;
+    __syncthreads();
+    const size_t lo = (size_t)blockIdx.x * XB_CHUNK, hi = min((size_t)nnz, lo + XB_CHUNK);
+    for (size_t a = lo + threadIdx.x; a < hi; a += XB_T) {       // diagonal terms (global REDs: n is large here)
+        const u32 pa = pem_pk[a];
+        const u64 ca = pa & CPH_CNTM;
+        atomicAdd(&diag[pem_row[a] & CPH_ROWM], __double2ull_rn((double)(ca * ca) * scale[use_high_order ? (pa >> 24) : 1u]));
+    }
+    xb_for_pairs(pem_row, pem_pk, nnz, lo, hi, [&](u32 i, u32 j, u64 ca, u64 cb, u32) {
+        if (ca * cb > XB_PROD_MAX) return;
+        const u32 l = i < j ? i : j, h = i < j ? j : i;
+        atomicAdd(&c[bin_of(g, l / g.bs, h / g.bs)], 1u);
+    });
+    __syncthreads();
+    for (u32 k = threadIdx.x; k < g.nbins; k += XB_T) cnt[(size_t)k * gridDim.x + blockIdx.x] = c[k];
+}
+
+__global__ void __launch_bounds__(XB_T) bin_fill_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
+                                                        BinGeom g, int use_high_order, int frac_bits, const u64* __restrict__ off,
+                                                        u64* __restrict__ rec, unsigned long long* __restrict__ acc) {
+    __shared__ u32 c[XB_MAXBINS];
+    __shared__ u64 base[XB_MAXBINS];
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    for (u32 k = threadIdx.x; k < XB_MAXBINS; k += XB_T) {
+        c[k] = 0;
+        base[k] = k < g.nbins ? off[(size_t)k * gridDim.x + blockIdx.x] : 0;
+    }
+    __syncthreads();
+    const size_t lo = (size_t)blockIdx.x * XB_CHUNK, hi = min((size_t)nnz, lo + XB_CHUNK);
+    xb_for_pairs(pem_row, pem_pk, nnz, lo, hi, [&](u32 i, u32 j, u64 ca, u64 cb, u32 D) {
+        const u32 l = i < j ? i : j, h = i < j ? j : i;
+        const u64 prod = ca * cb;
+        if (!use_high_order) D = 1;
+        if (prod > XB_PROD_MAX) {       // does not fit the record: straight to the accumulator
+            unsigned long long v = __double2ull_rn((double)prod * scale[D]);
+            if (i == j) v += v;
+            atomicAdd(&acc[tri_index(l, h, g.n)], v);
+            return;
+        }
+        const u32 I = l / g.bs, J = h / g.bs;
+        const u32 k = bin_of(g, I, J);
+        const u64 cell = (u64)(l - I * g.bs) * g.bs + (h - J * g.bs);
+        __stcs(&rec[base[k] + atomicAdd(&c[k], 1u)], (cell << 41) | ((u64)D << 34) | prod);    // streaming: keep L2 for acc
+    });
+}
+
+__global__ void __launch_bounds__(XB_T) bin_apply_kernel(const u64* __restrict__ rec, const u64* __restrict__ off, u32 grid_fill,
+                                                         BinGeom g, int frac_bits, unsigned long long* __restrict__ acc) {
+    __shared__ double scale[128];
+    fill_scale(scale, frac_bits);
+    __syncthreads();
+    const size_t stride = (size_t)gridDim.x * XB_T;
+    u32 k = 0;
+    for (u32 I = 0; I < g.nb; ++I)
+        for (u32 J = I; J < g.nb; ++J, ++k) {
+            const u64 beg = off[(size_t)k * grid_fill], end = off[(size_t)(k + 1) * grid_fill];   // off has nbins*grid + 1 entries
+            for (u64 p = beg + gtid(); p < end; p += stride) {
+                const u64 r = __ldcs(&rec[p]);          // evict-first: the block being updated must stay in L2
+                const u64 cell = r >> 41;
+                const u32 li = (u32)(cell / g.bs), lj = (u32)(cell % g.bs);
+                unsigned long long v = __double2ull_rn((double)(r & XB_PROD_MAX) * scale[(r >> 34) & 127u]);
+                const u64 i = (u64)I * g.bs + li, j = (u64)J * g.bs + lj;
+                if (i == j) v += v;
+                atomicAdd(&acc[tri_index(i, j, g.n)], v);
+            }
+        }
 }
 
 struct Epi {
@@ -330,6 +451,65 @@ extern "C" int cph_expand_accumulate_diag(const u32* pem_row, const u32* pem_pk,
     else XLAUNCH(false, false);
 #undef XLAUNCH
     KERNEL_CHECK();
+    return CPH_OK;
+}
+
+extern "C" int cph_expand_accumulate_binned(int phase, const u32* pem_row, const u32* pem_pk, u64 nnz, u32 n, int use_high_order,
+                                            int frac_bits, int zero_first, u64* acc, u64* diag_fx, u64* pair_records,
+                                            u64* h_pairs, void* ws, size_t ws_bytes, size_t* h_ws_need, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(n > 0);
+    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
+    // blocks of at most 50 MB (bs x bs u64 cells).  Measured on the workload-D shard (n = 20k, 371 M pairs; scripts/
+    // diag_binned.py): block size 600 / 887 / 1774 / 2508 -> fill 7.9 / 7.7 / 6.7 / 5.0 ms, apply 6.0 / 6.5 / 5.3 / 5.4 ms:
+    // smaller blocks do not make the apply pass faster (it is bound by the rate of scattered 64-bit REDs, ~70 G/s, not
+    // by DRAM) and make the fill pass slower (more write streams per CTA).
+    u32 bs_max = XB_BS_MAX;
+    if (const char* e = getenv("CPH_XB_BS")) {          // tuning knob for scripts/diag_binned.py
+        const long v = atol(e);
+        if (v >= 64 && v <= 65536) bs_max = (u32)v;
+    }
+    u32 nb = (u32)ceil_div((size_t)n, (size_t)bs_max);
+    ARG_CHECK(nb <= XB_MAXNB);
+    BinGeom g{n, (u32)ceil_div((size_t)n, (size_t)nb), nb, nb * (nb + 1) / 2};
+    const unsigned grid = grid_for(nnz, XB_CHUNK);
+    WS_BEGIN(ar);
+    const size_t cells = (size_t)g.nbins * grid + 1;
+    u64* cnt = ar.take<u64>(cells);
+    u64* total = ar.take<u64>(1);
+    if (!ar.dry && phase == 1) {
+        ARENA_CHECK(ar);
+        ARG_CHECK(acc && diag_fx && h_pairs && (nnz == 0 || (pem_row && pem_pk)));
+        const size_t tri = (size_t)n * ((size_t)n + 1) / 2;
+        if (zero_first) CUDA_TRY(cudaMemsetAsync(acc, 0, tri * sizeof(u64), st));
+        CUDA_TRY(cudaMemsetAsync(diag_fx, 0, (size_t)n * sizeof(u64), st));
+        CUDA_TRY(cudaMemsetAsync(cnt, 0, cells * sizeof(u64), st));
+        if (nnz > 0) {
+            bin_count_kernel<<<grid, XB_T, 0, st>>>(pem_row, pem_pk, nnz, g, use_high_order, frac_bits, cnt,
+                                                    (unsigned long long*)diag_fx);
+            KERNEL_CHECK();
+        }
+    }
+    // (the scan carves its scratch in every mode so that both phases see the same workspace layout)
+    if (ar.dry || phase == 1) TRY(scan_u64(cnt, cells, total, ar, st));
+    WS_QUERY_RETURN(ar);
+    if (phase == 1) {       // phase 1 ends here: the caller sizes pair_records from *h_pairs and comes back with phase 2
+        CUDA_TRY(cudaMemcpyAsync(h_pairs, total, sizeof(u64), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaStreamSynchronize(st));
+        return CPH_OK;
+    }
+    ARG_CHECK(phase >= 2 && phase <= 4 && acc);          // 3 / 4: fill only / apply only (timing the two halves apart)
+    if (nnz == 0) return CPH_OK;
+    ARG_CHECK(pem_row && pem_pk && pair_records);
+    if (phase != 4) {
+        bin_fill_kernel<<<grid, XB_T, 0, st>>>(pem_row, pem_pk, nnz, g, use_high_order, frac_bits, cnt, pair_records,
+                                               (unsigned long long*)acc);
+        KERNEL_CHECK();
+    }
+    if (phase != 3) {
+        bin_apply_kernel<<<148 * 8, XB_T, 0, st>>>(pair_records, cnt, grid, g, frac_bits, (unsigned long long*)acc);
+        KERNEL_CHECK();
+    }
     return CPH_OK;
 }
 

@@ -510,10 +510,10 @@ __global__ void __launch_bounds__(TPB) diag_hist_kernel(const u32* __restrict__ 
     for (size_t t = lo + threadIdx.x; t < hi; t += TPB) {
         u32 p = pem_pk[t];
         u32 r = pem_row[t] & CPH_ROWM;
-        double c = (double)(p & CPH_CNTM);
+        u64 c = p & CPH_CNTM;
         double sc = scale[use_high_order ? (p >> 24) : 1u];
         if (ew) sc *= (double)ew[t];
-        unsigned long long v = __double2ull_rn((c * sc) * c);
+        unsigned long long v = __double2ull_rn((double)(c * c) * sc);
         if (use_smem) atomicAdd(&dbins[r], v);
         else atomicAdd(&diag[r], v);
     }

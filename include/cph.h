@@ -171,6 +171,17 @@ int cph_expand_accumulate(const uint32_t* pem_row, const uint32_t* pem_pk, const
 int cph_expand_accumulate_diag(const uint32_t* pem_row, const uint32_t* pem_pk, const float* entry_w, uint64_t nnz,
                                uint32_t n, int use_high_order, int frac_bits, int zero_first, uint64_t* acc,
                                uint64_t* diag_fx, cph_stream_t stream);
+/* Binned form of cph_expand_accumulate_diag for accumulators beyond L2 (n > ~5.6k, no entry weights): the pair updates
+ * are first written out grouped by accumulator block (contig-block pairs of <= 48 MB), then applied block after block so
+ * that the cells being updated stay in L2; integer sums are order-free, so acc / diag_fx come out bit-identical to the
+ * direct kernel.  Two calls with the SAME workspace: phase 1 zeroes, counts the pairs per block, fills diag_fx and
+ * returns the number of records in *h_pairs; the caller allocates pair_records (u64 each) and calls phase 2, which
+ * writes and applies them.  n <= 115368 (46 block rows of <= 50 MB blocks).
+ * phase 3 / 4 run the two halves of phase 2 apart (record fill only / apply only) for timing. */
+int cph_expand_accumulate_binned(int phase, const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n,
+                                 int use_high_order, int frac_bits, int zero_first, uint64_t* acc, uint64_t* diag_fx,
+                                 uint64_t* pair_records, uint64_t* h_pairs, void* ws, size_t ws_bytes,
+                                 size_t* h_ws_need, cph_stream_t stream);
 int cph_expand_count(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,
                      uint64_t* h_nnz, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 int cph_expand_emit(const uint64_t* acc, const uint64_t* diag_fx, uint32_t n, int frac_bits, float min_weight,

@@ -422,3 +422,32 @@ def test_extract_rows_with_explicit_zero_counts(api):
     assert sub.shape == eo.shape
     for x, y in zip(canon_dup(sub), canon_dup(eo)):
         assert np.array_equal(x, y)
+
+
+@pytest.mark.parametrize("use_high_order", [True, False])
+def test_binned_expansion_is_bit_identical(api, use_high_order, monkeypatch):
+    """Accumulators beyond L2 (n > 5.6k) take the binned kernels (pairs grouped by accumulator block, then applied block
+    by block).  Integer fixed-point sums do not depend on the order of addition, so triangle and diagonal must equal the
+    direct kernel's bit for bit -- including pairs whose count product does not fit the 34-bit record field."""
+    _, _, D, synth = api
+    import torch
+    g = synth.make_genome(6000, 10, 4, seed=91)
+    t = synth.porec_table_device(g, 1_500_000, 92, law="poisson", first=0, device="cuda")
+    raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=1)
+    H = D.incidence(raw, min_contacts=5, min_mapq=0)
+    assert H.n_rows > D.BINNED_MIN_N and H.nnz >= D.BINNED_MIN_NNZ
+    pk = H.pem_pk.view(torch.int32)
+    big = torch.arange(0, H.nnz, 100_003, device=pk.device)
+    pk[big] = (pk[big] & ~0x00FFFFFF) | 200_000          # products above 2^34 with one another are unlikely; with
+    pk[big + 1] = (pk[big + 1] & ~0x00FFFFFF) | 150_000  # the neighbour entry (same hyperedge most of the time) they occur
+    H._bound = None
+    l0 = __import__("cphasing_b200")._lib.launches()
+    a1 = D.expand_accumulate(H, use_high_order=use_high_order)
+    binned_launches = __import__("cphasing_b200")._lib.launches() - l0
+    monkeypatch.setattr(D, "BINNED_MIN_N", 1 << 30)
+    a2 = D.expand_accumulate(H, use_high_order=use_high_order)
+    assert binned_launches >= 4                          # count, scan.., fill, apply
+    assert a1.frac_bits == a2.frac_bits
+    assert torch.equal(a1.diag, a2.diag)
+    assert torch.equal(a1.acc, a2.acc)
+    assert int((a1.acc != 0).sum().item()) > 1_000_000
