@@ -42,8 +42,9 @@ _SIGS = {
     "cph_pairs_to_edges": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U64, _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_porec_to_edges": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U64, _U32, _I,
                                 _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
-    "cph_porec_to_edges_host": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U32, _U64,
+    "cph_porec_to_edges_host": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U32, _U64, _I,
                                      _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
+    "cph_release_host_staging": (_I, []),
     "cph_edges_to_triplets": (_I, [_P, _P, _P, _P, _U64, _U32, _P, _P, _P, _P] + _WS),
     "cph_triplets_to_edges": (_I, [_P, _P, _P, _P, _U64, _U32, _P, _P, _P, _P] + _WS),
     "cph_row_sums": (_I, [_P, _P, _P, _U64, _U32, _I, _P, _I, _P, _P, _P]),

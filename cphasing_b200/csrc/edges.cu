@@ -12,6 +12,13 @@
 // order of the read; a scan compacts the survivors.  Bytes per record (sorted input): 9 read,
 // 8+8 key write/read x2, 10 flags -> HBM bound.
 #include "common.cuh"
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <cstring>
+#include <emmintrin.h>
+#include <mutex>
+#include <thread>
 #include <vector>
 
 namespace {
@@ -757,47 +764,281 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
     return CPH_OK;
 }
 
-// Host-table variant of the fast path: the three columns live in HOST memory (pinned for full PCIe rate) and are moved
-// to caller-owned device staging columns in chunks on a private copy stream; the tile kernel for the tiles a chunk
-// completes is launched as soon as that chunk has landed, so the group-by runs under the next chunk's transfer.
-// The ticket counter and the look-back state words carry over from launch to launch, which makes the sequence of
-// launches equivalent to one launch over the whole table.  A launch may only cover tiles whose window (tile + halo)
-// has arrived AND whose last read is known to end inside the arrived prefix (the slow path walks to the end of a
+
+namespace {
+// ------------------------------------------------------------------------------------------------
+// Packed host transfer.  The Pore-C table crosses PCIe at 9 B per record (read u32, contig u32, mapq i8) and PCIe, not the
+// kernels, bounds the end-to-end call.  A table grouped by read has small read-id steps and (below 65536 contigs) 16-bit
+// contig ids, so host threads re-encode each chunk into pinned staging as
+//     delta u8 (read[i] - read[i-1]) | mapq i8 | contig u16 (u32 when n_contigs > 65536) | anchor u32 per 1024 records
+// = 4 B per record, and pk_unpack_kernel restores the three device columns bit for bit (anchor + block-local prefix sum of
+// the deltas).  A chunk with a read-id step outside 0..255 (or an out-of-range contig id) is copied as it is.  The caller's
+// arrays need not be pinned: only the staging ring is.
+// ------------------------------------------------------------------------------------------------
+constexpr u64 PK_CHUNK = 1u << 20;        // records per packed chunk (default)
+constexpr u32 PK_GROUP = 1024;            // records per anchor = per CTA of the unpack kernel
+constexpr int PK_NSLOT = 32;              // pinned host slots
+constexpr int PK_NDEV = 8;                // device slots
+
+struct PkLayout {
+    size_t off_delta, off_mapq, off_contig, off_anchor, bytes;
+};
+inline PkLayout pk_layout(u64 len, int wide) {
+    const size_t L = ceil_div((size_t)len, (size_t)PK_GROUP) * PK_GROUP;
+    PkLayout o;
+    o.off_delta = 0;
+    o.off_mapq = L;
+    o.off_contig = 2 * L;
+    o.off_anchor = o.off_contig + L * (wide ? 4 : 2);
+    o.bytes = o.off_anchor + (L / PK_GROUP) * sizeof(u32);
+    o.bytes = (o.bytes + 255) & ~(size_t)255;
+    return o;
+}
+
+// streaming (non-temporal) stores: the packed bytes are read next by the DMA engine, not by this core, and a normal
+// store would first fetch the destination line (a third of the host memory traffic of the packing pass)
+inline void pk_stream_copy(unsigned char* __restrict__ dst, const unsigned char* __restrict__ src, u64 n) {    // dst 16 B aligned
+    u64 i = 0;
+    for (; i + 16 <= n; i += 16) _mm_stream_si128((__m128i*)(dst + i), _mm_loadu_si128((const __m128i*)(src + i)));
+    for (; i < n; ++i) dst[i] = src[i];
+}
+
+// host: records [lo, hi) -> slot; false when the chunk cannot be packed
+bool pk_pack(const u32* __restrict__ hr, const u32* __restrict__ hc, const int8_t* __restrict__ hq, u64 lo, u64 hi, int wide,
+             unsigned char* __restrict__ slot) {
+    const u64 len = hi - lo;
+    const PkLayout L = pk_layout(len, wide);
+    unsigned char* __restrict__ d = slot + L.off_delta;
+    const u32* __restrict__ r = hr + lo;
+    u32 bad = lo > 0 ? r[0] - hr[lo - 1] : 0u;        // order across the chunk border (the anchor carries the value)
+    d[0] = 0;
+    u64 i = 1;
+    for (; i < 16 && i < len; ++i) {
+        const u32 dl = r[i] - r[i - 1];
+        bad |= dl;
+        d[i] = (unsigned char)dl;
+    }
+    __m128i vb = _mm_setzero_si128();
+    for (; i + 16 <= len; i += 16) {
+        const __m128i d0 = _mm_sub_epi32(_mm_loadu_si128((const __m128i*)(r + i)), _mm_loadu_si128((const __m128i*)(r + i - 1)));
+        const __m128i d1 = _mm_sub_epi32(_mm_loadu_si128((const __m128i*)(r + i + 4)), _mm_loadu_si128((const __m128i*)(r + i + 3)));
+        const __m128i d2 = _mm_sub_epi32(_mm_loadu_si128((const __m128i*)(r + i + 8)), _mm_loadu_si128((const __m128i*)(r + i + 7)));
+        const __m128i d3 = _mm_sub_epi32(_mm_loadu_si128((const __m128i*)(r + i + 12)), _mm_loadu_si128((const __m128i*)(r + i + 11)));
+        vb = _mm_or_si128(vb, _mm_or_si128(_mm_or_si128(d0, d1), _mm_or_si128(d2, d3)));
+        // (steps above 255 saturate in the packs; they are caught through vb and the chunk is then not used)
+        _mm_stream_si128((__m128i*)(d + i), _mm_packus_epi16(_mm_packs_epi32(d0, d1), _mm_packs_epi32(d2, d3)));
+    }
+    for (; i < len; ++i) {
+        const u32 dl = r[i] - r[i - 1];
+        bad |= dl;
+        d[i] = (unsigned char)dl;
+    }
+    alignas(16) u32 lanes[4];
+    _mm_store_si128((__m128i*)lanes, vb);
+    bad |= lanes[0] | lanes[1] | lanes[2] | lanes[3];
+    if (bad >> 8) return false;
+    pk_stream_copy(slot + L.off_mapq, (const unsigned char*)(hq + lo), len);
+    const u32* __restrict__ c = hc + lo;
+    if (wide) pk_stream_copy(slot + L.off_contig, (const unsigned char*)c, len * 4);
+    else {
+        uint16_t* __restrict__ c16 = (uint16_t*)(slot + L.off_contig);
+        __m128i vc = _mm_setzero_si128();
+        u32 badc = 0;
+        u64 k = 0;
+        for (; k + 8 <= len; k += 8) {
+            const __m128i a0 = _mm_loadu_si128((const __m128i*)(c + k)), a1 = _mm_loadu_si128((const __m128i*)(c + k + 4));
+            vc = _mm_or_si128(vc, _mm_or_si128(a0, a1));
+            // low 16 bits of each lane, exactly: sign-extend them so that the signed pack cannot saturate
+            _mm_stream_si128((__m128i*)(c16 + k), _mm_packs_epi32(_mm_srai_epi32(_mm_slli_epi32(a0, 16), 16),
+                                                                 _mm_srai_epi32(_mm_slli_epi32(a1, 16), 16)));
+        }
+        for (; k < len; ++k) {
+            badc |= c[k];
+            c16[k] = (uint16_t)c[k];
+        }
+        _mm_store_si128((__m128i*)lanes, vc);
+        badc |= lanes[0] | lanes[1] | lanes[2] | lanes[3];
+        if (badc >> 16) return false;
+    }
+    u32* a = (u32*)(slot + L.off_anchor);
+    for (u64 g = 0; g * PK_GROUP < len; ++g) a[g] = r[g * PK_GROUP];
+    _mm_sfence();        // streaming stores are weakly ordered: make them visible before the chunk is announced
+    return true;
+}
+
+// one CTA per 1024 records, 4 records per thread
+template <bool WIDE>
+__global__ void __launch_bounds__(256) pk_unpack_kernel(const unsigned char* __restrict__ slot, PkLayout L, u64 len,
+                                                        u32* __restrict__ d_read, u32* __restrict__ d_contig,
+                                                        int8_t* __restrict__ d_mapq) {
+    __shared__ u32 wsum[8];
+    const u32 t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const u64 i0 = (u64)blockIdx.x * PK_GROUP + 4 * t;          // multiple of 4; the slot is padded to whole groups
+    const uchar4 dl = *(const uchar4*)(slot + L.off_delta + i0);
+    const u32 anchor = ((const u32*)(slot + L.off_anchor))[blockIdx.x];
+    u32 v0 = t == 0 ? 0u : dl.x, v1 = v0 + dl.y, v2 = v1 + dl.z, v3 = v2 + dl.w;
+    u32 x = v3;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const u32 y = __shfl_up_sync(0xffffffffu, x, o);
+        if ((int)lane >= o) x += y;
+    }
+    if (lane == 31) wsum[warp] = x;
+    __syncthreads();
+    u32 base = anchor + x - v3;
+    for (u32 w = 0; w < warp; ++w) base += wsum[w];
+    uint4 c;
+    if (WIDE) c = *(const uint4*)(slot + L.off_contig + i0 * 4);
+    else {
+        const ushort4 h = *(const ushort4*)(slot + L.off_contig + i0 * 2);
+        c = make_uint4(h.x, h.y, h.z, h.w);
+    }
+    const char4 q = *(const char4*)(slot + L.off_mapq + i0);
+    if (i0 + 4 <= len) {
+        *(uint4*)(d_read + i0) = make_uint4(base + v0, base + v1, base + v2, base + v3);
+        *(uint4*)(d_contig + i0) = c;
+        *(char4*)(d_mapq + i0) = q;
+    } else {
+        const u32 rv[4] = {base + v0, base + v1, base + v2, base + v3};
+        const u32 cv[4] = {c.x, c.y, c.z, c.w};
+        const int8_t qv[4] = {q.x, q.y, q.z, q.w};
+        for (u32 k = 0; k < 4 && i0 + k < len; ++k) {
+            d_read[i0 + k] = rv[k];
+            d_contig[i0 + k] = cv[k];
+            d_mapq[i0 + k] = qv[k];
+        }
+    }
+}
+
+// pinned staging ring, allocated on first use and kept (cudaHostAlloc of ~130 MB costs tens of ms)
+std::mutex g_pk_mutex;
+unsigned char* g_pk_host = nullptr;
+size_t g_pk_host_bytes = 0;
+
+}  // namespace
+
+extern "C" int cph_release_host_staging() {
+    std::lock_guard<std::mutex> lk(g_pk_mutex);
+    if (g_pk_host) cudaFreeHost(g_pk_host);
+    g_pk_host = nullptr;
+    g_pk_host_bytes = 0;
+    return CPH_OK;
+}
+
+// Host-table variant of the fast path: the three columns live in HOST memory.  Chunks are brought over on a private
+// copy stream while porec_tile_kernel already works on the tiles that have landed (its ticket counter and look-back
+// state carry across launches), so the group-by hides behind the transfer.  pack_threads = 0: the columns are copied as
+// they are (pinned memory for full PCIe speed); > 0: that many host threads re-encode the chunks to 4 B per record
+// first (see "Packed host transfer" above; the caller's arrays may be pageable); < 0: two fewer than the machine has
+// cores, at most 16.  A launch may only cover tiles whose window ([tile start, +PT_TILE+PT_HALO)) has landed, and must stop
+// before a read that is still growing at the end of the landed records (the tile would otherwise see a truncated
 // read that overflows the window); the host read column answers that in O(1) per chunk.
-// h_counts[2] = 1 when the table turned out not to be grouped by read: the staged device columns are complete, the
+// h_counts[3] = bytes that crossed to the device.  h_counts[2] = 1 when the table turned out not to be grouped by read: the staged device columns are complete, the
 // outputs are not, and the caller re-runs cph_porec_to_edges on them (general path).
 extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_contig_idx, const int8_t* h_mapq, u32* d_read_idx,
                                        u32* d_contig_idx, int8_t* d_mapq, u64 n_records, u32 n_contigs, int min_mapq,
-                                       u32 min_order, u32 max_order, u32 read_offset, u64 chunk_records, u32* rem_row,
-                                       u32* rem_col, u32* rem_count, int8_t* rem_mapq, u64* h_counts, void* ws, size_t ws_bytes,
-                                       size_t* h_ws_need, void* stream) {
+                                       u32 min_order, u32 max_order, u32 read_offset, u64 chunk_records, int pack_threads,
+                                       u32* rem_row, u32* rem_col, u32* rem_count, int8_t* rem_mapq, u64* h_counts, void* ws,
+                                       size_t ws_bytes, size_t* h_ws_need, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     const u64 N = n_records;
     ARG_CHECK(N < (1ull << 32) - 8192);
     ARG_CHECK(n_contigs > 0 && n_contigs < (1u << 23));
+    int nthreads = pack_threads;
+    if (nthreads < 0) {
+        const unsigned hw = std::thread::hardware_concurrency();
+        nthreads = (int)(hw < 4 ? 1 : hw > 18 ? 16 : hw - 2);       // two cores stay free: this thread feeds the streams
+    }
+    const bool packed = nthreads > 0;
+    const int wide = n_contigs > 65536u;
+    u64 pk_chunk = chunk_records ? ceil_div((size_t)chunk_records, (size_t)PK_GROUP) * PK_GROUP : PK_CHUNK;
+    if (pk_chunk > 8 * PK_CHUNK) pk_chunk = 8 * PK_CHUNK;
+    const PkLayout slot_layout = pk_layout(pk_chunk, wide);
     WS_BEGIN(ar);
     const u32 ntiles = (u32)ceil_div(N > 0 ? N : 1, (size_t)PT_TILE);
     u32* scal = ar.take<u32>(4);
     u64* tile_state = ar.take<u64>((size_t)ntiles);
+    unsigned char* dev_ring = packed ? ar.take<unsigned char>(slot_layout.bytes * PK_NDEV) : nullptr;
     WS_QUERY_RETURN(ar);
     ARG_CHECK(h_counts);
-    h_counts[0] = h_counts[1] = h_counts[2] = 0;
+    h_counts[0] = h_counts[1] = h_counts[2] = h_counts[3] = 0;
     if (N == 0) return CPH_OK;
     ARG_CHECK(h_read_idx && h_contig_idx && h_mapq && d_read_idx && d_contig_idx && d_mapq);
     ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq);
     PorecIn in{d_read_idx, d_contig_idx, d_mapq, nullptr, nullptr, nullptr, N, n_contigs, min_mapq, (i64)0};
-    u64 chunk = chunk_records ? chunk_records : (u64)(8u << 20);
-    chunk = ceil_div(chunk, (size_t)PT_TILE) * PT_TILE;
+    u64 chunk = packed ? pk_chunk : (chunk_records ? chunk_records : (u64)(8u << 20));
+    if (!packed) chunk = ceil_div(chunk, (size_t)PT_TILE) * PT_TILE;
     const u32 nchunks = (u32)ceil_div(N, chunk);
-    cudaStream_t cs = nullptr;
+    const u32 launch_every = packed ? 4u : 1u;          // packed chunks are small: one tile launch per 4 of them
+
+    // ---- host packing threads (packed mode) ----
+    std::unique_lock<std::mutex> ring_lock(g_pk_mutex, std::defer_lock);
+    struct Shared {
+        std::mutex m;
+        std::condition_variable cv;
+        std::vector<unsigned char> state;       // per chunk: 0 = pending, 1 = packed, 2 = copy as it is
+        u64 released = 0;                       // chunks whose host slot may be overwritten
+        std::atomic<u32> next{0};
+        bool abort = false;
+    } sh;
+    std::vector<std::thread> workers;
+    if (packed) {
+        ring_lock.lock();                       // one packed call at a time owns the pinned ring
+        const size_t want = slot_layout.bytes * PK_NSLOT;
+        if (g_pk_host_bytes < want) {
+            if (g_pk_host) cudaFreeHost(g_pk_host);
+            g_pk_host = nullptr;
+            g_pk_host_bytes = 0;
+            CUDA_TRY(cudaHostAlloc((void**)&g_pk_host, want, cudaHostAllocDefault));
+            g_pk_host_bytes = want;
+        }
+        sh.state.assign(nchunks, 0);
+        unsigned char* ring = g_pk_host;
+        auto work = [&, ring]() {
+            for (;;) {
+                const u32 k = sh.next.fetch_add(1);
+                if (k >= nchunks) return;
+                {
+                    std::unique_lock<std::mutex> lk(sh.m);
+                    sh.cv.wait(lk, [&] { return sh.abort || sh.released + PK_NSLOT > k; });
+                    if (sh.abort) return;
+                }
+                const u64 lo = (u64)k * chunk, hi = lo + chunk < N ? lo + chunk : N;
+                const bool ok = pk_pack(h_read_idx, h_contig_idx, h_mapq, lo, hi, wide, ring + (size_t)(k % PK_NSLOT) * slot_layout.bytes);
+                {
+                    std::lock_guard<std::mutex> lk(sh.m);
+                    sh.state[k] = ok ? 1 : 2;
+                }
+                sh.cv.notify_all();
+            }
+        };
+        const int nt = (u32)nthreads < nchunks ? nthreads : (int)nchunks;
+        for (int i = 0; i < nt; ++i) workers.emplace_back(work);
+    }
+
+    cudaStream_t cs = nullptr, us = nullptr;
     cudaEvent_t ready = nullptr;
-    std::vector<cudaEvent_t> landed(nchunks, nullptr);
+    std::vector<cudaEvent_t> landed(nchunks, nullptr), copied(packed ? nchunks : 0, nullptr);
     int rc = CPH_OK;
     auto cleanup = [&]() {
+        if (packed) {
+            {
+                std::lock_guard<std::mutex> lk(sh.m);
+                sh.abort = true;
+            }
+            sh.cv.notify_all();
+            for (std::thread& t : workers) t.join();
+            workers.clear();
+            if (cs) cudaStreamSynchronize(cs);       // the ring must be idle before the next call may take it
+            if (us) cudaStreamSynchronize(us);
+        }
         for (cudaEvent_t e : landed)
+            if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : copied)
             if (e) cudaEventDestroy(e);
         if (ready) cudaEventDestroy(ready);
         if (cs) cudaStreamDestroy(cs);
+        if (us) cudaStreamDestroy(us);
     };
 #define HT_TRY(expr)                                                    \
     do {                                                                \
@@ -809,6 +1050,7 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
         }                                                               \
     } while (0)
     HT_TRY(cudaStreamCreateWithFlags(&cs, cudaStreamNonBlocking));
+    if (packed) HT_TRY(cudaStreamCreateWithFlags(&us, cudaStreamNonBlocking));
     HT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
     HT_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
     HT_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
@@ -816,15 +1058,66 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     // the staging columns may be recycled blocks with work still queued on `st`: copies start after it
     HT_TRY(cudaEventRecord(ready, st));
     HT_TRY(cudaStreamWaitEvent(cs, ready, 0));
+    if (packed) HT_TRY(cudaStreamWaitEvent(us, ready, 0));
     const int use_tma = (((uintptr_t)d_read_idx | (uintptr_t)d_contig_idx | (uintptr_t)d_mapq) & 15) == 0;
-    u32 t_done = 0;
+    u32 t_done = 0, waited = 0;
+    u64 rel = 0, h2d_bytes = 0;
     for (u32 c = 0; c < nchunks; ++c) {
         const u64 lo = (u64)c * chunk, hi = lo + chunk < N ? lo + chunk : N, len = hi - lo;
-        HT_TRY(cudaMemcpyAsync(d_read_idx + lo, h_read_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
-        HT_TRY(cudaMemcpyAsync(d_contig_idx + lo, h_contig_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
-        HT_TRY(cudaMemcpyAsync(d_mapq + lo, h_mapq + lo, len, cudaMemcpyHostToDevice, cs));
+        int how = 2;
+        if (packed) {
+            for (;;) {       // wait for the chunk to be packed; meanwhile hand finished host slots back to the packers
+                bool moved = false;
+                while (rel < c) {
+                    const cudaError_t q = cudaEventQuery(copied[rel]);
+                    if (q == cudaSuccess) {
+                        ++rel;
+                        moved = true;
+                    } else {
+                        if (q == cudaErrorNotReady) (void)cudaGetLastError();
+                        else HT_TRY(q);
+                        break;
+                    }
+                }
+                std::unique_lock<std::mutex> lk(sh.m);
+                if (moved) {
+                    sh.released = rel;
+                    sh.cv.notify_all();
+                }
+                if (sh.cv.wait_for(lk, std::chrono::microseconds(50), [&] { return sh.state[c] != 0; })) {
+                    how = sh.state[c];
+                    break;
+                }
+            }
+        }
         HT_TRY(cudaEventCreateWithFlags(&landed[c], cudaEventDisableTiming));
-        HT_TRY(cudaEventRecord(landed[c], cs));
+        if (how == 1) {
+            const PkLayout L = pk_layout(len, wide);
+            unsigned char* dslot = dev_ring + (size_t)(c % PK_NDEV) * slot_layout.bytes;
+            if (c >= (u32)PK_NDEV) HT_TRY(cudaStreamWaitEvent(cs, landed[c - PK_NDEV], 0));      // device slot unpacked?
+            HT_TRY(cudaMemcpyAsync(dslot, g_pk_host + (size_t)(c % PK_NSLOT) * slot_layout.bytes, L.bytes, cudaMemcpyHostToDevice, cs));
+            h2d_bytes += L.bytes;
+            HT_TRY(cudaEventCreateWithFlags(&copied[c], cudaEventDisableTiming));
+            HT_TRY(cudaEventRecord(copied[c], cs));
+            HT_TRY(cudaStreamWaitEvent(us, copied[c], 0));
+            const unsigned g = (unsigned)ceil_div((size_t)len, (size_t)PK_GROUP);
+            if (wide) pk_unpack_kernel<true><<<g, 256, 0, us>>>(dslot, L, len, d_read_idx + lo, d_contig_idx + lo, d_mapq + lo);
+            else pk_unpack_kernel<false><<<g, 256, 0, us>>>(dslot, L, len, d_read_idx + lo, d_contig_idx + lo, d_mapq + lo);
+            ++g_cph_launches;
+            HT_TRY(cudaGetLastError());
+            HT_TRY(cudaEventRecord(landed[c], us));
+        } else {
+            HT_TRY(cudaMemcpyAsync(d_read_idx + lo, h_read_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
+            HT_TRY(cudaMemcpyAsync(d_contig_idx + lo, h_contig_idx + lo, len * 4, cudaMemcpyHostToDevice, cs));
+            HT_TRY(cudaMemcpyAsync(d_mapq + lo, h_mapq + lo, len, cudaMemcpyHostToDevice, cs));
+            h2d_bytes += len * 9;
+            if (packed) {
+                HT_TRY(cudaEventCreateWithFlags(&copied[c], cudaEventDisableTiming));
+                HT_TRY(cudaEventRecord(copied[c], cs));
+            }
+            HT_TRY(cudaEventRecord(landed[c], cs));
+        }
+        if ((c + 1) % launch_every != 0 && hi != N) continue;
         u32 t_hi;
         if (hi == N) t_hi = ntiles;
         else {
@@ -832,7 +1125,8 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
             while (t_hi > t_done && h_read_idx[(u64)t_hi * PT_TILE - 1] == h_read_idx[hi - 1]) --t_hi;
         }
         if (t_hi > t_done) {
-            HT_TRY(cudaStreamWaitEvent(st, landed[c], 0));
+            // (packed and unpacked chunks land on different streams: wait for every chunk since the last launch)
+            for (; waited <= c; ++waited) HT_TRY(cudaStreamWaitEvent(st, landed[waited], 0));
             porec_tile_kernel<<<t_hi - t_done, PT_THREADS, sizeof(PtSmem), st>>>(in, use_tma, min_order, max_order, read_offset,
                                                                                 (unsigned long long*)tile_state, scal, rem_row,
                                                                                 rem_col, rem_count, rem_mapq);
@@ -847,8 +1141,10 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     HT_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
     HT_TRY(cudaStreamSynchronize(st));
     HT_TRY(cudaStreamSynchronize(cs));
+    if (us) HT_TRY(cudaStreamSynchronize(us));
 #undef HT_TRY
     cleanup();
+    h_counts[3] = h2d_bytes;
     if (hs[1] != 0) {
         h_counts[2] = 1;
         return rc;

@@ -78,18 +78,27 @@ int cph_porec_to_edges(const uint32_t* read_idx, const uint32_t* contig_idx, con
                        uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 
 /* Host-table form of cph_porec_to_edges for tables grouped by read (what _load_and_filter_single,
- * hypergraph.py:1700-1789, hands to process_pore_c_table): h_* are HOST columns (pinned memory gives
- * the full PCIe rate), d_* caller-owned device staging columns of n_records elements.  The columns are
- * copied in chunks of `chunk_records` (0 = default) on a private stream and the group-by kernel runs on
- * the tiles of every chunk that has landed, i.e. under the transfer of the next one.  No edge filter
- * (edge_length == 0 only).  h_counts[0] = nnz, h_counts[1] = max col + 1, h_counts[2] = 1 if the table is
+ * hypergraph.py:1700-1789, hands to process_pore_c_table): h_* are HOST columns, d_* caller-owned device
+ * staging columns of n_records elements.  The columns are copied in chunks of `chunk_records` (0 = default)
+ * on a private stream and the group-by kernel runs on the tiles of every chunk that has landed, i.e. under
+ * the transfer of the next one.  pack_threads = 0: chunks are copied as they are (9 B per record; pinned
+ * memory gives the full PCIe rate).  pack_threads > 0: that many host threads first re-encode every chunk
+ * into a pinned staging ring owned by the library as (read-id delta u8 | mapq | contig u16 [u32 above 65536
+ * contigs] | one u32 anchor per 1024 records) = 4 B per record, and a kernel restores the device columns
+ * bit for bit; a chunk whose read ids step by more than 255 is copied as it is; the h_* arrays may be
+ * pageable.  pack_threads < 0: two fewer than the host has cores, at most 16.  No edge filter
+ * (edge_length == 0 only).  h_counts has FOUR entries: [0] = nnz, [1] = max col + 1, [3] = bytes copied to the
+ * device, [2] = 1 if the table is
  * NOT grouped by read: the d_* columns are complete, the outputs are not -- call cph_porec_to_edges on them. */
 int cph_porec_to_edges_host(const uint32_t* h_read_idx, const uint32_t* h_contig_idx, const int8_t* h_mapq,
                             uint32_t* d_read_idx, uint32_t* d_contig_idx, int8_t* d_mapq,
                             uint64_t n_records, uint32_t n_contigs, int min_mapq, uint32_t min_order,
-                            uint32_t max_order, uint32_t read_offset, uint64_t chunk_records,
+                            uint32_t max_order, uint32_t read_offset, uint64_t chunk_records, int pack_threads,
                             uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
                             uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
+/* frees the pinned staging ring that the packed form of cph_porec_to_edges_host keeps between calls */
+int cph_release_host_staging(void);
 
 /* ---- HyperEdges wire order <-> raw edge-major --------------------------------------------------
  * cph_edges_to_triplets: the `sort by chrom_idx` + casts of generate_edges (hypergraph.py:1877-1889,

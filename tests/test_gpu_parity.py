@@ -361,9 +361,11 @@ def test_porec_edges_unaligned_device_columns(api):
 
 @pytest.mark.parametrize("chunk", [3584, 3 * 3584, 1 << 20])
 @pytest.mark.parametrize("pinned", [False, True])
-def test_porec_host_streamed_chunks(api, chunk, pinned, monkeypatch):
+@pytest.mark.parametrize("pack", [0, 3])
+def test_porec_host_streamed_chunks(api, chunk, pinned, pack, monkeypatch):
     """cph_porec_to_edges_host: host columns copied in chunks with the tile kernel launched per landed chunk must give
-    exactly what the one-launch device path and the oracle give -- long reads crossing chunk borders included."""
+    exactly what the one-launch device path and the oracle give -- long reads crossing chunk borders included.
+    pack = 3: three host threads re-encode the chunks (read-id deltas, 16-bit contigs) and the device restores them."""
     _, _, D, _ = api
     import torch
     rng = np.random.default_rng(chunk % 97 + pinned)
@@ -380,6 +382,8 @@ def test_porec_host_streamed_chunks(api, chunk, pinned, monkeypatch):
     mapq = rng.choice(np.array([0, 3, 20, 60], dtype=np.int8), size=contig.size)
     monkeypatch.setattr(D, "STREAM_MIN_RECORDS", 1)
     monkeypatch.setattr(D, "STREAM_CHUNK_RECORDS", chunk)
+    monkeypatch.setattr(D, "STREAM_PACK_CHUNK_RECORDS", chunk)
+    monkeypatch.setattr(D, "STREAM_PACK_THREADS", pack)
     cols = (read, contig, mapq)
     if pinned:
         cols = tuple(torch.from_numpy(x.view(np.int32) if x.dtype == np.uint32 else x).pin_memory() for x in cols)
@@ -400,6 +404,33 @@ def test_porec_host_streamed_chunks(api, chunk, pinned, monkeypatch):
     row2, col2, cnt2, mq2 = D.edges_to_triplets(raw2)
     assert np.array_equal(row2.cpu().numpy(), exp[0]) and np.array_equal(col2.cpu().numpy() - 3, exp[1])
     assert np.array_equal(cnt2.view(torch.int32).cpu().numpy().view(np.uint32), exp[2])
+
+
+@pytest.mark.parametrize("n", [300, 70000])
+def test_porec_host_packed_fallbacks(api, n, monkeypatch):
+    """Packed host transfer: chunks whose read ids jump by more than 255 travel unpacked next to packed ones, and more
+    than 65536 contigs switch the packed contig column to 32 bits -- same edges as the oracle either way."""
+    _, _, D, _ = api
+    import torch
+    rng = np.random.default_rng(n)
+    lens = rng.integers(1, 9, size=40000)
+    ids = np.cumsum(rng.integers(1, 4, size=lens.size)).astype(np.int64)
+    ids[lens.size // 3:] += 1000            # one big step: that chunk cannot be delta-encoded
+    ids[2 * lens.size // 3:] += 255         # a step of 255+ at another chunk
+    read = np.repeat(ids.astype(np.uint32), lens)
+    contig = rng.integers(0, n, size=read.size).astype(np.uint32)
+    k = contig[1::5].size
+    contig[:5 * k:5] = contig[1::5]                         # duplicates inside reads
+    mapq = rng.choice(np.array([0, 3, 20, 60], dtype=np.int8), size=contig.size)
+    monkeypatch.setattr(D, "STREAM_MIN_RECORDS", 1)
+    monkeypatch.setattr(D, "STREAM_PACK_CHUNK_RECORDS", 4096)
+    monkeypatch.setattr(D, "STREAM_PACK_THREADS", 4)
+    exp = orc.porec_edges(read, contig, mapq, min_mapq=1, min_order=2, max_order=50, n_contigs=n)
+    raw = D.porec_to_edges(read, contig, mapq, n, min_mapq=1, min_order=2, max_order=50)
+    row, col, cnt, mq = D.edges_to_triplets(raw)
+    got = (row.cpu().numpy(), col.cpu().numpy(), cnt.view(torch.int32).cpu().numpy().view(np.uint32), mq.cpu().numpy())
+    for a, b in zip(got, exp):
+        assert np.array_equal(a, b)
 
 
 def test_extract_rows_with_explicit_zero_counts(api):
