@@ -468,6 +468,83 @@ __global__ void __launch_bounds__(CM_THREADS) agg_rows_kernel(LGraph g, const i3
     }
 }
 
+// Aggregation onto FEW super-vertices (ng <= AGG_DENSE_MAX): a warp per super-vertex would leave the machine empty (at
+// n = 20k, ng ~ 100 that was 8 ms per launch, the largest item of a clustering), so the members' rows are shared out over
+// the whole grid instead.  CTA b takes a slice of `members` (vertices sorted by super-vertex), sums the rows of one
+// super-vertex at a time into a shared-memory strip of ng int64 (entries that stay inside the super-vertex -- most of
+// them -- go to a register) and flushes the strip into the dense ng x ng matrix M with one RED per non-zero.  M lives in
+// the (all-zero) strip scratch; agg_emit_kernel turns its rows into the CSR of the next level and zeroes them again.
+constexpr int AGG_DENSE_MAX = 4096;
+
+__global__ void __launch_bounds__(CM_THREADS) agg_dense_kernel(LGraph g, const i32* __restrict__ lab, int ng,
+                                                               const i32* __restrict__ members, int per_cta, i64* __restrict__ M) {
+    extern __shared__ i64 agg_sm[];
+    for (int j = threadIdx.x; j < ng; j += CM_THREADS) agg_sm[j] = 0;
+    __syncthreads();
+    const int q0 = blockIdx.x * per_cta, q1 = min(g.n, q0 + per_cta);
+    if (q0 >= q1) return;
+    int cur = lab[members[q0]];
+    i64 own = 0;
+    for (int q = q0; q <= q1; ++q) {
+        const int v = q < q1 ? members[q] : -1;
+        const int c = q < q1 ? lab[v] : -1;          // the same for every thread of the CTA
+        if (c != cur) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) own += __shfl_xor_sync(0xffffffffu, own, o);
+            if (lane_id() == 0 && own != 0) atomicAdd((ull*)&agg_sm[cur], (ull)own);
+            __syncthreads();
+            for (int j = threadIdx.x; j < ng; j += CM_THREADS) {
+                const i64 x = agg_sm[j];
+                if (x != 0) {
+                    add64(&M[(size_t)cur * ng + j], x);
+                    agg_sm[j] = 0;
+                }
+            }
+            __syncthreads();
+            own = 0;
+            cur = c;
+        }
+        if (q == q1) break;
+        for (i64 t = g.beg[v] + threadIdx.x; t < g.end[v]; t += CM_THREADS) {
+            const i64 w = g.w[t];
+            if (w != 0) {
+                const int l = lab[g.idx[t]];
+                if (l == c) own += w;
+                else atomicAdd((ull*)&agg_sm[l], (ull)w);
+            }
+        }
+    }
+}
+
+// one warp per super-vertex: row c of M -> CSR row in increasing column order; M is left all zero
+__global__ void __launch_bounds__(CM_THREADS) agg_emit_kernel(int ng, const i64* __restrict__ off, i64* __restrict__ M,
+                                                              i64* __restrict__ nbeg, i64* __restrict__ nend,
+                                                              i32* __restrict__ nidx, i64* __restrict__ nw) {
+    const int n_warps = gridDim.x * CM_WPB;
+    const u32 lane = lane_id();
+    for (int c = blockIdx.x * CM_WPB + (threadIdx.x >> 5); c < ng; c += n_warps) {
+        i64* row = M + (size_t)c * ng;
+        i64 o = off[c];
+        const i64 o0 = o;
+        for (int j0 = 0; j0 < ng; j0 += 32) {
+            const int j = j0 + lane;
+            const i64 x = j < ng ? ld_cg(&row[j]) : 0;
+            const u32 m = __ballot_sync(0xffffffffu, x != 0);
+            if (x != 0) {
+                const i64 p = o + __popc(m & lanemask_lt());
+                nidx[p] = j;
+                nw[p] = x;
+                st_cg(&row[j], 0);
+            }
+            o += __popc(m);
+        }
+        if (lane == 0) {
+            nbeg[c] = o0;
+            nend[c] = o;
+        }
+    }
+}
+
 __global__ void gather_kernel(const i32* __restrict__ src, const i32* index, int n, i32* dst) {   // dst may alias index
     int v = blockIdx.x * blockDim.x + threadIdx.x;
     if (v < n) dst[v] = src[index[v]];
@@ -688,9 +765,18 @@ int aggregate(State& S, const LGraph& g, const i32* lab, int ng, int dst, LGraph
     KERNEL_CHECK();
     int blocks = (int)ceil_div((size_t)ng, CM_WPB);
     if (blocks > S.blocks) blocks = S.blocks;
-    agg_rows_kernel<<<blocks, CM_THREADS, 0, S.st>>>(g, lab, ng, S.mbeg, S.members, S.off, S.strip, S.n0, S.gbeg[dst], S.gend[dst],
-                                                     S.gidx[dst], S.gw[dst]);
-    KERNEL_CHECK();
+    if (ng <= AGG_DENSE_MAX && (size_t)ng * ng <= (size_t)S.blocks * CM_WPB * S.n0) {
+        const int per_cta = (int)ceil_div((size_t)g.n, (size_t)148 * 8);
+        agg_dense_kernel<<<(unsigned)ceil_div((size_t)g.n, (size_t)per_cta), CM_THREADS, sizeof(i64) * (size_t)ng, S.st>>>(
+            g, lab, ng, S.members, per_cta, S.strip);
+        KERNEL_CHECK();
+        agg_emit_kernel<<<blocks, CM_THREADS, 0, S.st>>>(ng, S.off, S.strip, S.gbeg[dst], S.gend[dst], S.gidx[dst], S.gw[dst]);
+        KERNEL_CHECK();
+    } else {
+        agg_rows_kernel<<<blocks, CM_THREADS, 0, S.st>>>(g, lab, ng, S.mbeg, S.members, S.off, S.strip, S.n0, S.gbeg[dst],
+                                                         S.gend[dst], S.gidx[dst], S.gw[dst]);
+        KERNEL_CHECK();
+    }
     out->n = ng;
     out->beg = S.gbeg[dst];
     out->end = S.gend[dst];
