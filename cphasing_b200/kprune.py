@@ -19,23 +19,26 @@ from ._lib import check, lib, ptr, stream
 logger = logging.getLogger(__name__)
 
 
+def _pairs_array(allele_pairs):
+    if isinstance(allele_pairs, np.ndarray):
+        return allele_pairs.astype(np.int64, copy=False).reshape(-1, 2)
+    return np.asarray(list(allele_pairs), dtype=np.int64).reshape(-1, 2)
+
+
 def allele_groups(allele_pairs, n, max_alleles=1):
-    """CSR-like allele lists per contig, in allele-table order (kprune.py:437-447 keeps the first)."""
-    lists = {}
-    for a, b in allele_pairs:
-        a = int(a); b = int(b)
-        l = lists.setdefault(a, [])
-        if len(l) < max_alleles:
-            l.append(b)
+    """CSR-like allele lists per contig, in allele-table order (kprune.py:437-447 keeps the first): for every contig a
+    the first `max_alleles` partners b of the rows (a, b), duplicates included."""
+    p = _pairs_array(allele_pairs)
+    a, b = p[:, 0], p[:, 1]
+    order = np.argsort(a, kind="stable")                     # table order survives inside each contig
+    a_s = a[order]
+    start = np.flatnonzero(np.r_[True, a_s[1:] != a_s[:-1]]) if a_s.size else np.zeros(0, dtype=np.int64)
+    rank = np.arange(a_s.size) - np.repeat(start, np.diff(np.r_[start, a_s.size]))
+    keep = (rank < max_alleles) & (a_s >= 0) & (a_s < n)
     ptr_ = np.zeros(n + 1, dtype=np.int64)
-    for a, l in lists.items():
-        if 0 <= a < n:
-            ptr_[a + 1] = len(l)
-    ptr_ = np.cumsum(ptr_)
+    np.cumsum(np.bincount(a_s[keep], minlength=n)[:n], out=ptr_[1:])
     idx = np.zeros(max(int(ptr_[-1]), 1), dtype=np.int32)
-    for a, l in lists.items():
-        if 0 <= a < n:
-            idx[ptr_[a]:ptr_[a] + len(l)] = l
+    idx[:int(ptr_[-1])] = b[order][keep]
     return ptr_, idx
 
 
@@ -43,7 +46,7 @@ def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False
     """-> (flag uint8[nnz] device, row_of int32[nnz] device[, best_with, best_all])."""
     dev = a.indptr.device
     n = a.n
-    pairs = np.asarray(list(allele_pairs), dtype=np.int64).reshape(-1, 2)
+    pairs = _pairs_array(allele_pairs)
     ag_ptr, ag_idx = allele_groups(pairs, n, max_alleles)
     agp = D.to_dev(ag_ptr, torch.int64, dev); agi = D.to_dev(ag_idx, torch.int32, dev)
     alr = D.to_dev(pairs[:, 0].copy(), torch.int64, dev); alc = D.to_dev(pairs[:, 1].copy(), torch.int64, dev)
