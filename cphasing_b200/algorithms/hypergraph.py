@@ -520,6 +520,26 @@ def _upper_pairs_symmetric(P):
     return np.concatenate([ru, cu]), np.concatenate([cu, ru])
 
 
+_PAIR_CACHE = []        # (list object 0, list object 1, device, result): the resolution search calls IRMM with the SAME pair lists
+
+
+def _upper_pairs_device(P, dev):
+    """`_upper_pairs_symmetric` as int64 device vectors, remembered for the last few pair lists by object identity (the
+    resolution auto-search hands the same two Series to every IRMM call; preparing 5 M pairs on the host each time cost
+    more than the clustering).  A caller that edits a list IN PLACE between calls must pass a new object."""
+    if not P:
+        return None
+    p0, p1 = (P[0], P[1]) if isinstance(P, (list, tuple)) and len(P) == 2 else (P, None)
+    for a, b, d, n, res in _PAIR_CACHE:
+        if a is p0 and b is p1 and d == dev and n == len(p0):
+            return res
+    up = _upper_pairs_symmetric(P)
+    res = None if up is None else (D.to_dev(up[0], torch.int64, dev), D.to_dev(up[1], torch.int64, dev))
+    _PAIR_CACHE.append((p0, p1, dev, len(p0), res))
+    del _PAIR_CACHE[:-4]
+    return res
+
+
 def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor=-1, cross_allelic_factor=0.3,
          resolution=1, min_weight=1, threshold=0.01, max_round=1, chunk=10000, threads=10, method="louvain",
          outprefix="all"):
@@ -542,8 +562,9 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
     raw_A = A
     a = graphops.clone_adjacency(graphops.upload_adjacency(A))
     if P_allelic_idx or P_weak_idx:
-        Pa = _upper_pairs_symmetric(P_allelic_idx) if P_allelic_idx else None
-        Pw = _upper_pairs_symmetric(P_weak_idx) if P_weak_idx else None
+        dev = a.indptr.device
+        Pa = _upper_pairs_device(P_allelic_idx, dev) if P_allelic_idx else None
+        Pw = _upper_pairs_device(P_weak_idx, dev) if P_weak_idx else None
         graphops.reweight_device(a, Pa, Pw, allelic_factor, 0.0)          # :1158-1170
     graphops.zero_diagonal(a)                                             # :1172 (kept as explicit zeros)
     use_leiden = (isinstance(allelic_factor, (int, float)) and allelic_factor < 0) or method == "leiden"

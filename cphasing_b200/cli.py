@@ -123,7 +123,7 @@ def cmd_kprune(args):
     kp = KPruneHyperGraph(_allele_table(args.alleletable), A, {c: i for i, c in enumerate(HG.nodes)})
     kp.run()
     kp.get_prune_table().to_csv(args.output, sep="\t", header=None, index=None)              # core.py:711-723
-    logger.info(f"Wrote {len(kp.allelic_prune_list)} allelic and {len(kp.weak_prune_list)} cross-allelic pairs "
+    logger.info(f"Wrote {len(kp.allelic_pairs)} allelic and {len(kp.weak_pairs)} cross-allelic pairs "
                 f"to `{args.output}`.")
     return 0
 

@@ -48,6 +48,24 @@ def group_sums(A, K, want_S=False, want_V=False):
     return (None if S is None else S.cpu().numpy()), (None if V is None else V.cpu().numpy())
 
 
+def _prune_frame(kph):
+    """index-space prune pairs of an in-process kprune as the frame get_prune_pairs (:423-461) would read back from its
+    table: rows (i, j), i < j, of the allelic list, then of the cross-allelic list, then the same rows swapped (mz1/mz2
+    swapped with them); the (c, c) rows of the cross-allelic list equal their swap and appear once."""
+    al, wk = kph.allelic_pairs, kph.weak_pairs
+    m = kph.allelic_meta()
+    c1 = np.concatenate([al[:, 0], wk[:, 0]]); c2 = np.concatenate([al[:, 1], wk[:, 1]])
+    ty = np.concatenate([np.zeros(len(al), dtype=np.int64), np.ones(len(wk), dtype=np.int64)])
+    z = np.zeros(len(wk))
+    mz1 = np.concatenate([m[:, 0], z]); mz2 = np.concatenate([m[:, 1], z])
+    sh = np.concatenate([m[:, 2], z]); sim = np.concatenate([m[:, 3], z])
+    sw = c1 != c2
+    return pd.DataFrame({'contig1': np.concatenate([c1, c2[sw]]), 'contig2': np.concatenate([c2, c1[sw]]),
+                         'mz1': np.concatenate([mz1, mz2[sw]]), 'mz2': np.concatenate([mz2, mz1[sw]]),
+                         'mzShared': np.concatenate([sh, sh[sw]]), 'similarity': np.concatenate([sim, sim[sw]]),
+                         'type': np.concatenate([ty, ty[sw]])}, copy=False)
+
+
 class HyperPartition:
     """Same constructor arguments as the reference (hyperpartition.py:114-166); options that belong to stages
     outside the accelerated path are accepted and stored."""
@@ -70,6 +88,7 @@ class HyperPartition:
         self.contigsizes = contigsizes
         self.k = k
         self.fasta = fasta
+        self._kph = None               # in-process kprune result; its name-keyed table is built only when asked for
         self.prunetable = prunetable
         self.alleletable = alleletable
         self.normalize = normalize
@@ -202,19 +221,38 @@ class HyperPartition:
         A = HyperGraph.clique_expansion_init(self.H, NW=self.get_normalize_weight() if self.normalize else None)
         kph = KPruneHyperGraph(self.alleletable, A, self.vertices_idx)
         kph.run()
-        kph.prunetable = kph.get_prune_table()
-        al = pd.DataFrame(kph.allelic_prune_list, columns=['contig1', 'contig2'])
-        wk = pd.DataFrame(kph.weak_prune_list, columns=['contig1', 'contig2'])
-        return [al['contig1'], al['contig2']], [wk['contig1'], wk['contig2']], kph.prunetable
+        al, wk = kph.allelic_pairs, kph.weak_pairs
+        return ([pd.Series(al[:, 0]), pd.Series(al[:, 1])], [pd.Series(wk[:, 0]), pd.Series(wk[:, 1])], kph)
+
+    @property
+    def prunetable(self):
+        """path / DataFrame handed in by the caller, or the 7-column table of the in-process kprune (built on first use:
+        naming millions of cross-allelic pairs is the expensive part and the partition itself works on indices)."""
+        if self._prunetable is None and self._kph is not None:
+            self._prunetable = self._kph.get_prune_table()
+        return self._prunetable
+
+    @prunetable.setter
+    def prunetable(self, value):
+        self._prunetable = value
 
     def kprune(self, alleletable=None, **kw):
-        """hyperpartition.py:1563-1595 shells out to `cphasing-rs kprune`; here the table is produced in-process."""
+        """Returns nothing, like the reference; `self.prunetable` is the 7-column table afterwards.
+        hyperpartition.py:1563-1595 shells out to `cphasing-rs kprune` and reads the table back through
+        get_prune_pairs (:423-461: name -> index, symmetric, de-duplicated).  Here the pairs are produced in-process and
+        stay in index space: rows (i, j), i < j, of the allelic list, then of the cross-allelic list, then the same rows
+        swapped -- what the reference's read-back yields (the (c, c) rows of the cross-allelic list equal their swap and
+        appear once)."""
         if alleletable is not None:
             self.alleletable = alleletable
-        _, _, table = self.get_prune_pairs_kprune()
-        self.prunetable = table
-        self.P_allelic_idx, self.P_weak_idx, self.prune_pair_df = self.get_prune_pairs()
-        return table
+        _, _, kph = self.get_prune_pairs_kprune()
+        self._kph = kph
+        self._prunetable = None
+        df = _prune_frame(kph)
+        self.prune_pair_df = df
+        c1, c2, t0 = df['contig1'].to_numpy(), df['contig2'].to_numpy(), df['type'].to_numpy() == 0
+        self.P_allelic_idx = [pd.Series(c1[t0]), pd.Series(c2[t0])]
+        self.P_weak_idx = [pd.Series(c1[~t0]), pd.Series(c2[~t0])]
 
     # -- hyperpartition.py:4012-4044
     def filter_cluster(self, verbose=1):
@@ -235,7 +273,7 @@ class HyperPartition:
         logger.info("Start hyperpartition ...")
         if sort_group:
             raise NotImplementedError("raw_sort (scaffolding order) is outside the accelerated path")
-        if is_kprune and self.alleletable is not None and self.prunetable is None:
+        if is_kprune and self.alleletable is not None and self._prunetable is None and self._kph is None:
             self.kprune(self.alleletable)
         A = self.HG.clique_expansion_init(self.H, allelic_factor=self.allelic_factor, min_weight=self.min_weight)
         # NB the reference passes the idx-keyed size dict with name-valued `nodes` (:989): no name maps, every size is
@@ -252,13 +290,13 @@ class HyperPartition:
             if self.NW is not None:
                 self.NW = self.NW[retain_idx]
             if self.prune_pair_df is not None:
+                # old index -> name -> new index (:1017-1032), as one array look-up (contig names are unique)
                 df = self.prune_pair_df
-                keep = set(retain_idx.tolist())
-                df = df[df['contig1'].isin(keep) & df['contig2'].isin(keep)].copy()
-                vi = self.vertices_idx
-                df['contig1'] = df['contig1'].map(idx_to_vertices.get).map(vi.get)
-                df['contig2'] = df['contig2'].map(idx_to_vertices.get).map(vi.get)
-                df = df.dropna(axis=0).reset_index(drop=True).astype({'contig1': 'int', 'contig2': 'int'})
+                new_of_old = np.full(raw_contig_counts, -1, dtype=np.int64)
+                new_of_old[retain_idx] = np.arange(len(retain_idx))
+                c1 = new_of_old[df['contig1'].to_numpy()]; c2 = new_of_old[df['contig2'].to_numpy()]
+                ok = (c1 >= 0) & (c2 >= 0)
+                df = df[ok].assign(contig1=c1[ok], contig2=c2[ok]).dropna(axis=0).reset_index(drop=True)
                 self.prune_pair_df = df
                 self.P_allelic_idx = [df.loc[df['type'] == 0, 'contig1'], df.loc[df['type'] == 0, 'contig2']]
                 self.P_weak_idx = [df.loc[df['type'] == 1, 'contig1'], df.loc[df['type'] == 1, 'contig2']]
@@ -561,12 +599,7 @@ class HyperPartition:
             _sub_A = HyperGraph.clique_expansion_init(sub_H, min_weight=min_weight, use_high_order=False)
             kph = KPruneHyperGraph(_AT, _sub_A, sub_vertices_idx)
             kph.run()
-            table = kph.get_prune_table()
-            sub_prune_pair_df = table.assign(contig1=table['contig1'].map(sub_vertices_idx.get),
-                                             contig2=table['contig2'].map(sub_vertices_idx.get))
-            sym = sub_prune_pair_df.rename(columns={'contig1': 'contig2', 'contig2': 'contig1', 'mz1': 'mz2', 'mz2': 'mz1'})
-            sub_prune_pair_df = pd.concat([sub_prune_pair_df, sym[sub_prune_pair_df.columns]], axis=0)
-            sub_prune_pair_df = sub_prune_pair_df.drop_duplicates(subset=['contig1', 'contig2']).reset_index(drop=True)
+            sub_prune_pair_df = _prune_frame(kph)         # table -> name -> index -> symmetric (:1336-1345), in index space
         elif prune_pair_df is not None:                                                    # :1347-1365
             K_set = set(K.tolist())
             sub_prune_pair_df = prune_pair_df[prune_pair_df.index.get_level_values(0).isin(K_set) &

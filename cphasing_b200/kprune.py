@@ -63,20 +63,31 @@ def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False
     return out + (bw[:a.nnz], ba[:a.nnz]) if want_scores else out
 
 
-def kprune_pairs(A, allele_pairs, max_alleles=1):
+def kprune_arrays(A, allele_pairs, max_alleles=1):
     """A: scipy matrix / DeviceBackedCSR; allele_pairs: (i, j) contig-index pairs in allele-table order.
-    Returns (allelic list[(i, j)], weak list[(i, j)]), each sorted, i < j -- plus the (c, c) entries the reference's weak
-    list carries (see `_self_pairs`)."""
+    Returns (allelic int64[ka, 2], weak int64[kw, 2]), rows sorted by (i, j), i < j -- plus the (c, c) rows the
+    reference's weak list carries (see `_self_pairs`).  No Python-level loop over the pairs."""
     a = graphops.upload_adjacency(A)
     flag, row_of = kprune_device(a, allele_pairs, max_alleles)
     cols = a.indices
-    al = torch.nonzero(flag == 1).flatten()
-    wk = torch.nonzero(flag == 2).flatten()
-    pick = lambda ix: sorted(zip(row_of[ix].cpu().numpy().tolist(), cols[ix].cpu().numpy().tolist()))
-    allelic, weak = pick(al), pick(wk)
+
+    def pick(code):             # CSR order = sorted by (row, col) already
+        ix = torch.nonzero(flag == code).flatten()
+        return np.stack([D.to_host(row_of[ix]).astype(np.int64), D.to_host(cols[ix]).astype(np.int64)], axis=1)
+    allelic, weak = pick(1), pick(2)
     if max_alleles == 1:
-        weak = sorted(weak + _self_pairs(a, allele_pairs))
+        selfp = np.asarray(sorted(_self_pairs(a, allele_pairs)), dtype=np.int64).reshape(-1, 2)
+        if selfp.size:
+            n = max(a.n, 1)
+            pos = np.searchsorted(weak[:, 0] * n + weak[:, 1], selfp[:, 0] * n + selfp[:, 1])
+            weak = np.insert(weak, pos, selfp, axis=0)
     return allelic, weak
+
+
+def kprune_pairs(A, allele_pairs, max_alleles=1):
+    """list form of `kprune_arrays`: (allelic list[(i, j)], weak list[(i, j)]), the reference's attribute types."""
+    allelic, weak = kprune_arrays(A, allele_pairs, max_alleles)
+    return list(map(tuple, allelic.tolist())), list(map(tuple, weak.tolist()))
 
 
 def _self_pairs(a: D.DeviceCSR, allele_pairs):
@@ -141,33 +152,61 @@ class KPruneHyperGraph:
         self.A = A
         self.contig2idx = contig2idx
         self.max_alleles = max_alleles
-        self.allelic_prune_list = []
-        self.weak_prune_list = []
+        self.allelic_pairs = np.zeros((0, 2), dtype=np.int64)      # array forms of the two lists
+        self.weak_pairs = np.zeros((0, 2), dtype=np.int64)
+        self._lists = None
 
     def run(self):
         pairs = self.alleletable_idx[[1, 2]].to_numpy()
-        al, wk = kprune_pairs(self.A, pairs, self.max_alleles)
+        al, wk = kprune_arrays(self.A, pairs, self.max_alleles)
         logger.info(f"Removed {len(al)} allelic contacts.")
         logger.info(f"Removed {len(wk)} weak contacts with allelic.")
-        self.allelic_prune_list.extend(al)
-        self.weak_prune_list.extend(wk)
+        self.allelic_pairs = np.concatenate([self.allelic_pairs, al])
+        self.weak_pairs = np.concatenate([self.weak_pairs, wk])
+        self._lists = None
 
-    def get_prune_table(self, symmetric=False):
-        """7-column prune table: contig1 contig2 mz1 mz2 mzShared similarity type (core.py:711-723)."""
-        idx2name = {i: c for c, i in self.contig2idx.items()}
+    def _as_lists(self):
+        if self._lists is None:
+            self._lists = (list(map(tuple, self.allelic_pairs.tolist())), list(map(tuple, self.weak_pairs.tolist())))
+        return self._lists
+
+    @property
+    def allelic_prune_list(self):       # kprune.py:412 (list of (i, j)); built on first use
+        return self._as_lists()[0]
+
+    @property
+    def weak_prune_list(self):          # kprune.py:413
+        return self._as_lists()[1]
+
+    def allelic_meta(self):
+        """(mz1, mz2, mzShared, similarity) float64[ka, 4] of the allelic pairs: first allele-table row of each (i, j)."""
+        df = self.alleletable_idx
         meta = {}
-        cols = list(self.alleletable_idx.columns)
-        for row in self.alleletable_idx.itertuples(index=False):
+        cols = list(df.columns)
+        for row in df.itertuples(index=False):
             d = dict(zip(cols, row))
             meta.setdefault((d[1], d[2]), tuple(d.get(k, d.get(nm, 0)) for k, nm in
                                                 ((3, 'mz1'), (4, 'mz2'), (5, 'mzShared'), (6, 'similarity'))))
-        rows = []
-        for a, b in self.allelic_prune_list:
-            mz1, mz2, sh, sim = meta.get((a, b), (0, 0, 0, 0))
-            rows.append((idx2name[a], idx2name[b], mz1, mz2, sh, sim, 0))
-        for a, b in self.weak_prune_list:
-            rows.append((idx2name[a], idx2name[b], 0, 0, 0, 0, 1))
-        res = pd.DataFrame(rows, columns=['contig1', 'contig2', 'mz1', 'mz2', 'mzShared', 'similarity', 'type'])
+        return np.array([meta.get((int(a), int(b)), (0, 0, 0, 0)) for a, b in self.allelic_pairs],
+                        dtype=np.float64).reshape(-1, 4)
+
+    def get_prune_table(self, symmetric=False):
+        """7-column prune table: contig1 contig2 mz1 mz2 mzShared similarity type (core.py:711-723)."""
+        names = np.empty(max(self.contig2idx.values(), default=-1) + 1, dtype=object)
+        for c, i in self.contig2idx.items():
+            names[i] = c
+        al, wk = self.allelic_pairs, self.weak_pairs
+        m = self.allelic_meta()
+        zeros = np.zeros(len(wk))
+
+        def col(x_al, x_wk, integral):
+            v = np.concatenate([x_al, x_wk])
+            return v.astype(np.int64) if integral and np.all(v == np.floor(v)) else v
+        res = pd.DataFrame({'contig1': np.concatenate([names[al[:, 0]], names[wk[:, 0]]]),
+                            'contig2': np.concatenate([names[al[:, 1]], names[wk[:, 1]]]),
+                            'mz1': col(m[:, 0], zeros, True), 'mz2': col(m[:, 1], zeros, True),
+                            'mzShared': col(m[:, 2], zeros, True), 'similarity': col(m[:, 3], zeros, False),
+                            'type': np.concatenate([np.zeros(len(al), dtype=np.int64), np.ones(len(wk), dtype=np.int64)])})
         if symmetric:
             res2 = res.rename(columns={'contig1': 'contig2', 'contig2': 'contig1', 'mz1': 'mz2', 'mz2': 'mz1'})
             res = pd.concat([res, res2[res.columns]], axis=0)

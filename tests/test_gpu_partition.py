@@ -286,7 +286,8 @@ def test_incremental_partition_two_rounds(case, use):
         P = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], alleletable=at, **kw)
     elif use == "prunetable":
         P0 = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], alleletable=at, **kw)
-        table = P0.kprune(at)
+        P0.kprune(at)
+        table = P0.prunetable
         assert (table["type"] == 0).sum() > 50
         P = hp.HyperPartition(ex.edges, g.contigsizes, k=[5, 4], prunetable=table, **kw)
     else:
