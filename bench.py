@@ -242,6 +242,47 @@ def e2e_step(cfg, g, host, names, trace=None):
     return A, d2h
 
 
+def api_partition(cfg, g, host):
+    """`hyperpartition` as a user of the reference runs it, through the public classes only (kind = porec): host table ->
+    HyperExtractor -> HyperPartition(alleletable) -> single_partition(k, is_kprune=True) with the resolution auto-search
+    -> groups.  Wall seconds, best of 2, everything (pandas bookkeeping included) inside."""
+    import pandas as pd
+    import torch
+    from cphasing_b200 import hypergraph as hg, synth
+    from cphasing_b200.hyperpartition import HyperPartition
+    from oracle import community_oracle as co                    # checker only (ARI against the planted groups)
+    sizes = pd.DataFrame({"length": pd.Series(g.contigsizes)})
+    names = g.names
+    at = pd.DataFrame([(0, names[a], names[b], 0, 0, 0, 0.9, 1) for a, b, *_ in synth.allele_pairs(g, seed=cfg["seed"] + 1)],
+                      columns=[0, 1, 2, "mz1", "mz2", "mzShared", "similarity", "strand"])
+
+    class AT:
+        data = at
+        filename = "synthetic"
+    G = g.G
+    best, hp = None, None
+    for _ in range(2):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        ex = hg.HyperExtractor.from_arrays(host["read_idx"], host["contig_idx"], host["mapq"], g.contig_idx, g.contigsizes,
+                                           min_quality=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
+                                           max_order=PARAMS["max_order"], edge_length=0)
+        hp = HyperPartition(ex.edges, sizes, k=[G], alleletable=AT(), min_contacts=PARAMS["min_contacts"],
+                            min_weight=PARAMS["min_weight"], min_cis_weight=20, resolution1=-1, init_resolution1=1.0,
+                            min_scaffold_length=2e6, allelic_factor=0, cross_allelic_factor=0)
+        hp.single_partition(k=G, is_kprune=True)
+        torch.cuda.synchronize(); dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    idx = {nm: i for i, nm in enumerate(names)}
+    mem = np.full(len(names), -1)
+    for gi, grp in enumerate(hp.K):
+        for v in grp:
+            mem[idx[hp.vertices[v]]] = gi
+    ok = mem >= 0
+    return {"wall_s": best, "groups": len(hp.K), "ari_vs_planted": float(co.ari(mem[ok], g.group[ok])),
+            "api": "HyperExtractor.from_arrays -> HyperPartition(alleletable=...).single_partition(k, is_kprune=True), "
+                   "resolution auto-search; host table in, groups out"}
+
+
 def cpu_baseline(cfg, g, t, n_sample):
     """the oracle (numpy/scipy port of the reference path) on the first n_sample concatemers of the same
     table, one core."""
@@ -406,6 +447,8 @@ def run_own(args):
                       "host_input_bytes_per_step": h2d, "host_pack_threads": Dm._pack_threads(),
                       "ms_per_step": dt * 1e3, "ms_each": each, "stages_ms_synchronised": stages_e2e, "api": "HyperExtractor.from_arrays -> HyperGraph.incidence_matrix -> "
                                                       "HyperGraph.clique_expansion_init -> scipy csr (host)"}
+        if not args.no_partition and cfg["kind"] == "porec" and "hyperpartition" in out:
+            out["hyperpartition"]["api"] = api_partition(cfg, g, host)
         t = {k: v.to(dev) for k, v in host.items()} if not args.no_cpu_baseline else None
     if world > 1 and not args.no_e2e:
         # every rank feeds its own shard from pinned host memory through the device-module API (chunked H2D under the
