@@ -89,6 +89,8 @@ class HyperPartition:
         self.k = k
         self.fasta = fasta
         self._kph = None               # in-process kprune result; its name-keyed table is built only when asked for
+        self._prune_src = None         # ... and so is its index-space frame (`prune_pair_df`)
+        self._prune_pair_df = None
         self.prunetable = prunetable
         self.alleletable = alleletable
         self.normalize = normalize
@@ -248,11 +250,24 @@ class HyperPartition:
         _, _, kph = self.get_prune_pairs_kprune()
         self._kph = kph
         self._prunetable = None
-        df = _prune_frame(kph)
-        self.prune_pair_df = df
-        c1, c2, t0 = df['contig1'].to_numpy(), df['contig2'].to_numpy(), df['type'].to_numpy() == 0
-        self.P_allelic_idx = [pd.Series(c1[t0]), pd.Series(c2[t0])]
-        self.P_weak_idx = [pd.Series(c1[~t0]), pd.Series(c2[~t0])]
+        self._prune_pair_df, self._prune_src = None, kph
+        al, wk = kph.allelic_pairs, kph.weak_pairs
+        sw = wk[:, 0] != wk[:, 1]
+        self.P_allelic_idx = [pd.Series(np.concatenate([al[:, 0], al[:, 1]])), pd.Series(np.concatenate([al[:, 1], al[:, 0]]))]
+        self.P_weak_idx = [pd.Series(np.concatenate([wk[:, 0], wk[sw, 1]])), pd.Series(np.concatenate([wk[:, 1], wk[sw, 0]]))]
+
+    @property
+    def prune_pair_df(self):
+        """symmetric index-space prune pairs (the frame get_prune_pairs returns); after an in-process kprune it is built
+        on first use -- the partition itself only needs P_allelic_idx / P_weak_idx."""
+        if self._prune_pair_df is None and self._prune_src is not None:
+            self._prune_pair_df = _prune_frame(self._prune_src)
+            self._prune_src = None
+        return self._prune_pair_df
+
+    @prune_pair_df.setter
+    def prune_pair_df(self, value):
+        self._prune_pair_df, self._prune_src = value, None
 
     # -- hyperpartition.py:4012-4044
     def filter_cluster(self, verbose=1):

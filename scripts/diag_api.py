@@ -66,5 +66,5 @@ pr.enable()
 run()
 pr.disable()
 s = io.StringIO()
-pstats.Stats(pr, stream=s).sort_stats("cumulative").print_stats(45)
+pstats.Stats(pr, stream=s).sort_stats(os.environ.get("SORT", "cumulative")).print_stats(45)
 print(s.getvalue()[:9000])
