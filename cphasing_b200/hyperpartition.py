@@ -358,7 +358,7 @@ class HyperPartition:
         A = _A
         self.K = list(map(list, self.K))
         self.K = self.filter_cluster()
-        vertices_idx_sizes = pd.DataFrame(self.vertices_idx_sizes, index=['length']).T
+        vertices_idx_sizes = pd.DataFrame({'length': pd.Series(self.vertices_idx_sizes)})   # = DataFrame(d, index=['length']).T, without 1 column per contig
         if k and len(self.K) > k:                                                          # :1148-1178
             logger.info(f"Merging {len(self.K)} groups into {k} groups ...")
             self.K = HyperPartition._merge(A, self.K, vertices_idx_sizes, k, allelic_idx_set=set(),
@@ -400,7 +400,7 @@ class HyperPartition:
             self.vertices = self.vertices[retain_idx]
             logger.info(f"Removed {raw_contig_counts - len(retain_idx):,} contigs that self edge weight < "
                         f"{self.min_cis_weight} (--min-cis-weight).")
-        vertices_idx_sizes = pd.DataFrame(self.vertices_idx_sizes, index=['length']).T
+        vertices_idx_sizes = pd.DataFrame({'length': pd.Series(self.vertices_idx_sizes)})   # = DataFrame(d, index=['length']).T, without 1 column per contig
         A = HyperGraph.normalize_adjacency_matrix(A, self.NW) if self.NW is not None else A
         allelic_idx_set = None
         if self.merge_use_allele:                                                          # :1794-1896 (no fasta branch)
@@ -512,7 +512,7 @@ class HyperPartition:
             self.H, self.vertices = self.get_hypergraph()
             raw_A = HyperGraph.clique_expansion_init(self.H, min_weight=self.min_weight, use_high_order=False)
             self.NW = self.get_normalize_weight() if self.normalize else None
-            vertices_idx_sizes = pd.DataFrame(self.vertices_idx_sizes, index=['length']).T
+            vertices_idx_sizes = pd.DataFrame({'length': pd.Series(self.vertices_idx_sizes)})   # = DataFrame(d, index=['length']).T, without 1 column per contig
             vi = self.vertices_idx
             removed = set(self.HG.remove_contigs)
             self.K = [[vi[y] for y in grp if y not in removed and y in vi] for grp in tmp_K]

@@ -80,7 +80,13 @@ def kprune_arrays(A, allele_pairs, max_alleles=1):
         if selfp.size:
             n = max(a.n, 1)
             pos = np.searchsorted(weak[:, 0] * n + weak[:, 1], selfp[:, 0] * n + selfp[:, 1])
-            weak = np.insert(weak, pos, selfp, axis=0)
+            out = np.empty((len(weak) + len(selfp), 2), dtype=np.int64)        # merge of two sorted lists
+            at = pos + np.arange(len(selfp))
+            keep = np.ones(len(out), dtype=bool)
+            keep[at] = False
+            out[at] = selfp
+            out[keep] = weak
+            weak = out
     return allelic, weak
 
 

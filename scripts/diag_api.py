@@ -68,3 +68,34 @@ pr.disable()
 s = io.StringIO()
 pstats.Stats(pr, stream=s).sort_stats(os.environ.get("SORT", "cumulative")).print_stats(45)
 print(s.getvalue()[:9000])
+
+# wall-clock (synchronised) per major call of one more run
+import functools
+from cphasing_b200 import hyperpartition as _hpm, kprune as _kpm
+from cphasing_b200.algorithms import hypergraph as _ahm
+acc = {}
+
+
+def timed(owner, name, label=None):
+    raw = getattr(owner, name)            # a staticmethod comes back as the plain function
+
+    @functools.wraps(raw)
+    def w(*a, **k):
+        torch.cuda.synchronize(); t0 = time.perf_counter()
+        r = raw(*a, **k)
+        torch.cuda.synchronize()
+        acc[label or name] = acc.get(label or name, 0.0) + (time.perf_counter() - t0) * 1e3
+        return r
+    setattr(owner, name, staticmethod(w) if isinstance(owner.__dict__.get(name), staticmethod) else w)
+
+
+timed(_hpm.HyperPartition, "kprune")
+timed(_hpm, "IRMM")
+timed(_ahm.HyperGraph, "clique_expansion_init")
+timed(_ahm.HyperGraph, "filter_adjacency_matrix")
+timed(_hpm.HyperPartition, "filter_cluster")
+timed(_kpm, "kprune_arrays")
+timed(_kpm, "kprune_device")
+t0 = time.perf_counter()
+run()
+print("timed run total %.1f ms:" % ((time.perf_counter() - t0) * 1e3), {k: round(v, 1) for k, v in acc.items()})
