@@ -197,17 +197,20 @@ def _host_columns(read_idx, contig_idx, mapq):
 
 
 def _pack_threads():
-    """host threads for the packed transfer: STREAM_PACK_THREADS, or (auto) the cores of this process less two, shared
-    between the ranks of the node; with fewer than 8 the re-encoding is slower than sending the columns as they are
-    (measured: 4 threads 82 ms, 8 threads 48 ms, 14 threads 35 ms against 47 ms unpacked for 286 M records)."""
+    """host threads for the packed transfer: STREAM_PACK_THREADS, or (auto) the cores of this process less two.  The
+    re-encoding is bound by host memory bandwidth (about 17 B of traffic per record against 9 B for the plain copy), so
+    it only pays when one rank has the host to itself and enough cores: measured for 286 M records on a 16-core box,
+    4 threads 82 ms, 8 threads 48 ms, 14 threads 33 ms against 47 ms unpacked; with two ranks on one host (11 threads
+    each) 60.8 ms packed against 53.9 ms unpacked -> several ranks per node send the columns as they are."""
     if STREAM_PACK_THREADS >= 0:
         return int(STREAM_PACK_THREADS)
+    if int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
+        return 0
     try:
         cores = len(os.sched_getaffinity(0))
     except AttributeError:
         cores = os.cpu_count() or 1
-    ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
-    t = min(16, (cores - 2) // ranks)
+    t = min(16, cores - 2)
     return t if t >= 8 else 0
 
 
