@@ -15,6 +15,7 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <cstring>
 #include <emmintrin.h>
 #include <mutex>
@@ -982,6 +983,7 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
         bool abort = false;
     } sh;
     std::vector<std::thread> workers;
+    u32 raw_every = 0;
     if (packed) {
         ring_lock.lock();                       // one packed call at a time owns the pinned ring
         const size_t want = slot_layout.bytes * PK_NSLOT;
@@ -994,10 +996,32 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
         }
         sh.state.assign(nchunks, 0);
         unsigned char* ring = g_pk_host;
+        // Re-encoding is bound by host memory bandwidth (17 B of traffic per record) and leaves PCIe a third idle; a plain
+        // copy costs 9 B of host reads per record but 9 B on PCIe.  Sending every k-th chunk as it is (pinned columns only)
+        // moves load from the host's memory system to PCIe.  Measured on workload C, ms per end-to-end step without the
+        // partition tail: none 39.0, every 6th 38.2, 5th 37.3, 4th 37.9, 3rd 42.8, 2nd 45.8 -- but 41.7 for every 5th in
+        // the full default bench run against 39.2-39.4 for none, so it is OFF unless CPH_PACK_RAW_EVERY asks for it.
+        {
+            cudaPointerAttributes pa;
+            bool pinned = true;
+            for (const void* q : {(const void*)h_read_idx, (const void*)h_contig_idx, (const void*)h_mapq}) {
+                if (cudaPointerGetAttributes(&pa, q) != cudaSuccess || pa.type != cudaMemoryTypeHost) pinned = false;
+            }
+            (void)cudaGetLastError();
+            if (const char* e = getenv("CPH_PACK_RAW_EVERY")) raw_every = pinned ? (u32)atoi(e) : 0u;      // tuning knob
+        }
         auto work = [&, ring]() {
             for (;;) {
                 const u32 k = sh.next.fetch_add(1);
                 if (k >= nchunks) return;
+                if (raw_every && k % raw_every == raw_every - 1) {       // this chunk travels as it is (see raw_every)
+                    {
+                        std::lock_guard<std::mutex> lk(sh.m);
+                        sh.state[k] = 2;
+                    }
+                    sh.cv.notify_all();
+                    continue;
+                }
                 {
                     std::unique_lock<std::mutex> lk(sh.m);
                     sh.cv.wait(lk, [&] { return sh.abort || sh.released + PK_NSLOT > k; });
