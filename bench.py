@@ -42,6 +42,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-partition", action="store_true", help="skip the kprune + clustering tail (hyperpartition wall s)")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra workloads (D and E shards) after the headline one")
+    ap.add_argument("--extra", default="D,E", help="comma-separated extra workloads, each at 1/8 of its named size per GPU")
+    ap.add_argument("--extra-steps", type=int, default=5)
     return ap.parse_args()
 
 
@@ -283,32 +286,241 @@ def api_partition(cfg, g, host):
                    "resolution auto-search; host table in, groups out"}
 
 
-def cpu_baseline(cfg, g, t, n_sample):
-    """the oracle (numpy/scipy port of the reference path) on the first n_sample concatemers of the same
-    table, one core."""
-    import torch
+def reference_module():
+    """the UNMODIFIED reference's ``cphasing.algorithms.hypergraph`` (baseline/_ref, polars/igraph/... stubbed -- see
+    baseline/ref_loader.py) or None when the install did not travel."""
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import ref_loader
+        if not ref_loader.available():
+            return None
+        import logging
+        ah = ref_loader.load()
+        logging.getLogger().setLevel(logging.ERROR)
+        logging.getLogger("cphasing").setLevel(logging.ERROR)
+        return ah
+    except Exception as e:                                   # noqa: BLE001
+        print(f"[bench] reference import failed ({e!r}); CPU legs fall back to the oracle port", file=sys.stderr)
+        return None
+
+
+def cpu_path(cfg, g, t, ah, counts=False, high_order=True):
+    """the reference's CPU path on a host table `t` (numpy columns): table -> triplets (oracle port of the polars
+    group-by, hypergraph.py:1395-1481 -- polars is not installable) -> HyperGraph.incidence_matrix(min_contacts) ->
+    clique_expansion_init(min_weight) with the REFERENCE's own classes when `ah` is given, else the oracle's
+    restatement.  -> (H, A, seconds per stage)"""
     from oracle import hypergraph_oracle as orc
+    tm = {}
+    t0 = time.perf_counter()
     if cfg["kind"] == "pairs":
-        k = min(n_sample, cfg["m"])
-        c1 = t["chrom1"][:k].cpu().numpy(); c2 = t["chrom2"][:k].cpu().numpy(); q = t["mapq"][:k].cpu().numpy()
-        t0 = time.perf_counter()
-        r, c, cnt, mq = orc.pairs_edges(c1, c2, q, min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
+        r, c, cnt, mq = orc.pairs_edges(t["chrom1"], t["chrom2"], t["mapq"], min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
+    else:
+        r, c, cnt, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=PARAMS["min_mapq"],
+                                        min_order=PARAMS["min_order"], max_order=PARAMS["max_order"], n_contigs=g.n)
+    tm["triplets"] = time.perf_counter() - t0; t0 = time.perf_counter()
+    if ah is not None:
+        edges = ah.HyperEdges(idx=g.contig_idx, row=r, col=c, count=cnt, contigsizes=g.contigsizes, mapq=mq)
+        HG = ah.HyperGraph(edges, min_quality=PARAMS["min_mapq"], mapq_filter=False)     # hyperpartition.py:249
+        H = HG.incidence_matrix(min_contacts=PARAMS["min_contacts"])
+        tm["incidence"] = time.perf_counter() - t0; t0 = time.perf_counter()
+        A = ah.HyperGraph.clique_expansion_init(H, min_weight=PARAMS["min_weight"], use_high_order=high_order)
+    else:
+        rr, cc, kk, ncol = orc.hypergraph_get_data(r, c, cnt, mq, PARAMS["min_mapq"], mapq_filter=False)
+        H, _, _ = orc.incidence_matrix(rr, cc, kk, g.n, ncol, PARAMS["min_contacts"])
+        tm["incidence"] = time.perf_counter() - t0; t0 = time.perf_counter()
+        A = orc.clique_expansion(H, min_weight=PARAMS["min_weight"], dtype=np.float32, use_high_order=high_order)
+    tm["expansion"] = time.perf_counter() - t0
+    return H, A, tm, len(r)
+
+
+def sample_of(cfg, t, n_sample):
+    """first n_sample concatemers of the device table -> (host numpy columns, device slices, k)"""
+    import torch
+    k = min(n_sample, cfg["m"])
+    if cfg["kind"] == "pairs":
+        cut = k
     else:
         rid = t["read_idx"].view(torch.int32)
         first = int(rid[0].item())
-        k = min(n_sample, cfg["m"])
         cut = int(torch.searchsorted(rid, torch.tensor([first + k], dtype=torch.int32, device=rid.device)).item())
-        ri = t["read_idx"][:cut].cpu().numpy(); ci = t["contig_idx"][:cut].cpu().numpy(); q = t["mapq"][:cut].cpu().numpy()
-        t0 = time.perf_counter()
-        r, c, cnt, mq = orc.porec_edges(ri, ci, q, min_mapq=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
-                                        max_order=PARAMS["max_order"], n_contigs=g.n)
-    rr, cc, kk, ncol = orc.hypergraph_get_data(r, c, cnt, mq, PARAMS["min_mapq"], mapq_filter=False)
-    H, _, _ = orc.incidence_matrix(rr, cc, kk, g.n, ncol, PARAMS["min_contacts"])
-    A = orc.clique_expansion(H, min_weight=PARAMS["min_weight"], dtype=np.float32)     # the reference's own float32 path
-    dt = time.perf_counter() - t0
-    return {"value": k / dt, "unit": "concatemers/s", "cores": 1, "kind": "port",
-            "sample": f"first {k} concatemers of the same table ({len(r)} H entries), oracle/hypergraph_oracle.py "
-                      f"(numpy+scipy restatement; polars/MKL absent), {dt:.1f} s"}, A
+    dev = {kk: v[:cut] for kk, v in t.items()}
+    host = {kk: v.cpu().numpy() for kk, v in dev.items()}
+    return host, dev, k
+
+
+def cpu_baseline(cfg, g, host, k, ah):
+    """the reference's CPU path on the first k concatemers of the benched table, one core (scipy's csr_matmat is
+    single-threaded; MKL and polars are absent)."""
+    H, A, tm, ntrip = cpu_path(cfg, g, host, ah)
+    dt = sum(tm.values())
+    kind = "reference" if ah is not None else "port"
+    what = ("the reference's own HyperGraph.incidence_matrix + clique_expansion_init (baseline/_ref, scipy float32) after "
+            "the oracle port of its polars group-by (polars not installable)") if ah is not None else \
+           "oracle/hypergraph_oracle.py (numpy+scipy restatement; the reference install is absent)"
+    return {"value": k / dt, "unit": "concatemers/s", "cores": 1, "kind": kind,
+            "seconds": {a: round(b, 3) for a, b in tm.items()},
+            "sample": f"first {k} concatemers of the same table ({ntrip} H entries): {what}, {dt:.1f} s"}, H, A
+
+
+def _canon(M):
+    M = M.tocsr().copy()
+    M.sort_indices()
+    return M
+
+
+def parity_check(D, cfg, g, host, dev_t, H_cpu, A_cpu, ah):
+    """the CUDA path on the SAME sample the CPU baseline just computed, compared output by output:
+    H and the integer contact-count matrix bit for bit, the weighted A against the fp64 oracle (1e-6, north_star) and
+    against the reference's float32 result (pattern; values to float32 accumulation error)."""
+    from scipy.sparse import csr_matrix
+    from oracle import hypergraph_oracle as orc
+    if cfg["kind"] == "pairs":
+        raw = D.pairs_to_edges(dev_t["chrom1"], dev_t["chrom2"], dev_t["mapq"], g.n, min_mapq=PARAMS["min_mapq"])
+    else:
+        raw = D.porec_to_edges(dev_t["read_idx"], dev_t["contig_idx"], dev_t["mapq"], g.n, min_mapq=PARAMS["min_mapq"],
+                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"])
+    H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0)
+    Hs = _canon(csr_matrix(((D.to_host(H.pk).view(np.uint32) & 0xFFFFFF).astype(np.float32), D.to_host(H.indices),
+                            D.to_host(H.indptr)), shape=(H.n_rows, H.n_cols)))
+    Hc = _canon(H_cpu)
+    out = {"sample_concatemers": None, "H_shape": list(Hs.shape), "H_nnz": int(Hs.nnz)}
+    out["H_bit_exact"] = bool(Hs.shape == Hc.shape and np.array_equal(Hs.indptr, Hc.indptr)
+                              and np.array_equal(Hs.indices, Hc.indices) and np.array_equal(Hs.data, Hc.data))
+    # integer contact counts (use_high_order=False): bit-exact against the CPU integer matrix
+    Au, acc = D.clique_expansion(H, use_high_order=False, min_weight=PARAMS["min_weight"], want32=False, want64=True)
+    Aus = _canon(csr_matrix((D.to_host(Au.data64), D.to_host(Au.indices), D.to_host(Au.indptr)), shape=(H.n_rows,) * 2))
+    if ah is not None:
+        Auc = ah.HyperGraph.clique_expansion_init(H_cpu, min_weight=PARAMS["min_weight"], use_high_order=False)
+    else:
+        Auc = orc.clique_expansion(H_cpu, use_high_order=False, min_weight=PARAMS["min_weight"])
+    Auc = _canon(Auc)
+    out["counts_bit_exact"] = bool(acc.frac_bits == 0 and np.array_equal(Aus.indptr, Auc.indptr)
+                                   and np.array_equal(Aus.indices, Auc.indices)
+                                   and np.array_equal(Aus.data.astype(np.int64), np.rint(Auc.data).astype(np.int64)))
+    out["counts_nnz"] = int(Aus.nnz)
+    del Au, acc
+    # weighted A
+    A, _ = D.clique_expansion(H, use_high_order=True, min_weight=PARAMS["min_weight"], want32=False, want64=True)
+    As = _canon(csr_matrix((D.to_host(A.data64), D.to_host(A.indices), D.to_host(A.indptr)), shape=(H.n_rows,) * 2))
+    A64 = _canon(orc.clique_expansion(Hc.astype(np.float64), min_weight=PARAMS["min_weight"], dtype=np.float64))
+    thr = PARAMS["min_weight"]
+
+    def compare(X, Y, near):
+        """-> (pattern_equal, entries present on one side only that are NOT within `near` of the threshold, max rel)"""
+        same = X.nnz == Y.nnz and np.array_equal(X.indptr, Y.indptr) and np.array_equal(X.indices, Y.indices)
+        if same:
+            rel = float(np.max(np.abs(X.data - Y.data) / np.maximum(np.abs(Y.data), 1e-300))) if X.nnz else 0.0
+            return True, 0, rel
+        d = (X - Y).tocsr()
+        Xp = X.copy(); Xp.data[:] = 1
+        Yp = Y.copy(); Yp.data[:] = 1
+        only = (Xp - Yp).tocsr(); only.eliminate_zeros()       # +1: only in X, -1: only in Y
+        oc = only.tocoo()
+        vals = np.where(oc.data > 0, np.asarray(X[oc.row, oc.col]).ravel(), np.asarray(Y[oc.row, oc.col]).ravel())
+        bad = int(np.sum(np.abs(vals - thr) > near * thr))
+        both = Xp.multiply(Yp).tocsr()
+        Xi = X.multiply(both).tocsr(); Yi = Y.multiply(both).tocsr()
+        Xi.sort_indices(); Yi.sort_indices()
+        rel = float(np.max(np.abs(Xi.data - Yi.data) / np.maximum(np.abs(Yi.data), 1e-300))) if Xi.nnz else 0.0
+        return False, bad, rel
+    pe, bad, rel = compare(As, A64, 1e-9)
+    out.update(weighted_nnz=int(As.nnz), pattern_equal=bool(pe), weighted_max_rel=rel, weighted_tol=1e-6,
+               weighted_against="oracle fp64 restatement of algorithms/hypergraph.py:372-455 on the CPU H")
+    pe32, bad32, rel32 = compare(As, _canon(A_cpu).astype(np.float64), 1e-4)
+    out.update(vs_cpu_float32={"pattern_equal": bool(pe32), "entries_off_threshold": bad32, "max_rel": rel32,
+                               "nnz_cpu": int(A_cpu.nnz),
+                               "note": "the CPU side multiplies sqrt-scaled float32 operands and accumulates in float32 "
+                                       "(scipy csr_matmat, algorithms/hypergraph.py:418-446): cells whose exact value equals "
+                                       "min_weight fall on either side of the cut by rounding, and long sums carry ~1e-4 "
+                                       "relative float32 error; informational except entries_off_threshold"})
+    out["ok"] = bool(out["H_bit_exact"] and out["counts_bit_exact"] and pe and bad == 0 and rel <= 1e-6 and bad32 == 0
+                     and rel32 <= 1e-3)
+    return out
+
+
+def timed_run(D, _lib, name, cfg, g, t, steps, warmup, world, rank, local, dev, barrier, clocks_on=True):
+    """W untimed + K timed passes of the device-resident step; CUDA events, max over ranks -> (json fields, raw, H, A)"""
+    import torch
+    import torch.distributed as dist
+    n_rec = int(next(iter(t.values())).numel())
+    for _ in range(max(warmup, 3)):
+        ev = []
+        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
+    barrier()
+    clocks = Clocks(local)
+    if rank == 0 and clocks_on:
+        clocks.start()
+    l0 = _lib.launches()
+    all_ev = []
+    t_start = torch.cuda.Event(enable_timing=True); t_end = torch.cuda.Event(enable_timing=True)
+    barrier()
+    t_start.record()
+    for _ in range(steps):
+        ev = []
+        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
+        all_ev.append(ev)
+    t_end.record()
+    barrier()
+    launches = _lib.launches() - l0
+    ms_total = t_start.elapsed_time(t_end)
+    if world > 1:
+        mt = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms_total = float(mt.item())
+    clk = clocks.stop() if (rank == 0 and clocks_on) else None
+    ms_step = ms_total / steps
+    stages = {}
+    for ev in all_ev:
+        for (n0, e0), (n1, e1) in zip(ev[:-1], ev[1:]):
+            stages.setdefault(n1, []).append(e0.elapsed_time(e1))
+    stages = {k: sum(v) / len(v) for k, v in stages.items()}
+
+    # roofline of the DOMINANT kernel (profiles/: the group-by kernel of cph_porec_to_edges on Pore-C tables; on pairs
+    # tables and at high order the expansion kernel).  ALGORITHMIC bytes (SURVEY.md 8d, DESIGN.md 4):
+    #   group-by kernel: 9 B per alignment record read + 8 B per surviving (read, contig) entry written
+    #   expansion kernel: 8 B per H entry read (row + packed count/degree); its work figure is the pair updates
+    # duration = CUDA events around the C-ABI call that launches it, averaged over the timed steps.
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    nnzH, nnzA, n_rows = H.nnz, A.nnz, H.n_rows
+    acc_ms = stages.get("accumulate", float("nan"))
+    edges_ms = stages.get("edges", float("nan"))
+    stage1_bytes = 9 * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
+    stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
+    s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
+    s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
+    xname = "expansion kernel(s) (cph_expand_accumulate_*)"
+    per_kernel = {xname: {"bytes": 8 * nnzH, "ms": acc_ms, "GBps": 8 * nnzH / acc_ms / 1e6, "frac": 8 * nnzH / acc_ms / 1e6 / peak}}
+    gname = "porec_tile_kernel (cph_porec_to_edges)" if cfg["kind"] != "pairs" else "pairs_flag/emit_kernel (cph_pairs_to_edges)"
+    per_kernel[gname] = {"bytes": 9 * n_rec + 8 * raw.nnz, "ms": edges_ms, "GBps": (9 * n_rec + 8 * raw.nnz) / edges_ms / 1e6,
+                         "frac": (9 * n_rec + 8 * raw.nnz) / edges_ms / 1e6 / peak}
+    traffic = None
+    if cfg["kind"] == "pairs" or acc_ms > edges_ms:
+        kname, kbytes, kms = xname, 8 * nnzH, acc_ms
+    else:
+        kname, kbytes, kms = gname, 9 * n_rec + 8 * raw.nnz, edges_ms
+        # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/)
+        traffic = NCU_TRAFFIC.get((name, cfg["m"]))
+    roof = {"bound": "hbm", "kernel": kname, "achieved": kbytes / kms / 1e6, "peak": peak, "unit": "GB/s",
+            "frac": kbytes / kms / 1e6 / peak, "traffic": traffic,
+            "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
+            "algorithmic_bytes_per_launch": kbytes, "kernel_ms": kms, "kernels": per_kernel,
+            "stage1_GBps": stage1_bytes / s1_ms / 1e6 if s1_ms else None,
+            "stage2_GBps": stage2_bytes / s2_ms / 1e6 if s2_ms else None}
+    out = {"metric": "concatemers/sec (H build + H*W*H^T)", "value": cfg["m"] * world / (ms_step / 1e3),
+           "unit": "concatemers/s", "n_gpus": world, "steps": steps, "warmup": max(warmup, 3),
+           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 fixed-point / f64",
+           "data": "synthetic", "gpu_launches": launches,
+           "config": {"workload": f"{name}: n={cfg['n']} contigs, m={cfg['m']} concatemers/GPU x {world} GPU, law={cfg['law']}, "
+                                  f"kind={cfg['kind']}", "records_per_gpu": n_rec, "nnz_H": nnzH, "nnz_A": nnzA,
+                      "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
+                      "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
+           "stages_ms": stages, "roofline": roof, "clocks": clk}
+    return out, raw, H, A
 
 
 def run_own(args):
@@ -326,7 +538,6 @@ def run_own(args):
     from cphasing_b200 import _lib, device as D
     name, cfg = workload(args)
     g, t = gen_table(cfg, rank, dev)
-    n_rec = int(next(iter(t.values())).numel())
     torch.cuda.synchronize()
 
     def barrier():
@@ -334,80 +545,8 @@ def run_own(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
-        ev = []
-        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
-    barrier()
-    clocks = Clocks(local)
-    if rank == 0:
-        clocks.start()
-    l0 = _lib.launches()
-    all_ev = []
-    t_start = torch.cuda.Event(enable_timing=True); t_end = torch.cuda.Event(enable_timing=True)
-    barrier()
-    t_start.record()
-    for _ in range(args.steps):
-        ev = []
-        raw, H, A = device_step(D, cfg, g, t, ev, world, rank)
-        all_ev.append(ev)
-    t_end.record()
-    barrier()
-    launches = _lib.launches() - l0
-    ms_total = t_start.elapsed_time(t_end)
-    if world > 1:
-        mt = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-        ms_total = float(mt.item())
-    clk = clocks.stop() if rank == 0 else None
-    ms_step = ms_total / args.steps
-    stages = {}
-    for ev in all_ev:
-        for (n0, e0), (n1, e1) in zip(ev[:-1], ev[1:]):
-            stages.setdefault(n1, []).append(e0.elapsed_time(e1))
-    stages = {k: sum(v) / len(v) for k, v in stages.items()}
-
-    # roofline of the DOMINANT kernel (profiles/r1j_launch_summary.txt: porec_tile_kernel = 42 % of the step on Pore-C
-    # tables; on pairs tables the expansion's expand_diag_kernel).  ALGORITHMIC bytes:
-    #   porec_tile_kernel: 9 B per alignment record read + 8 B per surviving (read, contig) entry written
-    #   expand_diag_kernel: 8 B per H entry read (row + packed count/degree); its work figure is the pair REDs
-    # duration = CUDA events around the C-ABI call that launches it, averaged over the timed steps.
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    peak = float(peaks.get("hbm_gbs", 6650.0))
-    nnzH, nnzA, n_rows = H.nnz, A.nnz, H.n_rows
-    acc_ms = stages.get("accumulate", float("nan"))
-    edges_ms = stages.get("edges", float("nan"))
-    stage1_bytes = 9 * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
-    stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
-    s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
-    s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
-    per_kernel = {"expand_diag_kernel (cph_expand_accumulate_diag)":
-                  {"bytes": 8 * nnzH, "ms": acc_ms, "GBps": 8 * nnzH / acc_ms / 1e6, "frac": 8 * nnzH / acc_ms / 1e6 / peak}}
-    if cfg["kind"] == "pairs":
-        kname, kbytes, kms, traffic = "expand_diag_kernel (cph_expand_accumulate_diag)", 8 * nnzH, acc_ms, None
-    else:
-        kname, kbytes, kms = "porec_tile_kernel (cph_porec_to_edges)", 9 * n_rec + 8 * raw.nnz, edges_ms
-        # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/r1j_ncu_full_top3.txt)
-        traffic = NCU_TRAFFIC.get((name, cfg["m"]))
-        per_kernel[kname] = {"bytes": kbytes, "ms": kms, "GBps": kbytes / kms / 1e6, "frac": kbytes / kms / 1e6 / peak}
-    roof = {"bound": "hbm", "kernel": kname, "achieved": kbytes / kms / 1e6, "peak": peak, "unit": "GB/s",
-            "frac": kbytes / kms / 1e6 / peak, "traffic": traffic,
-            "peak_source": "MEASURED_PEAKS.json hbm_gbs (measured copy)" if peaks else "fallback 6650",
-            "algorithmic_bytes_per_launch": kbytes, "kernel_ms": kms, "kernels": per_kernel,
-            "stage1_GBps": stage1_bytes / s1_ms / 1e6 if s1_ms else None,
-            "stage2_GBps": stage2_bytes / s2_ms / 1e6 if s2_ms else None}
-    out = {"metric": "concatemers/sec (H build + H*W*H^T)", "value": cfg["m"] * world / (ms_step / 1e3),
-           "unit": "concatemers/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-           "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 fixed-point / f64",
-           "data": "synthetic", "gpu_launches": launches,
-           "config": {"workload": f"{name}: n={cfg['n']} contigs, m={cfg['m']} concatemers/GPU x {world} GPU, law={cfg['law']}, "
-                                  f"kind={cfg['kind']}", "records_per_gpu": n_rec, "nnz_H": nnzH, "nnz_A": nnzA,
-                      "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
-                      "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
-           "stages_ms": stages, "roofline": roof, "clocks": clk}
+    out, raw, H, A = timed_run(D, _lib, name, cfg, g, t, args.steps, args.warmup, world, rank, local, dev, barrier)
+    ms_step = out["ms_per_step"]
     if not args.no_partition:
         tail = partition_tail(D, cfg, g, H, A, world=world, rank=rank)
         barrier()
@@ -487,51 +626,89 @@ def run_own(args):
                       "api": "per rank: device.porec_to_edges(host columns) -> device.incidence (row-sum all-reduce) -> "
                              "device.expand_accumulate -> triangle reduce-scatter/all-gather -> device.expand_emit; "
                              "rank 0 reads CSR(A) back"}
+    parity_ok = True
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cb, _ = cpu_baseline(cfg, g, t, args.cpu_sample)
+        ah = reference_module()
+        host_s, dev_s, k = sample_of(cfg, t, args.cpu_sample)
+        cb, Hc, Ac = cpu_baseline(cfg, g, host_s, k, ah)
         out["cpu_baseline"] = cb
+        # parity INSIDE the bench: the CUDA path on the sample the CPU leg just computed (rc != 0 on mismatch)
+        par_ = parity_check(D, cfg, g, host_s, dev_s, Hc, Ac, ah)
+        par_["sample_concatemers"] = k
+        par_["cpu_side"] = cb["kind"]
+        out["parity"] = par_
+        parity_ok = par_["ok"]
+    # ---- extra workloads, driver-timed next to the headline one: D (north_star's 8-GPU config: n = 20k, 62.5 M
+    # concatemers per GPU = 500 M at N = 8) and E (high-order HiFi-C: n = 10k, order <= 50, 25 M per GPU = 200 M at N = 8)
+    if not args.no_extra and args.workload is None and not args.m:
+        import gc
+        from cphasing_b200 import synth
+        raw = H = A = t = host = host_s = dev_s = Hc = Ac = Ah = None       # drop the headline workload's buffers
+        gc.collect()
+        _lib.release_workspace(); torch.cuda.empty_cache()
+        extra = {}
+        for xn in args.extra.split(","):
+            xcfg = dict(synth.CONFIGS[xn])
+            xcfg["m"] = xcfg["m"] // 8
+            try:
+                xg, xt = gen_table(xcfg, rank, dev)
+                xo, xraw, xH, xA = timed_run(D, _lib, xn, xcfg, xg, xt, args.extra_steps, 3, world, rank, local, dev, barrier,
+                                             clocks_on=False)
+                del xraw, xt
+                if not args.no_partition:
+                    tail = partition_tail(D, xcfg, xg, xH, xA, reps=1, world=world, rank=rank)
+                    barrier()
+                    if rank == 0:
+                        tail["wall_s"] = (xo["ms_per_step"] + tail["kprune_ms"] + tail["cluster_ms"]) / 1e3
+                        xo["hyperpartition"] = tail
+                for k_ in ("metric", "unit", "higher_is_better", "scaling", "vs_baseline", "data", "clocks", "warmup"):
+                    xo.pop(k_, None)
+                extra[xn] = xo
+                del xH, xA, xg
+            except Exception as e:                                   # noqa: BLE001
+                extra[xn] = {"error": repr(e)[:300]}
+            gc.collect()
+            _lib.release_workspace(); torch.cuda.empty_cache()
+        out["extra"] = extra
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+    if not parity_ok:
+        print("[bench] PARITY MISMATCH between the CUDA path and the CPU path on the sample", file=sys.stderr)
+        sys.exit(3)
 
 
 # ------------------------------------------------------------------------------------------------
-# reference arm: the reference's CPU algorithm (oracle port; the reference itself is pure Python over
-# polars / scipy / igraph and cannot be installed or travel -- DESIGN.md) on the host cores
+# reference arm: the reference's own CPU implementation of the path on the host cores.  The reference is pure Python
+# over polars / scipy / igraph; it is installed UNMODIFIED under baseline/_ref (pip --no-deps) and its
+# HyperEdges / HyperGraph.incidence_matrix / clique_expansion_init run as they are (scipy float32, single-threaded
+# csr_matmat -- MKL absent).  The one piece that cannot run is the polars group-by of process_pore_c_table
+# (hypergraph.py:1395-1481; polars is not in the wheelhouse): the oracle's numpy port stands in for it.  The reference
+# has no multi-core mode for this path without polars/MKL, so "all the host threads" = one independent replica of the
+# stock single-process path per core, each on its own table of the workload's shape; value = concatemers of all
+# replicas / wall time.  The same fixed sample (REF_SAMPLE concatemers per replica) is used at every N.
 # ------------------------------------------------------------------------------------------------
+REF_SAMPLE = int(os.environ.get("CPH_REF_SAMPLE", 1_000_000))
+
+
 def _ref_worker(conn, cfg, first, m):
     from cphasing_b200 import synth
-    from oracle import hypergraph_oracle as orc
-    from scipy.sparse import csr_matrix
+    ah = reference_module()
     g = synth.make_genome(cfg["n"], cfg["chromosomes"], cfg["ploidy"], cfg["seed"])
     if cfg["kind"] == "pairs":
         t = synth.pairs_table(g, m, cfg["seed"], first=first)
     else:
         t = synth.porec_table(g, m, cfg["seed"], law=cfg["law"], first=first)
-    conn.send(("ready", len(next(iter(t.values())))))
-    st = {}
+        t["read_idx"] = t["read_idx"] - np.uint32(first) if first else t["read_idx"]
+    conn.send(("ready", len(next(iter(t.values()))), ah is not None))
     while True:
         cmd = conn.recv()
         if cmd[0] == "stop":
             break
-        if cmd[0] == "phase1":      # table -> triplets -> local row sums
-            if cfg["kind"] == "pairs":
-                r, c, cnt, mq = orc.pairs_edges(t["chrom1"], t["chrom2"], t["mapq"], min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
-            else:
-                r, c, cnt, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=PARAMS["min_mapq"],
-                                                min_order=PARAMS["min_order"], max_order=PARAMS["max_order"], n_contigs=g.n)
-            c = c - first if len(c) else c
-            H, _, _ = orc.incidence_matrix(r, c, cnt, g.n, int(c.max()) + 1 if len(c) else 1, 0)
-            st["H"] = H
-            conn.send(np.asarray(H.sum(axis=1)).ravel())
-        elif cmd[0] == "phase2":    # global row filter, local column filter, partial A
-            keep = cmd[1]
-            H = st["H"][keep]
-            H = H[:, np.asarray(H.sum(axis=0)).ravel() >= 2]
-            A = orc.clique_expansion(H, min_weight=0, dtype=np.float32)
-            conn.send(A)
+        H, A, tm, ntrip = cpu_path(cfg, g, t, ah)
+        conn.send((tm, int(H.nnz), int(A.nnz)))
 
 
 def run_reference(args):
@@ -540,8 +717,12 @@ def run_reference(args):
         return
     import multiprocessing as mp
     name, cfg = workload(args)
-    cores = min(os.cpu_count() or 1, 32)
-    per = 400_000
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        cores = os.cpu_count() or 1
+    cores = max(1, min(cores, 64))
+    per = REF_SAMPLE
     m = per * cores
     ctx = mp.get_context("spawn")
     procs = []
@@ -550,42 +731,38 @@ def run_reference(args):
         p = ctx.Process(target=_ref_worker, args=(b, cfg, i * per, per), daemon=True)
         p.start()
         procs.append((p, a))
-    n_rec = sum(a.recv()[1] for _, a in procs)
+    ready = [a.recv() for _, a in procs]
+    n_rec = sum(r[1] for r in ready)
+    kind = "reference" if all(r[2] for r in ready) else "port"
 
     def step():
         for _, a in procs:
-            a.send(("phase1",))
-        rs = sum(a.recv() for _, a in procs)
-        keep = rs >= PARAMS["min_contacts"]
-        for _, a in procs:
-            a.send(("phase2", keep))
-        A = None
-        for _, a in procs:
-            P = a.recv()
-            A = P if A is None else A + P
-        A = A.tocsr()
-        A.data[A.data < np.float32(PARAMS["min_weight"])] = 0
-        A.eliminate_zeros()
-        return A
+            a.send(("step",))
+        return [a.recv() for _, a in procs]
     for _ in range(args.warmup):
         step()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        A = step()
+        res = step()
     dt = (time.perf_counter() - t0) / args.steps
     for p, a in procs:
         a.send(("stop",))
     v = m / dt
-    sample = (f"{m} concatemers ({n_rec} records) of workload {name} per step, {cores} worker processes each running "
-              f"oracle/hypergraph_oracle.py on a {per}-concatemer shard (phase 1 triplets+row sums, phase 2 partial A), "
-              f"partials summed on rank 0")
+    stage_s = {k_: round(float(np.mean([r[0][k_] for r in res])), 3) for k_ in res[0][0]}
+    what = ("the UNMODIFIED reference (baseline/_ref): HyperEdges -> HyperGraph(mapq_filter=False).incidence_matrix(25) -> "
+            "clique_expansion_init(min_weight=2.0), float32 scipy; its polars group-by replaced by the oracle's numpy port "
+            "(polars not installable)") if kind == "reference" else "oracle/hypergraph_oracle.py port (reference install absent)"
+    sample = (f"{cores} independent replicas (one per core; the path is single-threaded without polars/MKL), each "
+              f"{per} concatemers of workload {name} per step ({n_rec} records in all): {what}; mean seconds per stage "
+              f"per replica {stage_s}")
     print(json.dumps({"impl": "reference", "metric": "concatemers/sec (H build + H*W*H^T)", "value": v, "unit": "concatemers/s",
                       "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
                       "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32 (reference arithmetic)",
                       "data": "synthetic",
-                      "config": {"workload": f"{name}: n={cfg['n']} contigs, law={cfg['law']}, kind={cfg['kind']} (bounded sample)",
+                      "config": {"workload": f"{name}: n={cfg['n']} contigs, law={cfg['law']}, kind={cfg['kind']} "
+                                             f"(bounded sample: {per} concatemers x {cores} replicas per step)",
                                  "params": PARAMS},
-                      "cpu_baseline": {"value": v, "unit": "concatemers/s", "cores": cores, "kind": "port", "sample": sample},
+                      "cpu_baseline": {"value": v, "unit": "concatemers/s", "cores": cores, "kind": kind, "sample": sample},
                       "e2e": {"value": v, "unit": "concatemers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 

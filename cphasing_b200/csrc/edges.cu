@@ -253,17 +253,19 @@ __device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (co
 constexpr int PT_RPT = PT_TILE / PT_THREADS;      // records of the tile per thread: thread t owns the reads that start in its slice
 static_assert(PT_TILE % PT_THREADS == 0, "tile must split evenly over the threads");
 
-struct PtSmem {
+template <bool WARP>
+struct PtSmemT {
     alignas(16) u32 read[PT_WIN];
     alignas(16) u32 cvq[PT_WIN];   // window records, then IN PLACE the distinct-contig list of every read (slot s + d)
     alignas(16) u8 mq[PT_WIN];     // raw MAPQ bytes of the window (bulk-copy staging)
     alignas(8) unsigned long long mbar;
-    u16 cnt[PT_WIN];               // record count of the list entry in the same slot
-    u16 rn[PT_WIN];                // at a read start: number of entries the read emits (0 = filtered out)
-    u16 src[PT_WIN];               // output slot -> window position of the list entry
+    u16 cnt[PT_WIN];               // record count of the list entry in the same slot (warp kernel: bit 15 = first entry of a hyperedge)
+    u16 rn[WARP ? 2 : PT_WIN];     // walk kernel: at a read start, number of entries the read emits (0 = filtered out)
+    u16 src[WARP ? 2 : PT_WIN];    // walk kernel: output slot -> window position of the list entry
     u32 head[PT_WORDS];
     u32 hpref[PT_WORDS + 1];
     u32 tile, base, long_order, scan[PT_THREADS / 32 + 1];
+    u32 wstart[PT_THREADS / 32], wcnt[PT_THREADS / 32];   // warp kernel: window position and length of each warp's compacted output
     unsigned long long long_end;
 };
 
@@ -305,6 +307,13 @@ __device__ __forceinline__ int pt_prev_head(const u32* __restrict__ head, int i)
     while (m == 0) m = head[--w];
     return w * 32 + 31 - __clz(m);
 }
+// 32 consecutive bits of the head mask starting at window position pos (bit l = position pos + l; past the window: 0)
+__device__ __forceinline__ u32 pt_bits32(const u32* __restrict__ head, int pos) {
+    const int w = pos >> 5;
+    const u32 a = w < PT_WORDS ? head[w] : 0u;
+    const u32 b = (w + 1) < PT_WORDS ? head[w + 1] : 0u;
+    return __funnelshift_r(a, b, (u32)(pos & 31));
+}
 // TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
 // signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
@@ -330,12 +339,13 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
     } while (!ok);
 }
 
+template <bool WARP>
 __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                    unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
                                                                    u32* __restrict__ rem_row, u32* __restrict__ rem_col,
                                                                    u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
     extern __shared__ __align__(16) unsigned char pt_raw[];
-    PtSmem& S = *reinterpret_cast<PtSmem*>(pt_raw);
+    PtSmemT<WARP>& S = *reinterpret_cast<PtSmemT<WARP>*>(pt_raw);
     const int tid = threadIdx.x, lane = tid & 31;
     if (tid == 0) {
         S.tile = atomicAdd(&scal[3], 1u);        // ticket: every lower tile has already started
@@ -405,6 +415,7 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
     // distinct contigs is the read's order; reads outside [min_order, max_order] emit nothing.  No atomics.
     const int sl_lo = tid * PT_RPT, sl_hi = min(sl_lo + PT_RPT, own);
     u32 my_max_read = 0, my_out = 0;
+    if constexpr (!WARP) {
     {
         // ONE flat loop over the records of the slice's reads (a nested read / record loop makes the lanes of a warp
         // drift apart at every read boundary).  The first four distinct contigs of the current read live in registers,
@@ -461,9 +472,150 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
         }
         if (jend > s) finish();
     }
+    } else {
+        // One WARP per chunk of PT_WCH records, one LANE per record (hypergraph.py:1461-1477).  A round takes the next <= 32
+        // records that end on a read boundary: the lanes of one (read, contig) group find each other with MATCH.ANY on the key
+        // (read start lane << 24 | contig); the lowest lane of a group is its representative (first-seen order), the group's
+        // size is the record count, a REDUX.MAX over the group gives the largest MAPQ, the representatives inside the read's
+        // lane span are its distinct-contig order.  Kept entries are written back IN PLACE, compacted, at the front of the
+        // warp's own part of the window (output never overtakes input), so the copy-out below is a contiguous run per warp.
+        constexpr int PT_WCH = PT_TILE / (PT_THREADS / 32);
+        const int warp = tid >> 5;
+        const int w_lo = warp * PT_WCH, w_hi = min(w_lo + PT_WCH, own);
+        int p = w_lo < own ? pt_next_head(S.head, w_lo) : PT_WIN;
+        const int p0 = p;
+        int o = p;
+        const bool tail_end = (lo + (size_t)wn == N);            // the table ends inside the window: position wn closes the last read
+        const u32 lt = lanemask_lt();
+        while (p < w_hi && p != long_s) {
+            u32 em = pt_bits32(S.head, p + 1);                   // bit l: record p + l is the last of its read
+            {
+                const int d = wn - (p + 1);
+                if (tail_end && d >= 0 && d < 32) em |= 1u << d;
+            }
+            const u32 hm = pt_bits32(S.head, p);                 // bit l: record p + l starts a read (bit 0 is set)
+            if (w_hi - p < 32) {
+                // reads that start at or after w_hi belong to the next warp (or tile): the round stops at the end of the
+                // last read this warp owns
+                const u32 own_starts = hm & ((1u << (w_hi - p)) - 1u);
+                const int sA = 31 - __clz(own_starts);
+                const u32 at = em & ~((1u << sA) - 1u);
+                em = at ? (em & ((2u << (__ffs(at) - 1)) - 1u)) : (em & ((1u << sA) - 1u));
+            }
+            if (em != 0u) {
+                const int L = 31 - __clz(em);                    // the round covers lanes 0..L (whole reads only)
+                const bool act = lane <= L;
+                const int i = p + lane;
+                const u32 x = act ? S.cvq[i] : (PT_INVALID << 8);
+                const u32 r = act ? S.read[i] : 0u;
+                const int s_l = 31 - __clz(hm & (lt | (1u << lane)));
+                const int e_l = __ffs(em & ~lt) - 1;
+                const u32 span = act ? (((2u << e_l) - 1u) & ~((1u << s_l) - 1u)) : 0u;
+                const u32 c = x >> 8;
+                const bool valid = act && c != PT_INVALID;
+                const u32 key = valid ? (((u32)s_l << 24) | c) : (0x80000000u | (u32)lane);
+                const u32 peers = __match_any_sync(0xffffffffu, key);
+                const bool first = valid && (peers & lt) == 0u;
+                const u32 q = __reduce_max_sync(peers, x & 0xffu);
+                const u32 rm = __ballot_sync(0xffffffffu, first);
+                const u32 nd = __popc(rm & span);
+                const bool emit = first && nd >= min_order && nd <= max_order;
+                const u32 om = __ballot_sync(0xffffffffu, emit);
+                __syncwarp();                                    // every lane holds its record in registers from here on
+                if (emit) {
+                    const int slot = o + __popc(om & lt);
+                    const bool hd = (om & span & lt) == 0u;      // first kept entry of its read = head of the hyperedge
+                    S.cvq[slot] = (c << 8) | q;
+                    S.read[slot] = r;
+                    S.cnt[slot] = (u16)((u32)__popc(peers) | (hd ? 0x8000u : 0u));
+                    my_max_read = max(my_max_read, r);
+                }
+                __syncwarp();
+                o += __popc(om);
+                p += L + 1;
+            } else {
+                // a read of more than 32 records that ends inside the window: 32 records at a time against the list of
+                // distinct contigs found so far, kept in place at the front of the read's own span
+                int e = pt_next_head(S.head, p + 1);
+                if (e > wn) e = wn;
+                const u32 r = S.read[p];
+                int nd = 0;
+                for (int b0 = p; b0 < e; b0 += 32) {
+                    const int i = b0 + lane;
+                    const bool act = i < e;
+                    const u32 x = act ? S.cvq[i] : (PT_INVALID << 8);
+                    const u32 c = x >> 8;
+                    const bool valid = act && c != PT_INVALID;
+                    const u32 key = valid ? c : (0x80000000u | (u32)lane);
+                    const u32 peers = __match_any_sync(0xffffffffu, key);
+                    const bool first = valid && (peers & lt) == 0u;
+                    const u32 q = __reduce_max_sync(peers, x & 0xffu);
+                    const u32 gc = (u32)__popc(peers);
+                    __syncwarp();
+                    int f = -1;
+                    if (first)
+                        for (int d = 0; d < nd; ++d)
+                            if ((S.cvq[p + d] >> 8) == c) {
+                                f = d;
+                                break;
+                            }
+                    const u32 nm = __ballot_sync(0xffffffffu, first && f < 0);
+                    if (first) {
+                        if (f >= 0) {                            // distinct lanes hold distinct contigs: no two touch one slot
+                            S.cnt[p + f] = (u16)(S.cnt[p + f] + gc);
+                            const u32 old = S.cvq[p + f];
+                            if (((c << 8) | q) > old) S.cvq[p + f] = (c << 8) | q;
+                        } else {
+                            const int d = nd + __popc(nm & lt);
+                            S.cvq[p + d] = (c << 8) | q;
+                            S.cnt[p + d] = (u16)gc;
+                        }
+                    }
+                    nd += __popc(nm);
+                    __syncwarp();
+                }
+                if ((u32)nd >= min_order && (u32)nd <= max_order) {
+                    for (int d0 = 0; d0 < nd; d0 += 32) {        // slide the list down to the output position (o <= p)
+                        const int d = d0 + lane;
+                        u32 x = 0;
+                        u16 cn = 0;
+                        if (d < nd) {
+                            x = S.cvq[p + d];
+                            cn = S.cnt[p + d];
+                        }
+                        __syncwarp();
+                        if (d < nd) {
+                            S.cvq[o + d] = x;
+                            S.cnt[o + d] = (u16)((cn & 0x7fffu) | (d == 0 ? 0x8000u : 0u));
+                            S.read[o + d] = r;
+                        }
+                        __syncwarp();
+                    }
+                    o += nd;
+                    my_max_read = max(my_max_read, r);
+                }
+                p = e;
+            }
+        }
+        if (lane == 0) {
+            S.wstart[warp] = (u32)p0;
+            S.wcnt[warp] = (u32)(o - p0);
+        }
+    }
     // exclusive prefix of the per-thread output counts
-    u32 fast_total = 0;
-    const u32 my_ex = block_excl_scan<u32, PT_THREADS>(my_out, S.scan, &fast_total);
+    u32 fast_total = 0, my_ex = 0;
+    if constexpr (!WARP) {
+        my_ex = block_excl_scan<u32, PT_THREADS>(my_out, S.scan, &fast_total);
+    } else {
+        __syncthreads();
+        // exclusive prefix of the warps' output counts up to this thread's own warp, and the tile total
+#pragma unroll
+        for (int w = 0; w < PT_THREADS / 32; ++w) {
+            const u32 c = S.wcnt[w];
+            if (w < (tid >> 5)) my_ex += c;
+            fast_total += c;
+        }
+    }
     // slow path, part 1: order of the read that starts at `fend` and runs past the window
     u32 long_kept = 0;
     size_t ls = 0, le = 0;
@@ -526,7 +678,7 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
     }
     // output slot -> window position, so that the global stores below are coalesced (warps 1.. do this while
     // warp 0 is still looking back)
-    {
+    if constexpr (!WARP) {
         u32 o = my_ex;
         for (int s = pt_next_head(S.head, sl_lo); s < sl_hi && s != long_s; s = pt_next_head(S.head, s + 1)) {
             const int nd = S.rn[s];
@@ -536,14 +688,28 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
     }
     __syncthreads();
     const u32 base = S.base;
-    for (u32 p = tid; p < fast_total; p += PT_THREADS) {
-        const int pos = S.src[p];
-        const u32 x = S.cvq[pos];
-        const bool first = (S.head[pos >> 5] >> (pos & 31)) & 1u;             // slot s: first entry of the hyperedge
-        rem_row[base + p] = (x >> 8) | (first ? CPH_HEAD : 0u);
-        rem_col[base + p] = S.read[pos] + read_offset;                      // generate_edges :1871-1875
-        rem_count[base + p] = (u32)S.cnt[pos];
-        rem_mapq[base + p] = (int8_t)((int)(x & 0xffu) - 128);
+    if constexpr (!WARP) {
+        for (u32 p = tid; p < fast_total; p += PT_THREADS) {
+            const int pos = S.src[p];
+            const u32 x = S.cvq[pos];
+            const bool first = (S.head[pos >> 5] >> (pos & 31)) & 1u;             // slot s: first entry of the hyperedge
+            rem_row[base + p] = (x >> 8) | (first ? CPH_HEAD : 0u);
+            rem_col[base + p] = S.read[pos] + read_offset;                      // generate_edges :1871-1875
+            rem_count[base + p] = (u32)S.cnt[pos];
+            rem_mapq[base + p] = (int8_t)((int)(x & 0xffu) - 128);
+        }
+    } else {
+        // every warp copies its own compacted run out: consecutive lanes, consecutive addresses
+        const u32 ws = S.wstart[tid >> 5], wc = S.wcnt[tid >> 5];
+        for (u32 k = lane; k < wc; k += 32) {
+            const u32 x = S.cvq[ws + k];
+            const u32 cn = S.cnt[ws + k];
+            const size_t p = (size_t)base + my_ex + k;
+            rem_row[p] = (x >> 8) | ((cn & 0x8000u) ? CPH_HEAD : 0u);
+            rem_col[p] = S.read[ws + k] + read_offset;                          // generate_edges :1871-1875
+            rem_count[p] = cn & 0x7fffu;
+            rem_mapq[p] = (int8_t)((int)(x & 0xffu) - 128);
+        }
     }
     if (long_kept) {     // slow path, part 2: emit the long read after the tile's fast entries
         u32 carry = 0;
@@ -660,6 +826,31 @@ extern "C" int cph_pairs_to_edges(const u32* chrom1, const u32* chrom2, const in
     return CPH_OK;
 }
 
+// which tile kernel runs: the warp-cooperative one (default) or the per-read-slice walk (CPH_POREC_KERNEL=walk; kept for
+// A/B measurements -- profiles/)
+static int pt_mode() {
+    static int m = -1;
+    if (m < 0) {
+        const char* e = getenv("CPH_POREC_KERNEL");
+        m = (e && strcmp(e, "walk") == 0) ? 0 : 1;
+    }
+    return m;
+}
+static cudaError_t pt_prepare() {
+    cudaError_t e = cudaFuncSetAttribute(porec_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmemT<false>));
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(porec_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmemT<true>));
+}
+static void pt_launch(u32 grid, cudaStream_t st, const PorecIn& in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
+                      unsigned long long* tile_state, u32* scal, u32* rem_row, u32* rem_col, u32* rem_count, int8_t* rem_mapq) {
+    if (pt_mode())
+        porec_tile_kernel<true><<<grid, PT_THREADS, sizeof(PtSmemT<true>), st>>>(in, use_tma, min_order, max_order, read_offset, tile_state,
+                                                                                 scal, rem_row, rem_col, rem_count, rem_mapq);
+    else
+        porec_tile_kernel<false><<<grid, PT_THREADS, sizeof(PtSmemT<false>), st>>>(in, use_tma, min_order, max_order, read_offset, tile_state,
+                                                                                   scal, rem_row, rem_col, rem_count, rem_mapq);
+}
+
 extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, const int8_t* mapq, const u32* start, const u32* end,
                                   const i64* contig_len, u64 n_records, u32 n_contigs, int min_mapq, u32 min_order, u32 max_order,
                                   u64 edge_length, u32 read_offset, int sorted_by_read, u32* rem_row, u32* rem_col, u32* rem_count,
@@ -686,12 +877,11 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
         }
         CUDA_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
         CUDA_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
-        CUDA_TRY(cudaFuncSetAttribute(porec_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmem)));
+        CUDA_TRY(pt_prepare());
         // bulk (TMA) window loads need 16-byte aligned columns; the edge filter reads two more columns -> plain loads
         const int use_tma = edge_length == 0 && (((uintptr_t)read_idx | (uintptr_t)contig_idx | (uintptr_t)mapq) & 15) == 0;
-        porec_tile_kernel<<<ntiles, PT_THREADS, sizeof(PtSmem), st>>>(in, use_tma, min_order, max_order, read_offset,
-                                                                     (unsigned long long*)tile_state, scal, rem_row, rem_col,
-                                                                     rem_count, rem_mapq);
+        pt_launch(ntiles, st, in, use_tma, min_order, max_order, read_offset, (unsigned long long*)tile_state, scal, rem_row, rem_col,
+                  rem_count, rem_mapq);
         KERNEL_CHECK();
         u32 hs[4] = {0, 0, 0, 0};
         u64 last = 0;
@@ -1078,7 +1268,7 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     HT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
     HT_TRY(cudaMemsetAsync(scal, 0, 4 * sizeof(u32), st));
     HT_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
-    HT_TRY(cudaFuncSetAttribute(porec_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmem)));
+    HT_TRY(pt_prepare());
     // the staging columns may be recycled blocks with work still queued on `st`: copies start after it
     HT_TRY(cudaEventRecord(ready, st));
     HT_TRY(cudaStreamWaitEvent(cs, ready, 0));
@@ -1151,9 +1341,8 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
         if (t_hi > t_done) {
             // (packed and unpacked chunks land on different streams: wait for every chunk since the last launch)
             for (; waited <= c; ++waited) HT_TRY(cudaStreamWaitEvent(st, landed[waited], 0));
-            porec_tile_kernel<<<t_hi - t_done, PT_THREADS, sizeof(PtSmem), st>>>(in, use_tma, min_order, max_order, read_offset,
-                                                                                (unsigned long long*)tile_state, scal, rem_row,
-                                                                                rem_col, rem_count, rem_mapq);
+            pt_launch(t_hi - t_done, st, in, use_tma, min_order, max_order, read_offset, (unsigned long long*)tile_state, scal, rem_row,
+                      rem_col, rem_count, rem_mapq);
             ++g_cph_launches;
             HT_TRY(cudaGetLastError());
             t_done = t_hi;

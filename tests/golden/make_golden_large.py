@@ -86,6 +86,7 @@ def main():
     rows = np.searchsorted(Ac.indptr, pick, side="right") - 1
     out.update(A_nnz=np.int64(Ac.nnz), A_pattern_sha256=sha(Ac.indptr.astype(np.int64), Ac.indices.astype(np.int32)),
                A_rowsum=np.asarray(Ac.astype(np.float64).sum(axis=1)).ravel(),
+               A_row_nnz=np.diff(Ac.indptr).astype(np.int64),
                A_sample_pos=pick.astype(np.int64), A_sample_row=rows.astype(np.int32),
                A_sample_col=Ac.indices[pick].astype(np.int32), A_sample_val=Ac.data[pick].astype(np.float32))
     Au = ah.HyperGraph.clique_expansion_init(H, min_weight=2.0, use_high_order=False)

@@ -34,21 +34,28 @@ def gold():
     return dict(np.load(os.path.join(GOLDEN, "ref_workloadC_4M.npz")))
 
 
-def check_A(gold, A, rtol, near_thr_ok=True):
-    """A: canonical csr (float).  Pattern must equal the reference's except entries within rtol of the threshold."""
+def check_A(gold, A, rtol, exact_pattern=False):
+    """A: canonical csr (float64 values).  The reference computes A in float32 with sqrt-scaled operands
+    (algorithms/hypergraph.py:418-446), so cells whose exact value EQUALS min_weight (1 + 1/3 + 1/3 + 1/3, ...) land on
+    either side of the `< min_weight` cut by rounding alone ("entries within rounding of the cut = either").
+    Everything else must agree: every sampled reference entry is either present with the same value or sits at the cut,
+    and per row the difference of the row sums is explained by (difference of stored entries) x min_weight."""
     A = A.tocsr().copy(); A.sort_indices()
     pat = sha(A.indptr.astype(np.int64), A.indices.astype(np.int32))
     pos, rows, cols, vals = gold["A_sample_pos"], gold["A_sample_row"], gold["A_sample_col"], gold["A_sample_val"]
+    rs = np.asarray(A.sum(axis=1)).ravel()
     if pat == str(gold["A_pattern_sha256"]):
         np.testing.assert_allclose(A.data[pos], vals.astype(np.float64), rtol=rtol)
-    else:
-        # a value within rounding of min_weight may be kept on one side only (SURVEY.md 7): compare entry by entry
-        assert near_thr_ok and abs(A.nnz - int(gold["A_nnz"])) <= 8, (A.nnz, int(gold["A_nnz"]))
-        got = np.asarray(A[rows, cols]).ravel()
-        miss = got == 0
-        assert np.all(np.abs(vals[miss] - 2.0) <= 8e-6)
-        np.testing.assert_allclose(got[~miss], vals[~miss].astype(np.float64), rtol=rtol)
-    np.testing.assert_allclose(np.asarray(A.astype(np.float64).sum(axis=1)).ravel(), gold["A_rowsum"], rtol=2e-5)
+        np.testing.assert_allclose(rs, gold["A_rowsum"], rtol=2e-5)
+        return
+    assert not exact_pattern, "sparsity pattern differs from the reference run"
+    got = np.asarray(A[rows, cols]).ravel()
+    miss = got == 0
+    assert np.all(np.abs(vals[miss] - 2.0) <= 8e-6)                       # reference-only entries sit at the cut
+    np.testing.assert_allclose(got[~miss], vals[~miss].astype(np.float64), rtol=rtol)
+    dn = np.diff(A.indptr).astype(np.int64) - gold["A_row_nnz"]          # entries only one side stores, per row
+    assert abs(int(dn.sum())) <= 0.06 * int(gold["A_nnz"])                # ties at the cut are a few per cent of A
+    np.testing.assert_allclose(rs - 2.0 * dn, gold["A_rowsum"], rtol=2e-5)   # ... and each of them is worth min_weight
 
 
 def test_oracle_matches_reference_at_4M(gold):
@@ -68,7 +75,7 @@ def test_oracle_matches_reference_at_4M(gold):
     Au = orc.clique_expansion(H, use_high_order=False, min_weight=2.0)
     assert digest_csr_int(Au) == str(gold["Au_sha256"])
     A = orc.clique_expansion(H, min_weight=2.0, dtype=np.float32)
-    check_A(gold, A, rtol=3e-6)
+    check_A(gold, A, rtol=3e-6, exact_pattern=True)      # same float32 arithmetic -> same pattern
 
 
 @pytest.mark.gpu
@@ -98,5 +105,12 @@ def test_cuda_path_matches_reference_at_4M(gold):
     # weighted A: fp64 accumulation against the reference's float32
     A, _ = D.clique_expansion(H, use_high_order=True, min_weight=2.0, want32=True, want64=True)
     As = csr_matrix((D.to_host(A.data64), D.to_host(A.indices), D.to_host(A.indptr)), shape=(H.n_rows,) * 2)
-    check_A(gold, As, rtol=3e-6)
+    # against the reference's float32 values: its own accumulation error on long sums (the diagonal adds ~1e4 float32
+    # terms) reaches a few 1e-5 relative; the 1e-6 bar of north_star is held against the fp64 restatement below
+    check_A(gold, As, rtol=5e-5)
+    from oracle import hypergraph_oracle as orc
+    A64 = orc.clique_expansion(Hs.astype(np.float64), min_weight=2.0, dtype=np.float64).tocsr()
+    A64.sort_indices(); As.sort_indices()
+    assert np.array_equal(A64.indptr, As.indptr) and np.array_equal(A64.indices, As.indices)
+    np.testing.assert_allclose(As.data, A64.data, rtol=1e-6)
     torch.cuda.synchronize()
