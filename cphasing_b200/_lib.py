@@ -35,6 +35,14 @@ _D = C.c_double
 _SZ = C.c_size_t
 _WS = [_P, _SZ, C.POINTER(_SZ), _P]          # ws, ws_bytes, h_ws_need, stream
 
+class Prefilter(C.Structure):
+    """cph_prefilter of include/cph.h (device pointers; 0 / NULL = off)."""
+    _fields_ = [("bed_ptr", _P), ("bed_start", _P), ("bed_end", _P), ("hcr_invert", _I), ("split_length", _U64),
+                ("split_init", _P), ("n_names", _U32)]
+
+
+_PF = C.POINTER(Prefilter)
+
 _SIGS = {
     "cph_version": (C.c_int, []),
     "cph_last_error": (C.c_char_p, []),
@@ -42,6 +50,9 @@ _SIGS = {
     "cph_pairs_to_edges": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U64, _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_porec_to_edges": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U64, _U32, _I,
                                 _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
+    "cph_pairs_to_edges_pf": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U64, _PF, _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
+    "cph_porec_to_edges_pf": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U64, _U32, _I, _PF,
+                                   _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_porec_to_edges_host": (_I, [_P, _P, _P, _P, _P, _P, _U64, _U32, _I, _U32, _U32, _U32, _U64, _I,
                                      _P, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_release_host_staging": (_I, []),

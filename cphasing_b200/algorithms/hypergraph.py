@@ -328,7 +328,9 @@ class HyperGraph:
 
     # -- algorithms/hypergraph.py:590-602
     @staticmethod
-    def normalize_adjacency_matrix(A, NW):
+    def normalize_adjacency_matrix(A, NW=None):
+        if NW is None:                  # the reference's callers pass self.NW = None when --normalize is off (:1046, :1779)
+            return A
         from .. import graphops
         return graphops.scale_by_node_weights(A, _node_weights_from_NW(NW))
 

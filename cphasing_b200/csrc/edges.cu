@@ -12,6 +12,7 @@
 // order of the read; a scan compacts the survivors.  Bytes per record (sorted input): 9 read,
 // 8+8 key write/read x2, 10 flags -> HBM bound.
 #include "common.cuh"
+#include "cph.h"
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -29,6 +30,35 @@ constexpr int TPB = 256;
 __device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.x + threadIdx.x; }
 
 // ------------------------------------------------------------------------------------------------
+// Pre-filters of the extractors (cph_prefilter of include/cph.h, device view).
+//   HCR BED  hypergraph.py:1721-1752 (Pore-C, alignment midpoint), :786-893 (pairs, either end): join_asof(backward) on the
+//            BED starts of the same contig = the LAST interval whose start <= pos; the record is "in" iff pos < its end.
+//   split    hypergraph.py:1406-1424 (Pore-C: init_idx + midpoint // split_length), :994-1023 (pairs: init_idx + pos //
+//            split_length): the contig column then holds codes of the ORIGINAL contig names and the hyperedge rows are
+//            the split bins.
+// ------------------------------------------------------------------------------------------------
+struct PreF {
+    const u64* bed_ptr;      // [n_names + 1] or nullptr
+    const u32* bed_start;    // sorted by (name, start)
+    const u32* bed_end;
+    const u32* split_init;   // [n_names] first bin of each original contig (0xffffffff: not in the map) or nullptr
+    u64 split_length;
+    u32 n_names;             // size of the code space of the contig column(s)
+    int hcr_invert;
+};
+
+__device__ __forceinline__ bool pf_in_hcr(const PreF& f, u32 name, u32 pos) {
+    u64 lo = f.bed_ptr[name], hi = f.bed_ptr[name + 1];      // first interval with start > pos
+    const u64 base = lo;
+    while (lo < hi) {
+        const u64 mid = (lo + hi) >> 1;
+        if (f.bed_start[mid] <= pos) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo > base && pos < f.bed_end[lo - 1];
+}
+
+// ------------------------------------------------------------------------------------------------
 // Hi-C pairs
 // ------------------------------------------------------------------------------------------------
 struct PairsIn {
@@ -42,14 +72,30 @@ struct PairsIn {
     u32 n_contigs;
     int min_mapq;
     i64 edge_length;
+    PreF pf;
 };
 
 __device__ __forceinline__ bool pair_ok(const PairsIn& in, size_t p, u32& a, u32& b, int8_t& q) {
     a = in.c1[p];
     b = in.c2[p];
     q = in.mapq ? in.mapq[p] : (int8_t)0;
-    bool ok = a < in.n_contigs && b < in.n_contigs;
+    const bool pre = in.pf.bed_ptr != nullptr || in.pf.split_init != nullptr;
+    bool ok = pre ? (a < in.pf.n_names && b < in.pf.n_names) : (a < in.n_contigs && b < in.n_contigs);
     if (in.min_mapq > 0 && in.mapq) ok = ok && (int)q >= in.min_mapq;          // hypergraph.py:970-971
+    if (ok && pre) {
+        const u32 x1 = in.p1[p], x2 = in.p2[p];
+        if (in.pf.bed_ptr) {                                                    // :786-893 any end inside an HCR interval
+            const bool any = pf_in_hcr(in.pf, a, x1) || pf_in_hcr(in.pf, b, x2);
+            ok = in.pf.hcr_invert ? !any : any;
+        }
+        if (ok && in.pf.split_init) {                                           // :994-1023
+            const u32 ia = in.pf.split_init[a], ib = in.pf.split_init[b];
+            ok = ia != 0xffffffffu && ib != 0xffffffffu;
+            a = ia + (u32)(x1 / in.pf.split_length);
+            b = ib + (u32)(x2 / in.pf.split_length);
+            ok = ok && a < in.n_contigs && b < in.n_contigs;
+        }
+    }
     if (ok && in.edge_length > 0) {                                             // :977-992
         i64 x1 = in.p1[p], x2 = in.p2[p];
         i64 l1 = in.len[a], l2 = in.len[b];
@@ -97,6 +143,7 @@ struct PorecIn {
     u32 n_contigs;
     int min_mapq;
     i64 edge_length;
+    PreF pf;
 };
 
 __global__ void __launch_bounds__(TPB) max_u32_kernel(const u32* __restrict__ x, u64 n, u32* __restrict__ out) {
@@ -107,20 +154,44 @@ __global__ void __launch_bounds__(TPB) max_u32_kernel(const u32* __restrict__ x,
     if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
-__global__ void __launch_bounds__(TPB) porec_key_kernel(PorecIn in, int cb, u64* __restrict__ keys, u32* __restrict__ unsorted_flag) {
-    size_t t = gtid();
-    if (t >= in.n) return;
-    u32 r = in.read[t], c = in.contig[t];
+constexpr u32 PT_INVALID = 0x00ffffffu;          // contig field of a filtered-out record (n_contigs < 2^23)
+__device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (contig or INVALID) << 8 | mapq + 128
+    u32 c = in.contig[t];
     int8_t q = in.mapq[t];
-    bool ok = c < in.n_contigs;
+    const bool pre = in.pf.bed_ptr != nullptr || in.pf.split_init != nullptr;
+    bool ok = pre ? c < in.pf.n_names : c < in.n_contigs;
     if (in.min_mapq > 0) ok = ok && (int)q >= in.min_mapq;                      // hypergraph.py:1774-1775
-    if (ok && in.edge_length > 0) {                                             // :1449-1456
+    if (ok && pre) {
+        const u32 st = in.start[t], en = in.end[t];
+        const u32 mid = st + (en - st) / 2u;                                    // UInt32 arithmetic, as polars does it
+        if (in.pf.bed_ptr) {                                                    // :1730-1752
+            const bool hit = pf_in_hcr(in.pf, c, mid);
+            ok = in.pf.hcr_invert ? !hit : hit;
+        }
+        if (ok && in.pf.split_init) {                                           // :1406-1424 (no edge filter on this branch)
+            const u32 i0 = in.pf.split_init[c];
+            ok = i0 != 0xffffffffu;
+            c = i0 + (u32)(mid / in.pf.split_length);
+            ok = ok && c < in.n_contigs;
+        }
+    }
+    if (ok && in.edge_length > 0 && !in.pf.split_init) {                        // :1449-1456
         i64 st = in.start[t], en = in.end[t];
         i64 pos = st + (en - st) / 2;
         i64 L = in.len[c];
         ok = (pos < in.edge_length) || ((L - pos) < in.edge_length);
     }
-    u64 k = ((u64)r << (cb + 8)) | ((u64)(ok ? c : 0u) << 8) | (u64)(u8)((int)q + 128);
+    return ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
+}
+
+__global__ void __launch_bounds__(TPB) porec_key_kernel(PorecIn in, int cb, u64* __restrict__ keys, u32* __restrict__ unsorted_flag) {
+    size_t t = gtid();
+    if (t >= in.n) return;
+    const u32 r = in.read[t];
+    const u32 x = porec_cvq(in, t);              // every record filter (MAPQ, HCR, split index, edge) lives there
+    const u32 c = x >> 8;
+    const bool ok = c != PT_INVALID;
+    u64 k = ((u64)r << (cb + 8)) | ((u64)(ok ? c : 0u) << 8) | (u64)(x & 0xffu);
     if (!ok) k |= (1ull << 63);
     keys[t] = k;
     if (t > 0 && in.read[t - 1] > r) *unsorted_flag = 1u;   // benign race: everyone writes 1
@@ -233,22 +304,7 @@ constexpr int PT_TILE = 1792;     // + halo = 2048-record window: 31 KB of share
 constexpr int PT_HALO = 256;
 constexpr int PT_WIN = PT_TILE + PT_HALO;
 constexpr int PT_WORDS = PT_WIN / 32;
-constexpr u32 PT_INVALID = 0x00ffffffu;          // contig field of a filtered-out record (n_contigs < 2^23)
 constexpr u64 PT_AGG = 1ull << 62, PT_INCL = 2ull << 62, PT_VAL = (1ull << 62) - 1;
-
-__device__ __forceinline__ u32 porec_cvq(const PorecIn& in, size_t t) {   // (contig or INVALID) << 8 | mapq + 128
-    u32 c = in.contig[t];
-    int8_t q = in.mapq[t];
-    bool ok = c < in.n_contigs;
-    if (in.min_mapq > 0) ok = ok && (int)q >= in.min_mapq;                      // hypergraph.py:1774-1775
-    if (ok && in.edge_length > 0) {                                             // :1449-1456
-        i64 st = in.start[t], en = in.end[t];
-        i64 pos = st + (en - st) / 2;
-        i64 L = in.len[c];
-        ok = (pos < in.edge_length) || ((L - pos) < in.edge_length);
-    }
-    return ((ok ? c : PT_INVALID) << 8) | (u32)(u8)((int)q + 128);
-}
 
 constexpr int PT_RPT = PT_TILE / PT_THREADS;      // records of the tile per thread: thread t owns the reads that start in its slice
 static_assert(PT_TILE % PT_THREADS == 0, "tile must split evenly over the threads");
@@ -262,7 +318,7 @@ struct PtSmemT {
     u16 cnt[PT_WIN];               // record count of the list entry in the same slot (warp kernel: bit 15 = first entry of a hyperedge)
     u16 rn[WARP ? 2 : PT_WIN];     // walk kernel: at a read start, number of entries the read emits (0 = filtered out)
     u16 src[WARP ? 2 : PT_WIN];    // walk kernel: output slot -> window position of the list entry
-    u32 head[PT_WORDS];
+    u32 head[PT_WORDS + 3];        // + zero padding: the warp kernel reads 96-bit windows of the mask without bounds checks
     u32 hpref[PT_WORDS + 1];
     u32 tile, base, long_order, scan[PT_THREADS / 32 + 1];
     u32 wstart[PT_THREADS / 32], wcnt[PT_THREADS / 32];   // warp kernel: window position and length of each warp's compacted output
@@ -307,13 +363,6 @@ __device__ __forceinline__ int pt_prev_head(const u32* __restrict__ head, int i)
     while (m == 0) m = head[--w];
     return w * 32 + 31 - __clz(m);
 }
-// 32 consecutive bits of the head mask starting at window position pos (bit l = position pos + l; past the window: 0)
-__device__ __forceinline__ u32 pt_bits32(const u32* __restrict__ head, int pos) {
-    const int w = pos >> 5;
-    const u32 a = w < PT_WORDS ? head[w] : 0u;
-    const u32 b = (w + 1) < PT_WORDS ? head[w + 1] : 0u;
-    return __funnelshift_r(a, b, (u32)(pos & 31));
-}
 // TMA (bulk async copy) helpers: one elected thread moves the window's three columns global -> shared, completion is
 // signalled on an mbarrier (SASS: UBLKCP).  Addresses and sizes must be multiples of 16 bytes.
 __device__ __forceinline__ u32 smem_u32(const void* p) { return (u32)__cvta_generic_to_shared(p); }
@@ -339,8 +388,8 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
     } while (!ok);
 }
 
-template <bool WARP>
-__global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
+template <bool WARP, int MINB = 6>
+__global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                    unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
                                                                    u32* __restrict__ rem_row, u32* __restrict__ rem_col,
                                                                    u32* __restrict__ rem_count, int8_t* __restrict__ rem_mapq) {
@@ -385,6 +434,8 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
     __syncthreads();
     // read starts of the window as a bitmask
     const u32 prev_read = lo > 0 ? in.read[lo - 1] : 0u;
+    const bool tail_end = (lo + (size_t)wn == N);                // the table ends inside the window
+    if (WARP && tid < 3) S.head[PT_WORDS + tid] = (tid == 0 && tail_end && wn == PT_WIN) ? 1u : 0u;
     for (int i0 = 0; i0 < PT_WIN; i0 += PT_THREADS) {
         int i = i0 + tid;
         bool head = false;
@@ -393,7 +444,9 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
             u32 p = i > 0 ? S.read[i - 1] : prev_read;
             head = (lo + i == 0) || (p != r);
             if (i < own && (lo + i) > 0 && p > r) scal[1] = 1u;   // not grouped by read (benign race)
-        }
+        } else if (WARP && i == wn && tail_end) {
+            head = true;        // warp kernel: a virtual read start closes the last read of the table (never counted: is_long
+        }                       // needs lo + wn != N, and nr_own only looks below `own` <= wn)
         u32 m = __ballot_sync(0xffffffffu, head);
         if (lane == 0) S.head[i >> 5] = m;
     }
@@ -485,38 +538,47 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
         int p = w_lo < own ? pt_next_head(S.head, w_lo) : PT_WIN;
         const int p0 = p;
         int o = p;
-        const bool tail_end = (lo + (size_t)wn == N);            // the table ends inside the window: position wn closes the last read
+        // the warp's records: [p0, stop) = whole reads, from the first read start in its chunk to the first one after it
+        // (the next warp's p0); the read that overflows the window (long_s) belongs to the slow path
+        int stop = p < w_hi ? min(pt_next_head(S.head, w_hi), wn) : p;
+        if (long_s >= p && long_s < stop) stop = long_s;
         const u32 lt = lanemask_lt();
-        while (p < w_hi && p != long_s) {
-            u32 em = pt_bits32(S.head, p + 1);                   // bit l: record p + l is the last of its read
-            {
-                const int d = wn - (p + 1);
-                if (tail_end && d >= 0 && d < 32) em |= 1u << d;
-            }
-            const u32 hm = pt_bits32(S.head, p);                 // bit l: record p + l starts a read (bit 0 is set)
-            if (w_hi - p < 32) {
-                // reads that start at or after w_hi belong to the next warp (or tile): the round stops at the end of the
-                // last read this warp owns
-                const u32 own_starts = hm & ((1u << (w_hi - p)) - 1u);
-                const int sA = 31 - __clz(own_starts);
-                const u32 at = em & ~((1u << sA) - 1u);
-                em = at ? (em & ((2u << (__ffs(at) - 1)) - 1u)) : (em & ((1u << sA) - 1u));
-            }
+        const u32 self = 1u << lane;
+        while (p < stop) {
+            const int hw = p >> 5;
+            const u32 sh = (u32)(p & 31);
+            const u32 ha = S.head[hw], hb = S.head[hw + 1], hc = S.head[hw + 2];
+            const u32 hm = __funnelshift_r(ha, hb, sh);          // bit l: record p + l starts a read (bit 0 is set)
+            u32 em = (hm >> 1) | (__funnelshift_r(hb, hc, sh) << 31);   // bit l: record p + l is the last of its read
+            if (stop - p < 32) em &= (1u << (stop - p)) - 1u;
             if (em != 0u) {
                 const int L = 31 - __clz(em);                    // the round covers lanes 0..L (whole reads only)
                 const bool act = lane <= L;
                 const int i = p + lane;
                 const u32 x = act ? S.cvq[i] : (PT_INVALID << 8);
                 const u32 r = act ? S.read[i] : 0u;
-                const int s_l = 31 - __clz(hm & (lt | (1u << lane)));
-                const int e_l = __ffs(em & ~lt) - 1;
-                const u32 span = act ? (((2u << e_l) - 1u) & ~((1u << s_l) - 1u)) : 0u;
+                const int s_l = 31 - __clz(hm & (lt | self));    // lane where my read starts
+                const u32 nxt = hm & ~(lt | self);                // read starts after my lane
+                const u32 below_next = nxt ? ((nxt & (0u - nxt)) - 1u) : 0xffffffffu;
+                const u32 span = below_next & ~((1u << s_l) - 1u);   // lanes of my read
                 const u32 c = x >> 8;
                 const bool valid = act && c != PT_INVALID;
                 const u32 key = valid ? (((u32)s_l << 24) | c) : (0x80000000u | (u32)lane);
                 const u32 peers = __match_any_sync(0xffffffffu, key);
                 const bool first = valid && (peers & lt) == 0u;
-                const u32 q = __reduce_max_sync(peers, x & 0xffu);
+                // largest MAPQ of the group, gathered by its first lane (a REDUX over per-group masks is serialised by the
+                // hardware, one group at a time: 25 per round).  Groups are small: the loop runs (largest group - 1) times.
+                u32 q = x & 0xffu;
+                {
+                    const u32 q0 = q;
+                    u32 others = first ? (peers & ~self) : 0u;
+                    while (__any_sync(0xffffffffu, others != 0u)) {
+                        const int srcl = others ? (__ffs(others) - 1) : lane;
+                        const u32 oq = __shfl_sync(0xffffffffu, q0, srcl);
+                        q = max(q, oq);                          // lanes without work read their own value
+                        others &= others - 1u;
+                    }
+                }
                 const u32 rm = __ballot_sync(0xffffffffu, first);
                 const u32 nd = __popc(rm & span);
                 const bool emit = first && nd >= min_order && nd <= max_order;
@@ -536,8 +598,7 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
             } else {
                 // a read of more than 32 records that ends inside the window: 32 records at a time against the list of
                 // distinct contigs found so far, kept in place at the front of the read's own span
-                int e = pt_next_head(S.head, p + 1);
-                if (e > wn) e = wn;
+                int e = min(pt_next_head(S.head, p + 1), stop);
                 const u32 r = S.read[p];
                 int nd = 0;
                 for (int b0 = p; b0 < e; b0 += 32) {
@@ -549,7 +610,17 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
                     const u32 key = valid ? c : (0x80000000u | (u32)lane);
                     const u32 peers = __match_any_sync(0xffffffffu, key);
                     const bool first = valid && (peers & lt) == 0u;
-                    const u32 q = __reduce_max_sync(peers, x & 0xffu);
+                    u32 q = x & 0xffu;
+                    {
+                        const u32 q0 = q;
+                        u32 others = first ? (peers & ~self) : 0u;
+                        while (__any_sync(0xffffffffu, others != 0u)) {
+                            const int srcl = others ? (__ffs(others) - 1) : lane;
+                            const u32 oq = __shfl_sync(0xffffffffu, q0, srcl);
+                            q = max(q, oq);
+                            others &= others - 1u;
+                        }
+                    }
                     const u32 gc = (u32)__popc(peers);
                     __syncwarp();
                     int f = -1;
@@ -665,7 +736,10 @@ __global__ void __launch_bounds__(PT_THREADS, 6) porec_tile_kernel(PorecIn in, i
                 u32 incl = __ballot_sync(0xffffffffu, (st >> 62) == 2);
                 u32 first = incl ? (u32)__ffs(incl) - 1u : 32u;
                 u32 need = first >= 31u ? 0xffffffffu : ((2u << first) - 1u);
-                if (inval & need) continue;                 // a predecessor has not published yet: re-read
+                if (inval & need) {                         // a predecessor has not published yet: re-read
+                    __nanosleep(40);                        // ... without taking issue slots from the warps still working
+                    continue;
+                }
                 u64 v = ((u32)lane <= first) ? (st & PT_VAL) : 0ull;
                 running += warp_sum(v);
                 if (incl) break;
@@ -791,17 +865,51 @@ __global__ void __launch_bounds__(TPB) t2e_out_kernel(const u64* __restrict__ ke
 }  // namespace
 
 // =================================================================================================
+// host cph_prefilter -> device view; false when the combination is not supported
+static bool pf_view(const cph_prefilter* pf, PreF* out) {
+    *out = PreF{nullptr, nullptr, nullptr, nullptr, 0, 0, 0};
+    if (pf == nullptr) return true;
+    const bool hcr = pf->bed_ptr != nullptr, split = pf->split_length != 0;
+    if (!hcr && !split) return true;
+    if (pf->n_names == 0) return false;
+    if (hcr && !(pf->bed_start && pf->bed_end)) return false;
+    if (split && !pf->split_init) return false;
+    out->bed_ptr = hcr ? pf->bed_ptr : nullptr;
+    out->bed_start = pf->bed_start;
+    out->bed_end = pf->bed_end;
+    out->split_init = split ? pf->split_init : nullptr;
+    out->split_length = pf->split_length;
+    out->n_names = pf->n_names;
+    out->hcr_invert = pf->hcr_invert;
+    return true;
+}
+
 extern "C" int cph_pairs_to_edges(const u32* chrom1, const u32* chrom2, const int8_t* mapq, const u32* pos1, const u32* pos2,
                                   const i64* contig_len, u64 n_pairs, u32 n_contigs, int min_mapq, u64 edge_length, u32* rem_row,
                                   u32* rem_col, u32* rem_count, int8_t* rem_mapq, u64* h_counts, void* ws, size_t ws_bytes,
                                   size_t* h_ws_need, void* stream) {
+    return cph_pairs_to_edges_pf(chrom1, chrom2, mapq, pos1, pos2, contig_len, n_pairs, n_contigs, min_mapq, edge_length, nullptr,
+                                 rem_row, rem_col, rem_count, rem_mapq, h_counts, ws, ws_bytes, h_ws_need, stream);
+}
+
+extern "C" int cph_pairs_to_edges_pf(const u32* chrom1, const u32* chrom2, const int8_t* mapq, const u32* pos1, const u32* pos2,
+                                     const i64* contig_len, u64 n_pairs, u32 n_contigs, int min_mapq, u64 edge_length,
+                                     const cph_prefilter* prefilter, u32* rem_row, u32* rem_col, u32* rem_count, int8_t* rem_mapq,
+                                     u64* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     ARG_CHECK(n_pairs < (1ull << 31));
     ARG_CHECK(n_contigs > 0 && n_contigs < CPH_HEAD);
+    PreF pfv;
+    ARG_CHECK(pf_view(prefilter, &pfv));
+    const bool pre = pfv.bed_ptr != nullptr || pfv.split_init != nullptr;
+    ARG_CHECK(!pre || n_pairs == 0 || (pos1 && pos2));
+    // the reference joins the contig lengths on the ORIGINAL names while contigsizes holds the split names (:977-992 with
+    // split on): nothing survives.  Not reproduced -- refuse the combination instead of guessing.
+    ARG_CHECK(!(pfv.split_init && edge_length));
     WS_BEGIN(ar);
     u32* keep = ar.take<u32>(n_pairs + 1);
     u32* total = ar.take<u32>(1);
-    PairsIn in{chrom1, chrom2, mapq, pos1, pos2, contig_len, n_pairs, n_contigs, min_mapq, (i64)edge_length};
+    PairsIn in{chrom1, chrom2, mapq, pos1, pos2, contig_len, n_pairs, n_contigs, min_mapq, (i64)edge_length, pfv};
     if (!ar.dry) {
         ARENA_CHECK(ar);
         ARG_CHECK(n_pairs == 0 || (chrom1 && chrom2));
@@ -828,22 +936,28 @@ extern "C" int cph_pairs_to_edges(const u32* chrom1, const u32* chrom2, const in
 
 // which tile kernel runs: the warp-cooperative one (default) or the per-read-slice walk (CPH_POREC_KERNEL=walk; kept for
 // A/B measurements -- profiles/)
-static int pt_mode() {
-    static int m = -1;
+static int pt_mode() {      // 0: walk   1: warp, 6 CTAs per SM   2 (default): warp, 8 CTAs per SM (32 registers)
+    static int m = -1;      // measured on workload C: walk 3.47 ms, warp 3.00 ms, warp8 2.77 ms (profiles/r2_porec_kernels.txt)
     if (m < 0) {
         const char* e = getenv("CPH_POREC_KERNEL");
-        m = (e && strcmp(e, "walk") == 0) ? 0 : 1;
+        m = (e && strcmp(e, "walk") == 0) ? 0 : (e && strcmp(e, "warp6") == 0) ? 1 : 2;
     }
     return m;
 }
 static cudaError_t pt_prepare() {
     cudaError_t e = cudaFuncSetAttribute(porec_tile_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmemT<false>));
     if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(porec_tile_kernel<true, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmemT<true>));
+    if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(porec_tile_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PtSmemT<true>));
 }
 static void pt_launch(u32 grid, cudaStream_t st, const PorecIn& in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                       unsigned long long* tile_state, u32* scal, u32* rem_row, u32* rem_col, u32* rem_count, int8_t* rem_mapq) {
-    if (pt_mode())
+    const int m = pt_mode();
+    if (m == 2)
+        porec_tile_kernel<true, 8><<<grid, PT_THREADS, sizeof(PtSmemT<true>), st>>>(in, use_tma, min_order, max_order, read_offset,
+                                                                                    tile_state, scal, rem_row, rem_col, rem_count, rem_mapq);
+    else if (m == 1)
         porec_tile_kernel<true><<<grid, PT_THREADS, sizeof(PtSmemT<true>), st>>>(in, use_tma, min_order, max_order, read_offset, tile_state,
                                                                                  scal, rem_row, rem_col, rem_count, rem_mapq);
     else
@@ -855,13 +969,27 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
                                   const i64* contig_len, u64 n_records, u32 n_contigs, int min_mapq, u32 min_order, u32 max_order,
                                   u64 edge_length, u32 read_offset, int sorted_by_read, u32* rem_row, u32* rem_col, u32* rem_count,
                                   int8_t* rem_mapq, u64* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, void* stream) {
+    return cph_porec_to_edges_pf(read_idx, contig_idx, mapq, start, end, contig_len, n_records, n_contigs, min_mapq, min_order,
+                                 max_order, edge_length, read_offset, sorted_by_read, nullptr, rem_row, rem_col, rem_count, rem_mapq,
+                                 h_counts, ws, ws_bytes, h_ws_need, stream);
+}
+
+extern "C" int cph_porec_to_edges_pf(const u32* read_idx, const u32* contig_idx, const int8_t* mapq, const u32* start, const u32* end,
+                                     const i64* contig_len, u64 n_records, u32 n_contigs, int min_mapq, u32 min_order, u32 max_order,
+                                     u64 edge_length, u32 read_offset, int sorted_by_read, const cph_prefilter* prefilter,
+                                     u32* rem_row, u32* rem_col, u32* rem_count, int8_t* rem_mapq, u64* h_counts, void* ws,
+                                     size_t ws_bytes, size_t* h_ws_need, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     const u64 N = n_records;
     ARG_CHECK(N < (1ull << 32) - 8192);
     ARG_CHECK(n_contigs > 0 && n_contigs < (1u << 23));
+    PreF pfv;
+    ARG_CHECK(pf_view(prefilter, &pfv));
+    const bool pre = pfv.bed_ptr != nullptr || pfv.split_init != nullptr;
+    ARG_CHECK(!pre || N == 0 || (start && end));
     const int cb = bits_for(n_contigs);   // contig ids < n_contigs <= 2^cb - 1
     WS_BEGIN(ar);
-    PorecIn in{read_idx, contig_idx, mapq, start, end, contig_len, N, n_contigs, min_mapq, (i64)edge_length};
+    PorecIn in{read_idx, contig_idx, mapq, start, end, contig_len, N, n_contigs, min_mapq, (i64)edge_length, pfv};
     // ---- fast path: table grouped by read (two passes of the shared-memory tile kernel) ----
     const u32 ntiles = (u32)ceil_div(N > 0 ? N : 1, (size_t)PT_TILE);
     u32* scal = ar.take<u32>(4);   // [0] max kept read (fast) / max read (slow)  [1] unsorted flag  [2] scan total  [3] ticket
@@ -879,7 +1007,7 @@ extern "C" int cph_porec_to_edges(const u32* read_idx, const u32* contig_idx, co
         CUDA_TRY(cudaMemsetAsync(tile_state, 0, (size_t)ntiles * sizeof(u64), st));
         CUDA_TRY(pt_prepare());
         // bulk (TMA) window loads need 16-byte aligned columns; the edge filter reads two more columns -> plain loads
-        const int use_tma = edge_length == 0 && (((uintptr_t)read_idx | (uintptr_t)contig_idx | (uintptr_t)mapq) & 15) == 0;
+        const int use_tma = edge_length == 0 && !pre && (((uintptr_t)read_idx | (uintptr_t)contig_idx | (uintptr_t)mapq) & 15) == 0;
         pt_launch(ntiles, st, in, use_tma, min_order, max_order, read_offset, (unsigned long long*)tile_state, scal, rem_row, rem_col,
                   rem_count, rem_mapq);
         KERNEL_CHECK();
@@ -1156,7 +1284,8 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     if (N == 0) return CPH_OK;
     ARG_CHECK(h_read_idx && h_contig_idx && h_mapq && d_read_idx && d_contig_idx && d_mapq);
     ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq);
-    PorecIn in{d_read_idx, d_contig_idx, d_mapq, nullptr, nullptr, nullptr, N, n_contigs, min_mapq, (i64)0};
+    PorecIn in{d_read_idx, d_contig_idx, d_mapq, nullptr, nullptr, nullptr, N, n_contigs, min_mapq, (i64)0,
+               PreF{nullptr, nullptr, nullptr, nullptr, 0, 0, 0}};
     u64 chunk = packed ? pk_chunk : (chunk_records ? chunk_records : (u64)(8u << 20));
     if (!packed) chunk = ceil_div(chunk, (size_t)PT_TILE) * PT_TILE;
     const u32 nchunks = (u32)ceil_div(N, chunk);

@@ -16,6 +16,7 @@ namespace {
 
 constexpr int TPB = 256;
 constexpr u32 RS_MAX_SMEM_BINS = 49152;      // 192 KB of u32 bins
+constexpr u32 RS_PERSIST_MAX_BINS = 24576;   // 2 x u32 per bin: 192 KB
 constexpr u32 RS_CHUNK = 32768;              // entries per CTA; count < 2^16 each -> u32 bins cannot overflow
 
 __device__ __forceinline__ size_t gtid() { return (size_t)blockIdx.x * blockDim.x + threadIdx.x; }
@@ -58,6 +59,56 @@ __global__ void __launch_bounds__(1024) row_sums_kernel(const u32* __restrict__ 
             u32 v = bins[i];
             if (v) atomicAdd(&rowsum[i], (unsigned long long)v);
         }
+    }
+}
+
+// Persistent variant for n <= RS_PERSIST_MAX_BINS: a few CTAs per SM, each streams a contiguous slice with 128-bit loads
+// (four entries per load) into shared-memory bins kept as a low u32 word plus a carry word, and flushes every bin ONCE.
+// The chunked kernel above flushes n bins per 32 Ki entries: 2.2e7 global atomics onto 4 000 addresses on workload C.
+__global__ void __launch_bounds__(512) row_sums_persist_kernel(const u32* __restrict__ rem_row, const u32* __restrict__ rem_count,
+                                                               const int8_t* __restrict__ rem_mapq, u64 nnz, u32 n, int min_mapq,
+                                                               const u8* __restrict__ row_drop, u32 cmask,
+                                                               unsigned long long* __restrict__ rowsum, u32* __restrict__ max_count) {
+    extern __shared__ u32 bins[];      // [0, n): low words   [n, 2n): carries
+    for (u32 i = threadIdx.x; i < 2 * n; i += blockDim.x) bins[i] = 0;
+    __syncthreads();
+    const u64 quads = (nnz + 3) / 4;
+    const u64 per = (quads + gridDim.x - 1) / gridDim.x;
+    const u64 q_lo = (u64)blockIdx.x * per, q_hi = min(quads, q_lo + per);
+    u32 mx = 0;
+    auto add = [&](u32 rr, u32 cc, int qq) {
+        const u32 r = rr & CPH_ROWM;
+        if (qq < min_mapq || r >= n || (row_drop && row_drop[r])) return;
+        const u32 c = cc & cmask;
+        mx = max(mx, c);
+        const u32 old = atomicAdd(&bins[r], c);
+        if (old + c < old) atomicAdd(&bins[n + r], 1u);
+    };
+    const bool vec = ((((uintptr_t)rem_row) | ((uintptr_t)rem_count)) & 15) == 0 && (rem_mapq == nullptr || (((uintptr_t)rem_mapq) & 3) == 0);
+    for (u64 q = q_lo + threadIdx.x; q < q_hi; q += blockDim.x) {
+        const u64 t = q * 4;
+        if (vec && t + 4 <= nnz) {
+            const uint4 r4 = *reinterpret_cast<const uint4*>(rem_row + t);
+            const uint4 c4 = *reinterpret_cast<const uint4*>(rem_count + t);
+            int q0 = 127, q1 = 127, q2 = 127, q3 = 127;
+            if (rem_mapq) {
+                const u32 m4 = *reinterpret_cast<const u32*>(rem_mapq + t);
+                q0 = (int8_t)(m4 & 0xff); q1 = (int8_t)((m4 >> 8) & 0xff); q2 = (int8_t)((m4 >> 16) & 0xff); q3 = (int8_t)(m4 >> 24);
+            }
+            add(r4.x, c4.x, q0); add(r4.y, c4.y, q1); add(r4.z, c4.z, q2); add(r4.w, c4.w, q3);
+        } else {
+            for (u64 u = t; u < min(nnz, t + 4); ++u) add(rem_row[u], rem_count[u], rem_mapq ? (int)rem_mapq[u] : 127);
+        }
+    }
+    if (max_count) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((threadIdx.x & 31) == 0 && mx) atomicMax(max_count, mx);
+    }
+    __syncthreads();
+    for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
+        const u64 v = ((u64)bins[n + i] << 32) | bins[i];
+        if (v) atomicAdd(&rowsum[i], (unsigned long long)v);
     }
 }
 
@@ -536,6 +587,22 @@ extern "C" int cph_row_sums(const u32* rem_row, const u32* rem_count, const int8
     CUDA_TRY(cudaMemsetAsync(rowsum, 0, (size_t)n_contigs * sizeof(u64), st));
     if (max_count) CUDA_TRY(cudaMemsetAsync(max_count, 0, sizeof(u32), st));
     if (nnz == 0) return CPH_OK;
+    if (n_contigs <= RS_PERSIST_MAX_BINS && nnz >= (1u << 20)) {
+        const size_t sm = (size_t)n_contigs * 2 * sizeof(u32);
+        static int sms = 0;
+        if (!sms) {
+            int dev = 0;
+            CUDA_TRY(cudaGetDevice(&dev));
+            CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        }
+        CUDA_TRY(cudaFuncSetAttribute(row_sums_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        int per_sm = (int)((220u * 1024u) / (sm + 1024));
+        per_sm = per_sm < 1 ? 1 : (per_sm > 4 ? 4 : per_sm);
+        row_sums_persist_kernel<<<sms * per_sm, 512, sm, st>>>(rem_row, rem_count, rem_mapq, nnz, n_contigs, min_mapq, row_drop,
+                                                             packed ? CPH_CNTM : 0xffffffffu, (unsigned long long*)rowsum, max_count);
+        KERNEL_CHECK();
+        return CPH_OK;
+    }
     const int use_smem = n_contigs <= RS_MAX_SMEM_BINS;
     const size_t smem = use_smem ? (size_t)n_contigs * sizeof(u32) : 0;
     if (smem > 48 * 1024) CUDA_TRY(cudaFuncSetAttribute(row_sums_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -137,9 +137,43 @@ class DeviceCSR:
 # ------------------------------------------------------------------------------------------------
 # stage 1: tables -> raw edge-major
 # ------------------------------------------------------------------------------------------------
+@dataclass
+class PreFilter:
+    """extractor pre-filters (include/cph.h: cph_prefilter).  The contig column(s) then hold codes of the ORIGINAL contig
+    names, 0 <= code < n_names; bed_* describe the HCR intervals per name (sorted by name, start), split_init the first
+    split bin of every name."""
+    n_names: int
+    bed_ptr: object = None        # int64 [n_names + 1]
+    bed_start: object = None      # uint32
+    bed_end: object = None        # uint32
+    hcr_invert: bool = False
+    split_length: int = 0
+    split_init: object = None     # uint32 [n_names], 0xffffffff = name not in the split map
+
+    def struct(self, dev):
+        """-> (ctypes struct, tensors to keep alive)"""
+        keep = []
+
+        def d(x, dt):
+            if x is None:
+                return None
+            t = to_dev(x, dt, dev)
+            keep.append(t)
+            return t.data_ptr()
+        hcr = self.bed_ptr is not None
+        pf = _lib.Prefilter(d(self.bed_ptr, torch.int64) if hcr else None, d(self.bed_start, torch.uint32) if hcr else None,
+                            d(self.bed_end, torch.uint32) if hcr else None, int(bool(self.hcr_invert)),
+                            int(self.split_length or 0), d(self.split_init, torch.uint32) if self.split_length else None,
+                            int(self.n_names))
+        return pf, keep
+
+
 def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, contig_len=None, min_mapq=1,
-                   min_order=2, max_order=50, edge_length=0, read_offset=0, device=None) -> RawEdges:
+                   min_order=2, max_order=50, edge_length=0, read_offset=0, device=None, prefilter: PreFilter = None) -> RawEdges:
     dev = _dev(device)
+    if prefilter is not None:
+        return _porec_to_edges_pf(read_idx, contig_idx, mapq, n_contigs, start, end, contig_len, min_mapq, min_order,
+                                  max_order, edge_length, read_offset, dev, prefilter)
     if not edge_length:
         host = _host_columns(read_idx, contig_idx, mapq)
         if host is not None and host[0].numel() >= STREAM_MIN_RECORDS:
@@ -165,6 +199,30 @@ def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, 
     call_ws("cph_porec_to_edges", dev, ptr(r), ptr(c), ptr(q), ptr(st), ptr(en), ptr(ln), N, int(n_contigs),
             int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0,
             ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+
+
+def _porec_to_edges_pf(read_idx, contig_idx, mapq, n_contigs, start, end, contig_len, min_mapq, min_order, max_order,
+                       edge_length, read_offset, dev, prefilter):
+    r = to_dev(read_idx, torch.uint32, dev)
+    c = to_dev(contig_idx, torch.uint32, dev)
+    q = to_dev(mapq, torch.int8, dev)
+    st = to_dev(start, torch.uint32, dev); en = to_dev(end, torch.uint32, dev)
+    ln = to_dev(contig_len, torch.int64, dev) if (edge_length and not prefilter.split_length) else None
+    if prefilter.split_length:
+        edge_length = 0                      # hypergraph.py:1406-1424: the split branch has no edge filter
+    N = r.numel()
+    cap = max(N, 1)
+    o_row = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_col = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
+    o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
+    h = (C.c_uint64 * 2)()
+    pf, keep = prefilter.struct(dev)
+    call_ws("cph_porec_to_edges_pf", dev, ptr(r), ptr(c), ptr(q), ptr(st), ptr(en), ptr(ln), N, int(n_contigs),
+            int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0, C.byref(pf),
+            ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    del keep
     return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
 
 
@@ -240,13 +298,16 @@ def _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_o
 
 
 def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig_len=None, min_mapq=1,
-                   edge_length=0, device=None) -> RawEdges:
+                   edge_length=0, device=None, prefilter: PreFilter = None) -> RawEdges:
     dev = _dev(device)
     c1 = to_dev(chrom1, torch.uint32, dev)
     c2 = to_dev(chrom2, torch.uint32, dev)
     q = to_dev(mapq, torch.int8, dev)
     P = c1.numel()
-    if edge_length:
+    if prefilter is not None:
+        p1 = to_dev(pos1, torch.uint32, dev); p2 = to_dev(pos2, torch.uint32, dev)
+        ln = to_dev(contig_len, torch.int64, dev) if edge_length else None
+    elif edge_length:
         p1 = to_dev(pos1, torch.uint32, dev); p2 = to_dev(pos2, torch.uint32, dev)
         ln = to_dev(contig_len, torch.int64, dev)
     else:
@@ -257,8 +318,14 @@ def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig
     o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
     o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
     h = (C.c_uint64 * 2)()
-    call_ws("cph_pairs_to_edges", dev, ptr(c1), ptr(c2), ptr(q), ptr(p1), ptr(p2), ptr(ln), P, int(n_contigs),
-            int(min_mapq), int(edge_length or 0), ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+    if prefilter is not None:
+        pf, keep = prefilter.struct(dev)
+        call_ws("cph_pairs_to_edges_pf", dev, ptr(c1), ptr(c2), ptr(q), ptr(p1), ptr(p2), ptr(ln), P, int(n_contigs),
+                int(min_mapq), int(edge_length or 0), C.byref(pf), ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
+        del keep
+    else:
+        call_ws("cph_pairs_to_edges", dev, ptr(c1), ptr(c2), ptr(q), ptr(p1), ptr(p2), ptr(ln), P, int(n_contigs),
+                int(min_mapq), int(edge_length or 0), ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
     return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
 
 

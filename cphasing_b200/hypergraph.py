@@ -5,8 +5,9 @@ Text decoding (gzip / TSV -> columns) stays on the host, as SURVEY.md 8(a1) scop
 index join is a pandas categorical lookup; every filter, the per-read order filter, the
 ``group_by(read, contig)`` and the sort by contig run on the device (csrc/edges.cu).  Both classes
 also accept in-memory columnar input (``from_arrays``), which is what bench.py's end-to-end leg and
-the parity tests use.  HCR-BED filtering and contig splitting are host-side pre-filters in the
-reference (hypergraph.py:786-893, 1406-1424) and are not re-implemented here (out of scope, 8(a1)).
+the parity tests use.  The HCR-BED midpoint filter (hypergraph.py:1721-1752, 786-893) and the split-contig row index
+(:1406-1424, 994-1023) run inside the same record-filter step of the kernels (``cph_prefilter``): the host only
+decodes the BED file and builds the per-contig interval table.
 """
 from __future__ import annotations
 
@@ -75,21 +76,67 @@ def _name_codes(series, contig_idx):
     return out
 
 
+def _name_space(contig_idx, split_length, split_contig_boundarys):
+    """code space of the contig column(s): the contig index itself, or -- with splitting on -- the ORIGINAL contig names
+    of split_contig_boundarys (cli.py:4776-4779: name -> first split bin), in its own order."""
+    if split_length and split_contig_boundarys is not None:
+        return {c: i for i, c in enumerate(split_contig_boundarys.keys())}
+    return contig_idx
+
+
+def _hcr_table(hcr_bed, names):
+    """BED (chrom, start, end) -> (ptr int64[n + 1], start u32, end u32) ordered by (name code, start); stable, so that
+    among equal starts the last listed interval is the one join_asof(backward) lands on (hypergraph.py:1721-1731)."""
+    if isinstance(hcr_bed, (str, bytes)) or hasattr(hcr_bed, "__fspath__"):
+        bed = pd.read_csv(hcr_bed, sep="\t", header=None, usecols=[0, 1, 2], names=["chrom", "start", "end"], comment="#")
+    elif isinstance(hcr_bed, pd.DataFrame):
+        bed = hcr_bed.iloc[:, :3].copy()
+        bed.columns = ["chrom", "start", "end"]
+    else:
+        c, a, b = hcr_bed
+        bed = pd.DataFrame({"chrom": list(c), "start": np.asarray(a), "end": np.asarray(b)})
+    n = len(names)
+    code = bed["chrom"].map(names.get)
+    ok = code.notna().to_numpy()
+    code = code[ok].to_numpy().astype(np.int64)
+    st = bed["start"].to_numpy()[ok].astype(np.uint32)
+    en = bed["end"].to_numpy()[ok].astype(np.uint32)
+    order = np.lexsort((st, code))          # lexsort is stable: file order survives among equal (code, start)
+    code, st, en = code[order], st[order], en[order]
+    ptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(np.bincount(code, minlength=n), out=ptr[1:])
+    return ptr, st, en
+
+
+def _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_invert):
+    """-> (D.PreFilter or None, name -> code dict of the contig column)"""
+    names = _name_space(contig_idx, split_length, split_contig_boundarys)
+    if not (hcr_bed is not None or (split_length and split_contig_boundarys is not None)):
+        return None, names
+    pf = D.PreFilter(n_names=len(names), hcr_invert=bool(hcr_invert))
+    if hcr_bed is not None:
+        pf.bed_ptr, pf.bed_start, pf.bed_end = _hcr_table(hcr_bed, names)
+    if split_length and split_contig_boundarys is not None:
+        pf.split_length = int(split_length)
+        pf.split_init = np.array([int(v) for v in split_contig_boundarys.values()], dtype=np.uint32)
+    return pf, names
+
+
 class HyperExtractor:
     """hypergraph.py:1483-1911."""
 
     def __init__(self, pore_c_table_pathes, contig_idx, contigsizes, min_order=2, max_order=50, min_alignments=30,
                  min_quality=1, edge_length=2e6, split_length=None, split_contig_boundarys=None, hcr_bed=None,
                  hcr_invert=False, threads=4, is_parquet=False, log_dir="logs", _tables=None):
-        if split_length or hcr_bed:
-            raise NotImplementedError("contig splitting / HCR BED pre-filters are host-side steps outside the "
-                                      "accelerated path (SURVEY.md 8a1)")
         self.pore_c_table_pathes = list(pore_c_table_pathes) if pore_c_table_pathes is not None else []
         self.contig_idx = contig_idx
         self.contigsizes = contigsizes
         self.min_order, self.max_order = int(min_order), int(max_order)
         self.min_quality = int(min_quality)
         self.edge_length = int(edge_length) if edge_length else 0
+        self.split_length, self.split_contig_boundarys = split_length, split_contig_boundarys
+        self.hcr_bed, self.hcr_invert = hcr_bed, hcr_invert
+        self.prefilter, self.names = _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_invert)
         self.threads = threads
         self.is_parquet = is_parquet
         tables = _tables if _tables is not None else [self._load(p) for p in self.pore_c_table_pathes]
@@ -114,7 +161,7 @@ class HyperExtractor:
             except (pd.errors.EmptyDataError, ValueError):
                 logger.error(f"The pore-c table `{path}` is empty or malformed, please check it.")   # :1621-1630
                 sys.exit(-1)
-        return {"read_idx": df["read_idx"].to_numpy(), "contig": _name_codes(df["chrom"], self.contig_idx),
+        return {"read_idx": df["read_idx"].to_numpy(), "contig": _name_codes(df["chrom"], self.names),
                 "mapq": df["mapq"].to_numpy(), "start": df["start"].to_numpy(), "end": df["end"].to_numpy()}
 
     def generate_edges(self, tables):
@@ -125,12 +172,13 @@ class HyperExtractor:
         for t in tables:
             raw = D.porec_to_edges(t["read_idx"], t["contig"], t["mapq"], n, start=t.get("start"), end=t.get("end"),
                                    contig_len=ln, min_mapq=self.min_quality, min_order=self.min_order,
-                                   max_order=self.max_order, edge_length=self.edge_length, read_offset=offset)
+                                   max_order=self.max_order, edge_length=self.edge_length, read_offset=offset,
+                                   prefilter=self.prefilter)
             parts.append(raw)
-            # disjoint read ids per input file (hypergraph.py:1871-1875)
-            if len(tables) > 1:
-                r = np.asarray(t["read_idx"])
-                offset += (int(r.max()) if len(r) else 0) + 1
+            # disjoint read ids per input file (hypergraph.py:1871-1875): the next file starts after the largest
+            # SURVIVING (already shifted) read id of this one
+            if len(tables) > 1 and raw.nnz:
+                offset = raw.n_cols
         raw = parts[0] if len(parts) == 1 else _concat_raw(parts, n)
         logger.info(f"Only retained Pore-C concatemer that: {self.min_order} <= contig order <= {self.max_order}.")
         e = _edges_from_raw(raw, self.contig_idx, self.contigsizes)
@@ -153,14 +201,25 @@ class Extractor:
     def __init__(self, pairs_pathes, contig_idx, contigsizes, min_quality=1, hcr_bed=None, hcr_invert=False, threads=4,
                  edge_length=2e6, split_length=None, split_contig_boundarys=None, max_q0_ratio=0.0, low_memory=True,
                  log_dir="logs", _tables=None):
-        if split_length or hcr_bed:
-            raise NotImplementedError("contig splitting / HCR BED pre-filters are host-side steps outside the "
-                                      "accelerated path (SURVEY.md 8a1)")
+        if max_q0_ratio:
+            raise NotImplementedError("max_q0_ratio (per-contig MAPQ-0 ratio filter) is not implemented")
         self.pairs_pathes = list(pairs_pathes) if pairs_pathes is not None else []
         self.contig_idx = contig_idx
         self.contigsizes = contigsizes
         self.min_mapq = int(min_quality)
         self.edge_length = int(edge_length) if edge_length else 0
+        split_on = bool(split_length and split_contig_boundarys is not None)
+        if split_on and hcr_bed is not None:
+            # _filter_pairs_hcr (:786-893) looks the ORIGINAL names of the pairs up in a table keyed by the SPLIT names
+            # (:679-731): every join comes back null and no pair survives.  Refused rather than reproduced or "fixed".
+            raise NotImplementedError("pairs + HCR BED + split contigs: the reference's path filters every pair out")
+        if split_on and self.edge_length:
+            # likewise the edge filter joins lengths on original names against the split contigsizes (:977-992): the CLI
+            # default --edge-length would empty the table; run with edge_length=0 when splitting pairs
+            logger.warning("pairs + split contigs: the edge filter is skipped (the reference's join of original names "
+                           "against split contig sizes keeps nothing)")
+            self.edge_length = 0
+        self.prefilter, self.names = _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_invert)
         tables = _tables if _tables is not None else [self._load(p) for p in self.pairs_pathes]
         self.edges = self.generate_edges(tables)
 
@@ -177,7 +236,7 @@ class Extractor:
         except (pd.errors.EmptyDataError, ValueError):
             logger.error(f"The pairs `{path}` is empty, can not load anything, please check it.")
             sys.exit(-1)
-        return {"chrom1": _name_codes(df["chrom1"], self.contig_idx), "chrom2": _name_codes(df["chrom2"], self.contig_idx),
+        return {"chrom1": _name_codes(df["chrom1"], self.names), "chrom2": _name_codes(df["chrom2"], self.names),
                 "mapq": df["mapq"].to_numpy().astype(np.int8), "pos1": df["pos1"].to_numpy().astype(np.uint32),
                 "pos2": df["pos2"].to_numpy().astype(np.uint32)}
 
@@ -191,7 +250,8 @@ class Extractor:
                        for k in keys}]
         t = tables[0]
         raw = D.pairs_to_edges(t["chrom1"], t["chrom2"], t["mapq"], n, pos1=t.get("pos1"), pos2=t.get("pos2"),
-                               contig_len=ln, min_mapq=self.min_mapq, edge_length=self.edge_length)
+                               contig_len=ln, min_mapq=self.min_mapq, edge_length=self.edge_length,
+                               prefilter=self.prefilter)
         logger.info(f"Result of {raw.nnz:,} raw hyperedges of {raw.n_cols:,} pairs.")
         return _edges_from_raw(raw, self.contig_idx, self.contigsizes)
 

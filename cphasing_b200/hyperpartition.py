@@ -80,8 +80,8 @@ class HyperPartition:
                  min_quality2=2, mapq_filter_1_to_2=False, min_scaffold_length=10000, is_remove_misassembly=False,
                  is_recluster_contigs=False, disable_recluster_by_linkage=False, refine=False,
                  collapsed_contigs_df=None, threshold=0.01, max_round=1, threads=4, chunksize=None, **kw):
-        if split or ultra_long is not None or chunksize:
-            raise NotImplementedError("split contigs / ultra-long edges / chunked H are outside the accelerated path")
+        if ultra_long is not None or chunksize:
+            raise NotImplementedError("ultra-long edges / chunked H are outside the accelerated path")
         self.edges = edges
         if isinstance(contigsizes, dict):
             contigsizes = pd.DataFrame({"length": pd.Series(contigsizes)})
@@ -170,10 +170,14 @@ class HyperPartition:
         remove_contigs = set() if remove_contigs is None else set(remove_contigs)
         short = self.contigsizes[self.contigsizes < self.min_length].dropna().index.tolist()
         remove_contigs.update(short)
+        # with split contigs (`ctg|start_end` rows) the lists name the PARENT contigs (:372-391)
+        parent = (lambda x: x.rsplit("|", 1)[0]) if self.split else (lambda x: x)
         if self.whitelist:
-            remove_contigs.update(set(self.contigs) - set(self.whitelist))
+            wl = set(self.whitelist)
+            remove_contigs.update(x for x in self.contigs if parent(x) not in wl)
         if self.blacklist:
-            remove_contigs.update(set(self.blacklist))
+            bl = set(self.blacklist)
+            remove_contigs.update(x for x in self.contigs if parent(x) in bl) if self.split else remove_contigs.update(bl)
         if len(remove_contigs) == 0:
             return
         self.HG.remove_rows(remove_contigs)
@@ -381,9 +385,9 @@ class HyperPartition:
     #    processes (:2181-2187); CUDA contexts do not survive fork, so the groups run in-process, one after the other, on
     #    the same device-resident H.
     def incremental_partition(self, k, first_cluster=None):
-        if self.split or self.fasta is not None:
-            raise NotImplementedError("split contigs / on-the-fly `alleles` (sequence k-mer similarity) are outside the "
-                                      "accelerated path; pass an allele table or a prune table")
+        if self.fasta is not None:
+            raise NotImplementedError("on-the-fly `alleles` (sequence k-mer similarity) is outside the accelerated path; "
+                                      "pass an allele table or a prune table")
         k = list(k)
         self.P_allelic_idx, self.P_weak_idx = None, None                                   # :1736
         A = HyperGraph.clique_expansion_init(self.H, min_weight=self.min_weight)
@@ -472,6 +476,8 @@ class HyperPartition:
             else:
                 _A, self.K = first_irmm(self.resolution1)
             A1 = _A
+            if self.split:                                                                 # :1971-1972
+                _, self.K, _ = self.merge_split()
             self.K = self.filter_cluster()
             if k[0] and len(self.K) > k[0]:                                                # :1972-1998
                 if self.disable_merge_in_first:
@@ -541,6 +547,12 @@ class HyperPartition:
                 results.append(new_K)
                 assignments.append(ca)
         self.cluster_assignments = assignments
+        if self.split:                                                                     # :2204-2211
+            merged = []
+            for res in results:
+                self.K = res
+                merged.append(self.merge_split()[1])
+            results = merged
         self.inc_chr_idx = [i for i, res in enumerate(results) for _ in res]
         self.second_group_info = [f"{i}g{j}" for i, res in enumerate(results, 1) for j, _ in enumerate(res, 1)]
         self.K = [list(g) for res in results for g in res]
@@ -806,11 +818,69 @@ class HyperPartition:
             self.K = [sorted(int(x) for x in g) for g in new_K]
         return count
 
+    # -- hyperpartition.py:4075-4091: parent contig -> summed length of its split bins
+    def get_raw_contigsizes(self):
+        if getattr(self, "_raw_sizes", None) is None:
+            s = pd.Series(self.contig_sizes)
+            self._raw_sizes = s.groupby(s.index.str.rsplit("|", n=1).str[0], sort=False).sum().to_dict()
+        return self._raw_sizes
+
+    # -- hyperpartition.py:4136-4235.  Rows are split bins `ctg|start_end`; a parent contig goes, whole, to the group that
+    #    holds most of its clustered length (first such group on ties); groups left without a parent disappear.
+    #    -> (groups of parent names, groups of ALL bin indices of those parents, parent sizes)
+    def merge_split(self, secondary=False, confidence_threshold=0.0):
+        verts = np.asarray(self.vertices)
+        parents = pd.Series(verts).str.rsplit("|", n=1)
+        pname = parents.str[0].to_numpy()
+        span = parents.str[1].str.split("_")
+        blen = (span.str[1].astype(np.int64) - span.str[0].astype(np.int64)).to_numpy()
+        gid = np.full(len(verts), -1, dtype=np.int64)
+        order = []                                   # clustered bins in group-then-member order (first-seen order of parents)
+        for i, grp in enumerate(self.K):
+            g = np.asarray(list(grp), dtype=np.int64)
+            gid[g] = i
+            order.append(g)
+        order = np.concatenate(order) if order else np.zeros(0, dtype=np.int64)
+        best = {}
+        if len(order):
+            d = pd.DataFrame({"p": pname[order], "g": gid[order], "l": blen[order]})
+            tot = d.groupby(["p", "g"], sort=False)["l"].sum().reset_index()
+            # largest length, earliest group on ties (the reference's stable descending sort over groups in index order)
+            tot = tot.sort_values(["l", "g"], ascending=[False, True], kind="stable")
+            top = tot.drop_duplicates("p", keep="first").set_index("p")
+            psum = tot.groupby("p", sort=False)["l"].sum()
+            low = [(p, top.at[p, "l"] / psum[p]) for p in top.index if psum[p] and top.at[p, "l"] / psum[p] < confidence_threshold]
+            if low:
+                logger.warning(f"Found {len(low)} contigs with low support ratio (<{confidence_threshold}). "
+                               "They might be misassembled or chimeric.")
+            first_seen = pd.unique(d["p"])
+            best = {p: int(top.at[p, "g"]) for p in first_seen}
+        by_group = defaultdict(list)
+        for p, g in best.items():
+            by_group[g].append(p)
+        live = [g for g in range(len(self.K)) if by_group.get(g)]
+        new_of = {g: i for i, g in enumerate(live)}
+        merged = [by_group[g] for g in live]
+        bins = [[] for _ in live]
+        for v_idx, p in enumerate(pname):            # every bin of a placed parent follows it, clustered or not
+            g = best.get(p)
+            if g is not None and g in new_of:
+                bins[new_of[g]].append(v_idx)
+        if secondary:
+            inc = list(self.inc_chr_idx)
+            default = inc[-1] if inc else 0
+            self.inc_chr_idx = [inc[g] if g < len(inc) else default for g in live]
+        return merged, bins, self.get_raw_contigsizes()
+
     # -- hyperpartition.py:4238-4296: `ChrNN\t<count>\t<contigs>` after one round, `ChrNNgH` after the second round
     def to_cluster(self, output, merge=True):
         itv = self.idx_to_vertices
-        clusters = [[itv[x] for x in grp] for grp in self.K]
         inc = getattr(self, "inc_chr_idx", None)
+        if self.split and merge:
+            clusters, _, _ = self.merge_split(secondary=inc is not None)
+            inc = getattr(self, "inc_chr_idx", None)
+        else:
+            clusters = [[itv[x] for x in grp] for grp in self.K]
         with open(output, 'w') as out:
             if inc is not None:
                 n = min(len(inc), len(clusters))

@@ -77,6 +77,40 @@ int cph_porec_to_edges(const uint32_t* read_idx, const uint32_t* contig_idx, con
                        uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
                        uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 
+/* ---- extractor pre-filters (all device pointers; NULL / 0 = off) ------------------------------
+ * HCR BED: keep a Pore-C record iff its alignment midpoint start + (end - start) / 2 lies inside the LAST BED interval
+ * of the same contig whose start is <= the midpoint (polars join_asof(strategy="backward") + pos < end_bed,
+ * hypergraph.py:1721-1752; hcr_invert keeps the others); a pair iff EITHER end does (:786-893).
+ * split: the contig column(s) carry codes of the ORIGINAL contig names (0 <= code < n_names), the hyperedge row is
+ * split_init[code] + position / split_length with position = the midpoint (Pore-C, :1406-1424) or pos1 / pos2 (pairs,
+ * :994-1023); n_contigs is then the number of split bins and no edge filter applies (the reference's else-branch).
+ * With either filter on, bed_ptr / split_init index the same code space of n_names names. */
+typedef struct cph_prefilter {
+    const uint64_t* bed_ptr;    /* [n_names + 1] offsets into bed_start / bed_end, intervals sorted by (name, start) */
+    const uint32_t* bed_start;
+    const uint32_t* bed_end;
+    int hcr_invert;
+    uint64_t split_length;      /* 0 = no splitting */
+    const uint32_t* split_init; /* [n_names] first split bin of each original contig; 0xffffffff = not in the map */
+    uint32_t n_names;
+} cph_prefilter;
+
+/* cph_pairs_to_edges / cph_porec_to_edges with the pre-filters above (`prefilter` is a HOST pointer, may be NULL).
+ * pos1/pos2 resp. start/end must be given when a filter is on. */
+int cph_pairs_to_edges_pf(const uint32_t* chrom1, const uint32_t* chrom2, const int8_t* mapq,
+                          const uint32_t* pos1, const uint32_t* pos2, const int64_t* contig_len,
+                          uint64_t n_pairs, uint32_t n_contigs, int min_mapq, uint64_t edge_length,
+                          const cph_prefilter* prefilter,
+                          uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
+                          uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+int cph_porec_to_edges_pf(const uint32_t* read_idx, const uint32_t* contig_idx, const int8_t* mapq,
+                          const uint32_t* start, const uint32_t* end, const int64_t* contig_len,
+                          uint64_t n_records, uint32_t n_contigs, int min_mapq, uint32_t min_order,
+                          uint32_t max_order, uint64_t edge_length, uint32_t read_offset, int sorted_by_read,
+                          const cph_prefilter* prefilter,
+                          uint32_t* rem_row, uint32_t* rem_col, uint32_t* rem_count, int8_t* rem_mapq,
+                          uint64_t* h_counts, void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
+
 /* Host-table form of cph_porec_to_edges for tables grouped by read (what _load_and_filter_single,
  * hypergraph.py:1700-1789, hands to process_pore_c_table): h_* are HOST columns, d_* caller-owned device
  * staging columns of n_records elements.  The columns are copied in chunks of `chunk_records` (0 = default)

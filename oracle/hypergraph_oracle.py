@@ -27,10 +27,47 @@ COL_DTYPE = np.int32           # _config.py:18  HYPERGRAPH_COL_DTYPE
 
 
 # --------------------------------------------------------------------------------------------
+# extractor pre-filters: HCR BED and split-contig index
+# --------------------------------------------------------------------------------------------
+def hcr_hits(names, pos, bed_names, bed_start, bed_end):
+    """hypergraph.py:1721-1752 / :786-893 restated without polars: ``join_asof(strategy="backward", by=chrom, on=pos)``
+    against the BED sorted by start picks, per record, the LAST interval of the same contig whose start <= pos; the record
+    is inside the HCR iff ``pos < end`` of that interval (no match -> outside).  Plain per-record loop over a per-contig
+    list: deliberately the slow, obviously-correct form.  Returns a bool array."""
+    names = np.asarray(names); pos = np.asarray(pos).astype(np.int64)
+    by = {}
+    for c, a, b in zip(np.asarray(bed_names).tolist(), np.asarray(bed_start).tolist(), np.asarray(bed_end).tolist()):
+        by.setdefault(c, []).append((a, b))
+    for c in by:
+        by[c].sort(key=lambda t: t[0])          # python's sort is stable, like the sort("start_bed") it restates
+    out = np.zeros(len(names), dtype=bool)
+    for i, (c, p) in enumerate(zip(names.tolist(), pos.tolist())):
+        hit = None
+        for a, b in by.get(c, ()):
+            if a <= p:
+                hit = b
+            else:
+                break
+        out[i] = hit is not None and p < hit
+    return out
+
+
+def split_index(names, pos, split_init, split_length):
+    """hypergraph.py:1406-1424 / :994-1023: row = init_idx[name] + pos // split_length; names outside the map drop
+    (inner join).  split_init: dict name code -> first bin (or array with -1 for missing).  Returns (row, ok)."""
+    names = np.asarray(names).astype(np.int64); pos = np.asarray(pos).astype(np.int64)
+    init = np.asarray(split_init).astype(np.int64)
+    ok = (names >= 0) & (names < len(init))
+    i0 = np.where(ok, init[np.where(ok, names, 0)], -1)
+    ok &= i0 >= 0
+    return i0 + pos // int(split_length), ok
+
+
+# --------------------------------------------------------------------------------------------
 # stage 1a: Pore-C records -> hyperedge triplets
 # --------------------------------------------------------------------------------------------
 def porec_edges(read_idx, contig_idx, mapq, start=None, end=None, contig_len=None,
-                min_mapq=1, min_order=2, max_order=50, edge_length=0, n_contigs=None):
+                min_mapq=1, min_order=2, max_order=50, edge_length=0, n_contigs=None, hcr=None, split=None):
     """hypergraph.py:1774-1775 (mapq >= min_quality), :1438-1457 (edge filter),
     :1461-1468 (distinct-contig order filter), :1470-1477 (group_by read,contig -> count, max mapq),
     :1877-1889 (sort by contig; cast).  Records whose contig is not in the index (inner join
@@ -42,10 +79,23 @@ def porec_edges(read_idx, contig_idx, mapq, start=None, end=None, contig_len=Non
     contig_idx = np.asarray(contig_idx).astype(np.int64)
     mapq = np.asarray(mapq).astype(np.int8)
     keep = np.ones(read_idx.shape, dtype=bool)
-    if n_contigs is not None:
+    if n_contigs is not None and split is None and hcr is None:
         keep &= contig_idx < n_contigs
     if min_mapq > 0:                                        # :1774
         keep &= mapq >= min_mapq
+    if hcr is not None or split is not None:
+        # hcr = (bed_names, bed_start, bed_end, invert); split = (split_init per name code, split_length).  The contig
+        # column holds codes of the ORIGINAL names here.  UInt32 midpoint as in :1738 / :1419.
+        mid = np.asarray(start).astype(np.int64) + (np.asarray(end).astype(np.int64) - np.asarray(start).astype(np.int64)) // 2
+        if hcr is not None:
+            hit = hcr_hits(contig_idx, mid, hcr[0], hcr[1], hcr[2])
+            keep &= ~hit if hcr[3] else hit
+        if split is not None:
+            contig_idx, ok = split_index(contig_idx, mid, split[0], split[1])
+            keep &= ok
+            edge_length = 0                                  # the split branch of :1406-1457 has no edge filter
+        if n_contigs is not None:
+            keep &= (contig_idx >= 0) & (contig_idx < n_contigs)
     if edge_length:
         # pos = start + (end-start)//2 ; keep pos < L_e or (length - pos) < L_e   (:1452-1456)
         st = np.asarray(start).astype(np.int64)
@@ -87,7 +137,7 @@ def porec_edges(read_idx, contig_idx, mapq, start=None, end=None, contig_len=Non
 # stage 1b: Hi-C pairs -> triplets
 # --------------------------------------------------------------------------------------------
 def pairs_edges(chrom1, chrom2, mapq, pos1=None, pos2=None, contig_len=None,
-                min_mapq=1, edge_length=0, n_contigs=None):
+                min_mapq=1, edge_length=0, n_contigs=None, hcr=None, split=None):
     """hypergraph.py:970-971 (mapq filter), :977-992 (both-ends edge filter, note the strict
     ``pos > length - edge_length`` form), :1031 (col = running row number of the surviving pairs),
     :1033-1044 (two triplets per pair, sorted by row), :1287-1292 (count = ones u32).
@@ -97,10 +147,19 @@ def pairs_edges(chrom1, chrom2, mapq, pos1=None, pos2=None, contig_len=None,
     c2 = np.asarray(chrom2).astype(np.int64)
     q = np.asarray(mapq).astype(np.int8)
     keep = np.ones(c1.shape, dtype=bool)
-    if n_contigs is not None:
+    if n_contigs is not None and hcr is None and split is None:
         keep &= (c1 < n_contigs) & (c2 < n_contigs)
     if min_mapq > 0:
         keep &= q >= min_mapq
+    if hcr is not None:                                      # :786-893: a pair stays iff EITHER end is inside an HCR
+        any_in = hcr_hits(c1, pos1, hcr[0], hcr[1], hcr[2]) | hcr_hits(c2, pos2, hcr[0], hcr[1], hcr[2])
+        keep &= ~any_in if hcr[3] else any_in
+    if split is not None:                                    # :994-1023
+        c1, ok1 = split_index(c1, pos1, split[0], split[1])
+        c2, ok2 = split_index(c2, pos2, split[0], split[1])
+        keep &= ok1 & ok2
+    if n_contigs is not None and (hcr is not None or split is not None):
+        keep &= (c1 >= 0) & (c1 < n_contigs) & (c2 >= 0) & (c2 < n_contigs)
     if edge_length:
         L = np.asarray(contig_len).astype(np.int64)
         p1 = np.asarray(pos1).astype(np.int64); p2 = np.asarray(pos2).astype(np.int64)

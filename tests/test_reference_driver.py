@@ -1,0 +1,149 @@
+"""The drop-in boundary, shown rather than asserted.
+
+* ``test_dropin_matches_reference_driver_golden``: cphasing_b200.HyperPartition against groups produced by the REFERENCE's
+  own driver (single_partition, incremental_partition / _incremental_partition) on its own HyperGraph / IRMM
+  (tests/golden/make_golden_driver.py -> ref_driver.npz).
+* ``test_reference_driver_on_dropin_classes``: the reference's ``cphasing.hyperpartition`` module (the unmodified install under
+  baseline/_ref, which travels to the GPU box) with ``HyperGraph, IRMM, extract_incidence_matrix2`` rebound to
+  cphasing_b200's -- the import switch of INTEGRATION.md -- runs ITS single_partition and incremental_partition; the groups
+  must equal those of cphasing_b200.HyperPartition.
+* ``test_merge_split_matches_reference`` (CPU): the split-contig merge against the reference's own method.
+"""
+import contextlib
+import io
+import os
+import sys
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from helpers import GOLDEN
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "baseline"))
+sys.path.insert(0, GOLDEN)
+
+
+def partition_of(hp, names):
+    idx = {nm: i for i, nm in enumerate(names)}
+    return {frozenset(idx[hp.vertices[v]] for v in grp) for grp in hp.K if len(grp)}
+
+
+def partition_of_labels(lab):
+    return {frozenset(np.where(lab == g)[0].tolist()) for g in np.unique(lab[lab >= 0])}
+
+
+def reference_module():
+    import ref_loader
+    if not ref_loader.available():
+        pytest.skip("the reference install (baseline/_ref) is not present")
+    import make_golden_driver as mgd
+    mgd.pandas_writable_shim()
+    ref_loader.load()
+    import cphasing.hyperpartition as rhp
+    return rhp, mgd
+
+
+@pytest.fixture(scope="module")
+def setup(tmp_path_factory):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    import make_golden_driver as mgd
+    from cphasing_b200 import hypergraph as hg, synth
+    g = synth.make_genome(mgd.N_CONTIGS, mgd.CHROMS, mgd.PLOIDY, seed=mgd.SEED)
+    t = synth.porec_table(g, mgd.M, seed=mgd.SEED + 1)
+    ex = hg.HyperExtractor.from_arrays(t["read_idx"], t["contig_idx"], t["mapq"], g.contig_idx, g.contigsizes,
+                                       min_quality=1, edge_length=0)
+    g2, trip = mgd.inputs()
+    pt = mgd.prune_table(g2, trip)
+    wd = tmp_path_factory.mktemp("driver")
+    ptf = str(wd / "prune.table")
+    pt.to_csv(ptf, sep="\t", header=False, index=False)
+    return g, ex.edges, pd.DataFrame({"length": pd.Series(g.contigsizes)}), ptf, wd, mgd
+
+
+def run_dropin(setup, method, extra, use_pt):
+    from cphasing_b200.hyperpartition import HyperPartition
+    g, edges, sizes, ptf, wd, mgd = setup
+    hp = HyperPartition(edges, sizes, k=[mgd.CHROMS, mgd.PLOIDY], prunetable=ptf if use_pt else None, **mgd.KW, **extra)
+    if method == "single":
+        hp.single_partition(k=mgd.CHROMS * mgd.PLOIDY)
+    else:
+        hp.incremental_partition([mgd.CHROMS, mgd.PLOIDY])
+    return hp
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["single", "single_prune_leiden", "incremental", "incremental_prune"])
+def test_dropin_matches_reference_driver_golden(setup, case):
+    g, edges, sizes, ptf, wd, mgd = setup
+    gold = np.load(os.path.join(GOLDEN, "ref_driver.npz"))
+    method, extra, use_pt = mgd.CASES[case]
+    hp = run_dropin(setup, method, extra, use_pt)
+    assert partition_of(hp, g.names) == partition_of_labels(gold[f"{case}_labels"])
+    if method == "incremental":
+        # same chromosome -> haplotype structure: groups of one first-round cluster share their inc_chr_idx
+        lab = gold[f"{case}_labels"]
+        ref_chr = {frozenset(np.where(lab == gi)[0].tolist()): int(c) for gi, c in enumerate(gold[f"{case}_inc_chr_idx"])}
+        idx = {nm: i for i, nm in enumerate(g.names)}
+        mine = {frozenset(idx[hp.vertices[v]] for v in grp): c for grp, c in zip(hp.K, hp.inc_chr_idx)}
+        same_chr = lambda d: {frozenset(k for k in d if d[k] == c) for c in set(d.values())}
+        assert same_chr(mine) == same_chr(ref_chr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("case", ["single_prune_leiden", "incremental_prune", "incremental"])
+def test_reference_driver_on_dropin_classes(setup, case):
+    rhp, _ = reference_module()
+    from cphasing_b200.algorithms import hypergraph as bah
+    g, edges, sizes, ptf, wd, mgd = setup
+    method, extra, use_pt = mgd.CASES[case]
+    saved = (rhp.HyperGraph, rhp.IRMM, rhp.extract_incidence_matrix2)
+    rhp.HyperGraph, rhp.IRMM, rhp.extract_incidence_matrix2 = bah.HyperGraph, bah.IRMM, bah.extract_incidence_matrix2
+    cwd = os.getcwd()
+    os.chdir(wd)
+    try:
+        with contextlib.redirect_stdout(io.StringIO()):
+            hp = rhp.HyperPartition(edges, sizes, k=[mgd.CHROMS, mgd.PLOIDY], prunetable=ptf if use_pt else None,
+                                    ultra_complex=0, **mgd.KW, **extra)
+            if method == "single":
+                hp.single_partition(k=mgd.CHROMS * mgd.PLOIDY)
+            else:
+                hp.incremental_partition([mgd.CHROMS, mgd.PLOIDY])
+    finally:
+        os.chdir(cwd)
+        rhp.HyperGraph, rhp.IRMM, rhp.extract_incidence_matrix2 = saved
+    mine = run_dropin(setup, method, extra, use_pt)
+    assert partition_of(hp, g.names) == partition_of(mine, g.names)
+    assert len(hp.K) == mgd.CHROMS * mgd.PLOIDY
+
+
+def test_merge_split_matches_reference():
+    rhp, _ = reference_module()
+    from cphasing_b200.hyperpartition import HyperPartition as HP
+    rng = np.random.default_rng(0)
+    names, sizes = [], {}
+    for c in range(60):
+        L = int(rng.integers(100, 1500))
+        for a in range(0, L, 250):
+            b = min(L, a + 250)
+            names.append(f"ctg{c}|{a}_{b}")
+            sizes[names[-1]] = b - a
+    verts = np.array(names)
+    perm = rng.permutation(len(verts))[:int(0.8 * len(verts))]
+    K = [sorted(perm[i::6].tolist()) for i in range(6)] + [[]]
+
+    def mk(cls):
+        o = cls.__new__(cls)
+        o.vertices, o.K, o.contig_sizes, o.split = verts, [list(x) for x in K], dict(sizes), True
+        o.contigsizes = pd.DataFrame({"length": pd.Series(sizes)})
+        o._cached_raw_contigsizes = None
+        o.inc_chr_idx = [0, 0, 1, 1, 2, 2, 3]
+        return o
+    a, b = mk(rhp.HyperPartition), mk(HP)
+    for secondary in (False, True):
+        ra, rb = a.merge_split(secondary=secondary), b.merge_split(secondary=secondary)
+        assert ra[0] == rb[0] and ra[1] == rb[1] and ra[2] == rb[2]
+        assert list(a.inc_chr_idx) == list(b.inc_chr_idx)
