@@ -2,11 +2,13 @@
 
     python -m cphasing_b200 hypergraph     <table[.gz]> <contigsizes> <out.hg> [--pairs] ...     (cli.py:3709-3941)
     python -m cphasing_b200 hyperpartition <in.hg|table> <contigsizes> <out.clusters.txt> ...    (cli.py:3945-5360)
-    python -m cphasing_b200 kprune         <alleletable> <in.hg> <contigsizes> <out.prune.table> (cli.py:3525-3669)
+    python -m cphasing_b200 kprune         <AlleleTable> <contacts.tsv> -o <out.prune.table> [-n -m -fc -t]   (cli.py:3525-3669)
+    python -m cphasing_b200 utils hg2contacts <in.hg> <contigsizes> -o <out.contacts>            (cli.py:9290-9401)
 
 Same positional arguments, option names and defaults (cphasing/_config.py:30-55) for the options that belong to the
-accelerated path; the reference's other ~60 options steer stages that are out of scope (splitting, HCR, fasta alleles,
-plotting) and are not accepted here.  This is a thin argparse layer over HyperExtractor / Extractor / HyperPartition.
+accelerated path (HCR BED, contig splitting, prune / allele tables included); the reference's remaining options steer stages
+that are out of scope (fasta alleles, ultra-long reads, plotting) and are not accepted.  This is a thin argparse layer over
+HyperExtractor / Extractor / HyperPartition / KPrunerRust.
 """
 from __future__ import annotations
 
@@ -39,27 +41,49 @@ def read_contigsizes(path):
 
 
 def load_hg(path):
-    from .algorithms.hypergraph import HyperEdges, numpy_dec_hook
-    with open(path, "rb") as fh:
-        e = msgspec.msgpack.decode(fh.read(), type=HyperEdges, dec_hook=numpy_dec_hook)
-    e.to_numpy()
-    return e
+    """cli.py:4811-4834; the binary sidecar next to the file is preferred when it is current (cphasing_b200/hgio.py)"""
+    from . import hgio
+    return hgio.load(path)
+
+
+def split_contigs(sizes, split_length):
+    """cli.py:4776-4790: contigs cut into `split_length` bins named `ctg|start_end`.  -> (split sizes DataFrame, dict
+    original contig -> index of its first bin)"""
+    names, lens, first = [], [], {}
+    for c, L in zip(sizes.index, sizes["length"].astype(int)):
+        first[c] = len(names)
+        for a in range(0, max(L, 1), split_length):
+            b = min(L, a + split_length)
+            names.append(f"{c}|{a}_{b}")
+            lens.append(b - a)
+    return pd.DataFrame({"length": lens}, index=pd.Index(names, name="contig")), first
 
 
 def _extract(args, sizes):
+    """-> (extractor, contig sizes actually indexed: the split bins when --split-length is on)"""
     from . import hypergraph as hg
+    sl = getattr(args, "split_length", "none")
+    if str(sl).lower() == "auto":
+        raise NotImplementedError("--split-length auto (utilities.determine_split_length) is not built; give a length or `none`")
+    sl = None if str(sl).lower() in ("none", "no", "null", "0") else _size(sl)
+    boundarys = None
+    if sl:
+        sizes, boundarys = split_contigs(sizes, sl)
     idx = {c: i for i, c in enumerate(sizes.index)}
     sz = sizes["length"].to_dict()
     el = _size(args.edge_length) if args.edge_length else 0
+    pre = dict(hcr_bed=getattr(args, "hcr_bed", None), hcr_invert=getattr(args, "hcr_invert", False), split_length=sl,
+               split_contig_boundarys=boundarys)
     if args.pairs:
-        return hg.Extractor([args.table], idx, sz, min_quality=args.min_quality, edge_length=el, threads=args.threads)
+        return hg.Extractor([args.table], idx, sz, min_quality=args.min_quality, edge_length=el, threads=args.threads,
+                            **pre), sizes
     return hg.HyperExtractor([args.table], idx, sz, min_order=args.min_order, max_order=args.max_order,
-                             min_quality=args.min_quality, edge_length=el, threads=args.threads)
+                             min_quality=args.min_quality, edge_length=el, threads=args.threads, **pre), sizes
 
 
 def cmd_hypergraph(args):
     sizes = read_contigsizes(args.contigsizes)
-    ex = _extract(args, sizes)
+    ex, _ = _extract(args, sizes)
     ex.save(args.output)
     return 0
 
@@ -76,9 +100,12 @@ def _allele_table(path):
 def cmd_hyperpartition(args):
     from .hyperpartition import HyperPartition
     sizes = read_contigsizes(args.contigsizes)
+    split = False
     if args.porec or args.pairs:
         args.table = args.hypergraph
-        edges = _extract(args, sizes).edges
+        ex, sizes2 = _extract(args, sizes)
+        split = sizes2 is not sizes
+        sizes, edges = sizes2, ex.edges
     else:
         edges = load_hg(args.hypergraph)
     n = [int(x) if x else 0 for x in re.split(r":|x|\|", args.n)] if args.n else None      # cli.py:4637
@@ -90,7 +117,7 @@ def cmd_hyperpartition(args):
                                                                           else "basal")
     if not n and args.resolution1 < 0:
         args.resolution1 = args.init_resolution1          # no group number to search for: one clustering at the start value
-    hp = HyperPartition(edges, sizes, k=n, alleletable=at, prunetable=args.prunetable, normalize=args.normalize,
+    hp = HyperPartition(edges, sizes, k=n, alleletable=at, prunetable=args.prunetable, normalize=args.normalize, split=split,
                         allelic_factor=args.allelic_factor, cross_allelic_factor=args.cross_allelic_factor,
                         allelic_similarity=args.allelic_similarity, min_allelic_overlap=args.min_allelic_overlap,
                         disable_merge_in_first=args.disable_merge_in_first, whitelist=read_list(args.whitelist),
@@ -113,18 +140,23 @@ def cmd_hyperpartition(args):
 
 
 def cmd_kprune(args):
+    """cli.py:3642-3669: AlleleTable + contacts -> prune table, through the KPrunerRust-shaped class (in-process, no binary)"""
+    from .kprune import KPrunerRust
+    kp = KPrunerRust(args.alleletable, args.contacts, args.output, method=args.method, first_cluster=args.first_cluster,
+                     count_re=args.count_re, norm_method=args.norm_method, threads=args.threads).run()
+    logger.info(f"Wrote {len(kp.allelic_pairs)} allelic and {len(kp.weak_pairs)} cross-allelic pairs to `{args.output}`.")
+    return 0
+
+
+def cmd_hg2contacts(args):
+    """cli.py:9350-9401: .hg -> H -> unweighted clique expansion -> 3-column contacts (what `kprune` reads)"""
     from .algorithms.hypergraph import HyperGraph
-    from .kprune import KPruneHyperGraph
     sizes = read_contigsizes(args.contigsizes)
     edges = load_hg(args.hypergraph)
     HG = HyperGraph(edges, min_quality=args.min_quality, mapq_filter=False)
     H = HG.incidence_matrix(args.min_contacts)
     A = HyperGraph.clique_expansion_init(H, min_weight=args.min_weight, use_high_order=False)    # hyperpartition.py:1566
-    kp = KPruneHyperGraph(_allele_table(args.alleletable), A, {c: i for i, c in enumerate(HG.nodes)})
-    kp.run()
-    kp.get_prune_table().to_csv(args.output, sep="\t", header=None, index=None)              # core.py:711-723
-    logger.info(f"Wrote {len(kp.allelic_pairs)} allelic and {len(kp.weak_pairs)} cross-allelic pairs "
-                f"to `{args.output}`.")
+    HyperGraph.to_contacts(A, HG.nodes, min_weight=args.min_weight, output=args.output)
     return 0
 
 
@@ -140,6 +172,10 @@ def build_parser():
         p.add_argument("--max-order", type=int, default=MAX_ORDER)
         p.add_argument("-q", "--min-quality", type=int, default=1)
         p.add_argument("-t", "--threads", type=int, default=4)
+        p.add_argument("-hcr", "--hcr-bed", dest="hcr_bed", default=None, help="BED of high-confidence regions")
+        p.add_argument("-hcr-invert", "--hcr-invert", dest="hcr_invert", action="store_true")
+        p.add_argument("-sl", "--split-length", dest="split_length", default="none",
+                       help="split contigs into bins of this length (`none`: off; the reference's `auto` rule is not built)")
 
     g = sub.add_parser("hypergraph", aliases=["hg"])
     g.add_argument("table"); g.add_argument("contigsizes"); g.add_argument("output")
@@ -178,12 +214,26 @@ def build_parser():
     h.add_argument("--max-round", type=int, default=1)
     h.set_defaults(fn=cmd_hyperpartition)
 
-    k = sub.add_parser("kprune")
-    k.add_argument("alleletable"); k.add_argument("hypergraph"); k.add_argument("contigsizes"); k.add_argument("output")
-    k.add_argument("-mc", "--min-contacts", type=int, default=MIN_CONTACTS)
-    k.add_argument("-mw", "--min-weight", type=float, default=1.0)
-    k.add_argument("-q", "--min-quality", type=int, default=1)
+    k = sub.add_parser("kprune")                                                   # cli.py:3525-3645
+    k.add_argument("alleletable", metavar="AlleleTable")
+    k.add_argument("contacts", metavar="INPUT_CONTACTS_PATH")
+    k.add_argument("-o", "--output", default="prune.contig.table")
+    k.add_argument("-m", "--method", choices=["fast", "precise", "greedy"], default="precise")
+    k.add_argument("-fc", "--first-cluster", dest="first_cluster", default=None)
+    k.add_argument("-cr", "--countre", "--count-re", dest="count_re", default=None)
+    k.add_argument("-n", "--norm-method", dest="norm_method", choices=["none", "cis", "cis_unique", "auto"], default="none")
+    k.add_argument("-t", "--threads", type=int, default=4)
     k.set_defaults(fn=cmd_kprune)
+
+    u = sub.add_parser("utils")
+    usub = u.add_subparsers(dest="util", required=True)
+    c = usub.add_parser("hg2contacts")                                             # cli.py:9290-9401
+    c.add_argument("hypergraph"); c.add_argument("contigsizes")
+    c.add_argument("-o", "--output", default="hypergraph.expansion.contacts")
+    c.add_argument("-mc", "--min-contacts", type=int, default=MIN_CONTACTS)
+    c.add_argument("-mw", "--min-weight", type=float, default=1.0)
+    c.add_argument("-q", "--min-quality", type=int, default=1)
+    c.set_defaults(fn=cmd_hg2contacts)
     return ap
 
 

@@ -14,13 +14,12 @@ from __future__ import annotations
 import logging
 import sys
 
-import msgspec
 import numpy as np
 import pandas as pd
 import torch
 
 from . import device as D
-from .algorithms.hypergraph import HyperEdges, LazyTriplets, numpy_enc_hook
+from .algorithms.hypergraph import HyperEdges, LazyTriplets
 
 logger = logging.getLogger(__name__)
 
@@ -53,9 +52,11 @@ def _materialise(edges):
 
 
 def _save(edges, output):
+    """hypergraph.py:1302-1306, 1907-1911: the same msgpack document (readable by the reference) plus the binary sidecar
+    `output + '.bin'` that `hgio.load` prefers (0.1 s instead of 8 s per 8e7 ints on the way back in)."""
+    from . import hgio
     _materialise(edges)
-    with open(output, "wb") as out:
-        out.write(msgspec.msgpack.encode(edges, enc_hook=numpy_enc_hook))      # hypergraph.py:1302-1306, 1907-1911
+    hgio.save(edges, output)
     logger.info(f"Successful output graph into `{output}`")
 
 

@@ -42,12 +42,26 @@ def allele_groups(allele_pairs, n, max_alleles=1):
     return ptr_, idx
 
 
-def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False):
-    """-> (flag uint8[nnz] device, row_of int32[nnz] device[, best_with, best_all])."""
+def groups_from_first(first, n):
+    """{contig: its one allele} -> the CSR-like (ptr, idx) form of `allele_groups`"""
+    ptr_ = np.zeros(n + 1, dtype=np.int64)
+    ks = np.array(sorted(k for k in first if 0 <= k < n), dtype=np.int64)
+    cnt = np.zeros(n, dtype=np.int64)
+    cnt[ks] = 1
+    np.cumsum(cnt, out=ptr_[1:])
+    idx = np.zeros(max(len(ks), 1), dtype=np.int32)
+    idx[:len(ks)] = [first[int(k)] for k in ks]
+    return ptr_, idx
+
+
+def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False, first=None):
+    """-> (flag uint8[nnz] device, row_of int32[nnz] device[, best_with, best_all]).
+    first: {contig: allele} overriding the allele groups derived from `allele_pairs` (max_alleles = 1 only)."""
     dev = a.indptr.device
     n = a.n
     pairs = _pairs_array(allele_pairs)
-    ag_ptr, ag_idx = allele_groups(pairs, n, max_alleles)
+    ag_ptr, ag_idx = groups_from_first(first, n) if (first is not None and max_alleles == 1) else \
+        allele_groups(pairs, n, max_alleles)
     agp = D.to_dev(ag_ptr, torch.int64, dev); agi = D.to_dev(ag_idx, torch.int32, dev)
     alr = D.to_dev(pairs[:, 0].copy(), torch.int64, dev); alc = D.to_dev(pairs[:, 1].copy(), torch.int64, dev)
     row_of = torch.empty(max(a.nnz, 1), dtype=torch.int32, device=dev)
@@ -63,12 +77,12 @@ def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False
     return out + (bw[:a.nnz], ba[:a.nnz]) if want_scores else out
 
 
-def kprune_arrays(A, allele_pairs, max_alleles=1):
+def kprune_arrays(A, allele_pairs, max_alleles=1, first=None):
     """A: scipy matrix / DeviceBackedCSR; allele_pairs: (i, j) contig-index pairs in allele-table order.
     Returns (allelic int64[ka, 2], weak int64[kw, 2]), rows sorted by (i, j), i < j -- plus the (c, c) rows the
     reference's weak list carries (see `_self_pairs`).  No Python-level loop over the pairs."""
     a = graphops.upload_adjacency(A)
-    flag, row_of = kprune_device(a, allele_pairs, max_alleles)
+    flag, row_of = kprune_device(a, allele_pairs, max_alleles, first=first)
     cols = a.indices
 
     def pick(code):             # CSR order = sorted by (row, col) already
@@ -76,7 +90,7 @@ def kprune_arrays(A, allele_pairs, max_alleles=1):
         return np.stack([D.to_host(row_of[ix]).astype(np.int64), D.to_host(cols[ix]).astype(np.int64)], axis=1)
     allelic, weak = pick(1), pick(2)
     if max_alleles == 1:
-        selfp = np.asarray(sorted(_self_pairs(a, allele_pairs)), dtype=np.int64).reshape(-1, 2)
+        selfp = np.asarray(sorted(_self_pairs(a, allele_pairs, first)), dtype=np.int64).reshape(-1, 2)
         if selfp.size:
             n = max(a.n, 1)
             pos = np.searchsorted(weak[:, 0] * n + weak[:, 1], selfp[:, 0] * n + selfp[:, 1])
@@ -96,16 +110,17 @@ def kprune_pairs(A, allele_pairs, max_alleles=1):
     return list(map(tuple, allelic.tolist())), list(map(tuple, weak.tolist()))
 
 
-def _self_pairs(a: D.DeviceCSR, allele_pairs):
+def _self_pairs(a: D.DeviceCSR, allele_pairs, first=None):
     """The reference's `A.setdiag(0)` (kprune.py:419) stores an explicit zero on every diagonal cell and `triu(A)` keeps
     stored zeros (:427), so every (c, c) is a candidate pair as well.  Its 2x2 block is [c, al] x [c, al]: the straight
     matching scores 0, the crossed one A[c, al] + A[al, c] (minus the allelic zeroing of the upper triangle, :466), so
     (c, c) lands in the weak list exactly when c has an allele group and a stored non-zero contact with it.  n look-ups."""
-    first = {}
-    for x, y in allele_pairs:
-        x = int(x); y = int(y)
-        if x not in first:
-            first[x] = y
+    if first is None:
+        first = {}
+        for x, y in allele_pairs:
+            x = int(x); y = int(y)
+            if x not in first:
+                first[x] = y
     cs = np.array([c for c, al in first.items() if al in first and 0 <= c < a.n and 0 <= al < a.n and c != al],
                   dtype=np.int64)
     if cs.size == 0:
@@ -150,6 +165,11 @@ class KPruneHyperGraph:
     def __init__(self, alleletable, A, contig2idx, max_alleles=1):
         self.alleletable = alleletable
         df = allele_frame(alleletable)
+        # allele group = the FIRST partner listed for a contig in the UNFILTERED table; the contig has a group only if that
+        # partner (and the contig itself) is in contig2idx -- a later, surviving partner does not step in (kprune.py:437-447)
+        g = df.groupby(1, sort=False)[2].first()
+        g = g[g.index.isin(contig2idx) & g.isin(contig2idx)]
+        self.allele_group_db = {int(contig2idx[k]): int(contig2idx[v]) for k, v in g.items()}
         df[1] = df[1].map(contig2idx.get)
         df[2] = df[2].map(contig2idx.get)
         df = df.dropna(subset=[1, 2])
@@ -164,7 +184,7 @@ class KPruneHyperGraph:
 
     def run(self):
         pairs = self.alleletable_idx[[1, 2]].to_numpy()
-        al, wk = kprune_arrays(self.A, pairs, self.max_alleles)
+        al, wk = kprune_arrays(self.A, pairs, self.max_alleles, first=self.allele_group_db)
         logger.info(f"Removed {len(al)} allelic contacts.")
         logger.info(f"Removed {len(wk)} weak contacts with allelic.")
         self.allelic_pairs = np.concatenate([self.allelic_pairs, al])
@@ -217,3 +237,110 @@ class KPruneHyperGraph:
             res2 = res.rename(columns={'contig1': 'contig2', 'contig2': 'contig1', 'mz1': 'mz2', 'mz2': 'mz1'})
             res = pd.concat([res, res2[res.columns]], axis=0)
         return res
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# File contract of `cphasing-rs kprune` (kprune.py:51-85, cli.py:3525-3670; call sites hyperpartition.py:1573-1586,
+# 1704-1718):   kprune <AlleleTable> <contacts.tsv> <out.prune.table> -n NORM -f FIRST_CLUSTER -w WHITELIST -t T -m METHOD
+# The Rust source is not in the reference tree, so its arithmetic is restated from what the tree does say:
+# the in-tree Python scorers (KPruneHyperGraph :385-552 = first listed allele, KPruner :269-335 = every listed allele) and
+# the option help texts.  PARITY UNPINNED for everything beyond `-n none -m fast|precise`: options whose meaning only the
+# binary defines raise instead of guessing silently.
+# ------------------------------------------------------------------------------------------------------------------
+UNPINNED = "parity unpinned (cphasing-rs absent)"
+
+
+def read_contacts(path):
+    """3-column contacts TSV `contig1<TAB>contig2<TAB>weight` written by HyperGraph.to_contacts
+    (algorithms/hypergraph.py:712-753: rows i <= j of A) -> (names list, scipy CSR symmetric float64)."""
+    from scipy.sparse import coo_matrix
+    df = pd.read_csv(path, sep="\t", header=None, names=["c1", "c2", "w"], comment="#",
+                     dtype={"c1": str, "c2": str, "w": np.float64})
+    cat = pd.Categorical(pd.concat([df["c1"], df["c2"]], ignore_index=True))
+    names = list(cat.categories)
+    k = len(df)
+    i, j = np.asarray(cat.codes[:k], dtype=np.int64), np.asarray(cat.codes[k:], dtype=np.int64)
+    w = df["w"].to_numpy()
+    off = i != j
+    n = len(names)
+    A = coo_matrix((np.concatenate([w, w[off]]), (np.concatenate([i, j[off]]), np.concatenate([j, i[off]]))), shape=(n, n))
+    A = A.tocsr()
+    A.sum_duplicates()
+    A.sort_indices()
+    return names, A
+
+
+def read_first_cluster(path):
+    """cluster table `group<TAB>n<TAB>ctg ctg ...` (core.py:1060-) -> dict contig -> group number"""
+    out = {}
+    with open(path) as fh:
+        for gi, line in enumerate(fh):
+            f = line.rstrip("\n").split("\t")
+            if len(f) >= 3:
+                for c in f[2].split(" "):
+                    if c:
+                        out[c] = gi
+    return out
+
+
+class KPrunerRust:
+    """Same constructor and `run()` as the reference's wrapper of the `cphasing-rs kprune` binary (kprune.py:51-85), but the
+    scoring runs in-process on the device (csrc/kprune.cu) and no subprocess is started."""
+    METHODS = {"fast": 1, "precise": 5}          # alleles per contig that enter the score block (KP_MAXL - 1 = 5)
+
+    def __init__(self, alleletable, contacts, output="prune.contig.table", method="greedy", first_cluster=None, count_re=None,
+                 whitelist=None, norm_method="none", threads=4, log_dir="logs"):
+        self.alleletable = alleletable
+        self.contacts = contacts
+        self.output = output
+        self.method = method
+        self.first_cluster = None if (not first_cluster or first_cluster == "none") else first_cluster
+        self.count_re = None if (not count_re or count_re == "none") else count_re
+        self.whitelist = None if (not whitelist or whitelist == "none") else whitelist
+        self.norm_method = norm_method
+        self.threads = threads
+        if self.method not in self.METHODS:
+            raise NotImplementedError(f"kprune -m {self.method}: only the binary defines this method; {UNPINNED}.  "
+                                      "`fast` scores the first listed allele (KPruneHyperGraph), `precise` every listed "
+                                      "allele (KPruner)")
+        if self.norm_method not in ("none", "cis"):
+            raise NotImplementedError(f"kprune -n {self.norm_method}: only the binary defines this normalisation; {UNPINNED}")
+        if self.count_re is not None:
+            raise NotImplementedError(f"kprune --count-re: restriction-site normalisation is defined by the binary only; {UNPINNED}")
+
+    def run(self):
+        names, A = read_contacts(self.contacts)
+        if self.norm_method == "cis":
+            # contacts scaled by the cis (self) contacts of both contigs: w_ij / sqrt(w_ii w_jj); contigs without a cis
+            # contact keep their raw weights.  The binary's exact formula is not in the tree.
+            logger.warning(f"kprune -n cis: w_ij / sqrt(w_ii * w_jj) is this implementation's reading of the option; {UNPINNED}")
+            d = A.diagonal().astype(np.float64)
+            s = np.where(d > 0, 1.0 / np.sqrt(np.where(d > 0, d, 1.0)), 1.0)
+            C = A.tocoo()
+            A = type(A)((C.data * s[C.row] * s[C.col], (C.row, C.col)), shape=A.shape).tocsr()
+            A.sort_indices()
+        idx = {c: i for i, c in enumerate(names)}
+        keep = None
+        if self.whitelist is not None:
+            wl = {l.strip().split()[0] for l in open(self.whitelist) if l.strip()}
+            keep = np.array([c in wl for c in names])
+        if self.first_cluster is not None:
+            # "Use the first cluster results to execute kprune" (cli.py:3594-3601): only contacts inside one first-round
+            # group are candidates; contigs outside every group take no part
+            grp = read_first_cluster(self.first_cluster)
+            g = np.array([grp.get(c, -1) for c in names], dtype=np.int64)
+            C = A.tocoo()
+            ok = (g[C.row] >= 0) & (g[C.row] == g[C.col])
+            A = type(A)((C.data[ok], (C.row[ok], C.col[ok])), shape=A.shape).tocsr()
+            A.sort_indices()
+        if keep is not None:
+            C = A.tocoo()
+            ok = keep[C.row] & keep[C.col]
+            A = type(A)((C.data[ok], (C.row[ok], C.col[ok])), shape=A.shape).tocsr()
+            A.sort_indices()
+        kp = KPruneHyperGraph(self.alleletable, A, idx, max_alleles=self.METHODS[self.method])
+        kp.run()
+        kp.get_prune_table().to_csv(self.output, sep="\t", header=None, index=None)          # core.py:711-723
+        logger.info(f"Successful output the allelic and cross-allelic information into `{self.output}`")
+        self.kp = kp
+        return kp

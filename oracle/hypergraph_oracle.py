@@ -333,7 +333,7 @@ def allele_group_first(pairs):
     return db
 
 
-def kprune_hypergraph(A, allele_pairs):
+def kprune_hypergraph(A, allele_pairs, first_group=None):
     """kprune.py:407-517 (KPruneHyperGraph.run).
 
     A: csr adjacency (diagonal ignored, :419).  allele_pairs: list of (i, j) index pairs in
@@ -356,7 +356,9 @@ def kprune_hypergraph(A, allele_pairs):
         L[a, b] = 0                       # :466 only the upper entry is zeroed
     D = L.todok()
     pairs -= set(al)
-    grp = allele_group_first(allele_pairs)
+    # first_group: {contig: allele} taken from the UNFILTERED name table (get_allele_group, :437-447) when the contig
+    # index does not cover the whole allele table; by default the first partner among the given index pairs
+    grp = allele_group_first(allele_pairs) if first_group is None else dict(first_group)
     # `self.A.setdiag(0)` (:419) stores an explicit zero on EVERY diagonal cell and triu(A) keeps stored zeros, so every
     # (c, c) is a candidate pair too (:427).  Its 2x2 block is [c, al] x [c, al]: straight = 0, cross = A[c,al] + A[al,c]
     # after the allelic zeroing of the upper triangle -- the reference lists (c, c) as weak whenever c touches its allele.

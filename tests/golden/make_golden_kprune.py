@@ -81,6 +81,29 @@ def main():
     out["allele_group"] = np.array(sorted((int(a), int(b)) for a, b in grp.items()), dtype=np.int64)
     print("allelic", len(out["allelic"]), "weak", len(out["weak"]), "self pairs in weak",
           int((out["weak"][:, 0] == out["weak"][:, 1]).sum()))
+    # second case: the contig index does NOT cover the whole allele table (what HyperPartition hands over after its
+    # min_contacts / min_length / min_cis_weight filters).  A contig whose FIRST listed partner is missing gets no allele
+    # group -- a later, surviving partner does not step in (kprune.py:437-447).
+    rng = np.random.default_rng(64)
+    first_partner = {}
+    for a, b, *_ in al:
+        first_partner.setdefault(int(a), int(b))
+    multi = [a for a in first_partner if sum(1 for x, *_ in al if int(x) == a) > 1]
+    drop = set(int(first_partner[a]) for a in rng.choice(multi, size=min(10, len(multi)), replace=False))
+    drop |= set(int(x) for x in rng.choice(g.n, size=4, replace=False))
+    keep = np.array([i for i in range(g.n) if i not in drop], dtype=np.int64)
+    sub_idx = {g.names[i]: j for j, i in enumerate(keep)}
+    A_sub = A[keep][:, keep].tocsr()
+    with contextlib.redirect_stdout(io.StringIO()):
+        k2 = kp.KPruneHyperGraph(at, A_sub.copy(), sub_idx)
+    k2.run()
+    out["sub_keep"] = keep
+    out["sub_allelic"] = np.array(sorted(map(tuple, k2.allelic_prune_list)), dtype=np.int64).reshape(-1, 2)
+    out["sub_weak"] = np.array(sorted(map(tuple, k2.weak_prune_list)), dtype=np.int64).reshape(-1, 2)
+    out["sub_allele_group"] = np.array(sorted((int(a), int(b)) for a, b in k2.allele_group_db.items()), dtype=np.int64)
+    n_lost = sum(1 for a in first_partner if a not in drop and first_partner[a] in drop)
+    print("subset case: kept", len(keep), "contigs;", n_lost, "contigs lose their group; allelic", len(out["sub_allelic"]),
+          "weak", len(out["sub_weak"]))
     try:
         pt = k.get_prune_table()
         out["table_shape"] = np.array(pt.shape, dtype=np.int64)

@@ -52,3 +52,21 @@ def test_no_cuda_means_loud_failure():
     import numpy as np
     with pytest.raises(_lib.CphError):
         D.porec_to_edges(np.zeros(1, np.uint32), np.zeros(1, np.uint32), np.zeros(1, np.int8), 1)
+
+
+def test_kprune_cli_contract_and_unpinned_modes():
+    """`cphasing kprune AlleleTable INPUT_CONTACTS_PATH -o out -n .. -m .. -fc .. -t ..` (cli.py:3525-3645) parses; options whose
+    meaning only the absent cphasing-rs binary defines refuse loudly instead of being ignored."""
+    from cphasing_b200 import cli
+    from cphasing_b200.kprune import KPrunerRust, UNPINNED
+    a = cli.build_parser().parse_args(["kprune", "allele.table", "c.contacts", "-o", "p.table", "-n", "cis", "-m", "fast",
+                                       "-fc", "first.clusters.txt", "-t", "8"])
+    assert (a.alleletable, a.contacts, a.output, a.norm_method, a.method, a.first_cluster, a.threads) == \
+        ("allele.table", "c.contacts", "p.table", "cis", "fast", "first.clusters.txt", 8)
+    d = cli.build_parser().parse_args(["kprune", "a", "c"])
+    assert (d.output, d.method, d.norm_method, d.threads) == ("prune.contig.table", "precise", "none", 4)
+    for kw in (dict(method="greedy"), dict(method="fast", norm_method="cis_unique"), dict(method="fast", norm_method="auto"),
+               dict(method="fast", count_re="x.counts")):
+        with pytest.raises(NotImplementedError, match="parity unpinned"):
+            KPrunerRust("a", "c", "o", **kw)
+    assert "cphasing-rs" in UNPINNED

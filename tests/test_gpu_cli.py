@@ -56,8 +56,41 @@ def test_cli_files_end_to_end(tmp_path):
     run("hyperpartition", str(table), str(sizes), str(out1), "--porec", "-e", "0", "-n", "20")
     l1 = out1.read_text().strip().split("\n")
     assert len(l1) == 20 and l1[0].startswith("Chr01\t")
-    # kprune: 7-column prune table (core.py:711-723)
+    # kprune, the reference's file contract (cli.py:3525-3669): AlleleTable + 3-column contacts -> 7-column prune table
+    # (core.py:711-723).  The contacts come from `utils hg2contacts` (cli.py:9290-9401), as in hyperpartition.py:1566-1572.
+    contacts = tmp_path / "hypergraph.expansion.contacts"
+    run("utils", "hg2contacts", str(hgf), str(sizes), "-o", str(contacts), "-mc", "5")
+    first = contacts.read_text().split("\n")[0].split("\t")
+    assert len(first) == 3 and first[0] in truth and float(first[2]) >= 1
     pt = tmp_path / "prune.table"
-    run("kprune", str(at), str(hgf), str(sizes), str(pt))
+    run("kprune", str(at), str(contacts), "-o", str(pt), "-m", "fast", "-n", "none", "-t", "2")
     rows = [l.split("\t") for l in pt.read_text().strip().split("\n")]
     assert all(len(r) == 7 for r in rows) and {r[6] for r in rows} == {"0", "1"}
+    # the same decision as the in-tree Python scorer restated by the oracle (KPruneHyperGraph, kprune.py:385-552) on the A
+    # the contacts file describes
+    from cphasing_b200.kprune import read_contacts, allele_frame
+    from oracle import hypergraph_oracle as orc
+    cn, A = read_contacts(str(contacts))
+    ci = {c: i for i, c in enumerate(cn)}
+    af = allele_frame(str(at))
+    fg = af.groupby(1, sort=False)[2].first()
+    first_group = {ci[k]: ci[v] for k, v in fg.items() if k in ci and v in ci}
+    pairs = [(ci[a], ci[b]) for a, b in zip(af[1], af[2]) if a in ci and b in ci]
+    al, wk = orc.kprune_hypergraph(A, pairs, first_group=first_group)
+    got_al = sorted((ci[r[0]], ci[r[1]]) for r in rows if r[6] == "0")
+    got_wk = sorted((ci[r[0]], ci[r[1]]) for r in rows if r[6] == "1")
+    assert got_al == al and got_wk == wk
+    # -fc: only contacts inside one first-round group are candidates -> a subset of the pairs above, none across groups
+    pt2 = tmp_path / "prune.fc.table"
+    run("kprune", str(at), str(contacts), "-o", str(pt2), "-m", "fast", "-fc", str(out1))
+    grp_of = {}
+    for gi, l in enumerate(l1):
+        for m in l.split("\t")[2].split(" "):
+            grp_of[m] = gi
+    rows2 = [l.split("\t") for l in pt2.read_text().strip().split("\n")]
+    assert 0 < len(rows2) <= len(rows)
+    assert all(grp_of[r[0]] == grp_of[r[1]] for r in rows2)
+    # -m precise scores every listed allele (KPruner, kprune.py:269-335): runs and still writes both types
+    pt3 = tmp_path / "prune.precise.table"
+    run("kprune", str(at), str(contacts), "-o", str(pt3))
+    assert {l.split("\t")[6] for l in pt3.read_text().strip().split("\n")} == {"0", "1"}

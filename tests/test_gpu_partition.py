@@ -54,6 +54,46 @@ def test_kprune_matches_oracle(case):
     assert len(al) > 50 and len(wk) > 50           # the case exercises both lists
 
 
+@pytest.mark.parametrize("max_alleles", [2, 3])
+def test_kprune_general_blocks_match_oracle(case, max_alleles):
+    """max_alleles > 1: the l1 x l2 score block over [contig, *alleles] of KPruner (kprune.py:269-335) with an exact
+    maximum-weight assignment, against the oracle's brute force over permutations."""
+    from cphasing_b200 import kprune
+    ah = case["ah"]
+    A = ah.HyperGraph.clique_expansion_init(case["H"], min_weight=1.0, use_high_order=False)
+    Ao = orc.clique_expansion(case["Ho"], use_high_order=False, min_weight=1.0).tocsr().astype(np.float64)
+    g = case["g"]
+    # every contig lists the contigs of the other haplotypes of its chromosome region: up to ploidy - 1 alleles each
+    from cphasing_b200 import synth
+    pairs = []
+    name2new = {nm: i for i, nm in enumerate(case["nodes"])}
+    names = sorted(g.contig_idx, key=g.contig_idx.get)
+    for a, b, *_ in synth.allele_pairs(g, seed=77, per_contig=3):
+        if names[a] in name2new and names[b] in name2new:
+            pairs.append((name2new[names[a]], name2new[names[b]]))
+    al, wk = kprune.kprune_pairs(A, pairs, max_alleles=max_alleles)
+    # oracle: allelic pairs (stored upper entries that are allele pairs) are zeroed in the upper triangle, then every other
+    # stored upper entry is scored on its block
+    from scipy.sparse import triu
+    Az = Ao.copy(); Az.setdiag(0); Az.eliminate_zeros()
+    U = triu(Az).tocoo()
+    stored = set(zip(U.row.tolist(), U.col.tolist()))
+    al_o = sorted(set((a, b) for a, b in pairs if a < b) & stored)
+    assert al == al_o
+    D = Az.todok()
+    for a, b in al_o:
+        D[a, b] = 0.0
+    lists = {}
+    for a, b in pairs:
+        if len(lists.setdefault(a, [])) < max_alleles:
+            lists[a].append(b)
+    score = lambda i, j: 0.0 if i == j else float(D.get((i, j), 0.0))
+    wk_o = orc.kprune_general(score, lists, sorted(stored - set(al_o)))
+    assert wk == sorted(wk_o)
+    assert len(wk) > 50
+    assert max(len(v) for v in lists.values()) == max_alleles
+
+
 def test_kprune_hypergraph_class_and_table(case):
     import pandas as pd
     from cphasing_b200 import kprune
@@ -445,3 +485,11 @@ def test_kprune_against_reference_run():
     assert kp.weak_prune_list == [tuple(x) for x in g["weak"]]
     pt = kp.get_prune_table()
     assert len(pt) == len(g["allelic"]) + len(g["weak"])
+    # second case: the contig index covers only part of the allele table (kprune.py:437-447)
+    keep = g["sub_keep"]
+    sub_names = {names[int(o)]: j for j, o in enumerate(keep)}
+    kp2 = kprune.KPruneHyperGraph(AT(), A[keep][:, keep].tocsr(), sub_names)
+    kp2.run()
+    assert sorted(kp2.allele_group_db.items()) == [tuple(x) for x in g["sub_allele_group"]]
+    assert kp2.allelic_prune_list == [tuple(x) for x in g["sub_allelic"]]
+    assert kp2.weak_prune_list == [tuple(x) for x in g["sub_weak"]]

@@ -134,3 +134,23 @@ def test_kprune_oracle_matches_reference_run():
     assert sum(1 for a, b in wk if a == b) > 100          # the (c, c) entries of the reference's weak list
     grp = orc.allele_group_first([tuple(x) for x in g["allele_pairs"]])
     assert sorted(grp.items()) == [tuple(x) for x in g["allele_group"]]
+
+
+def test_kprune_oracle_subset_index_matches_reference_run():
+    """the contig index covers only part of the allele table: groups come from the FIRST listed partner of the unfiltered
+    table and vanish when that partner is missing (kprune.py:437-447) -- second case of ref_kprune.npz"""
+    g = load_golden("kprune")
+    keep = g["sub_keep"]
+    A = csr_from(g, "A")[keep][:, keep].tocsr()
+    new = {int(o): j for j, o in enumerate(keep)}
+    first = {}
+    for a, b in g["allele_pairs"]:
+        first.setdefault(int(a), int(b))
+    first_group = {new[a]: new[b] for a, b in first.items() if a in new and b in new}
+    assert sorted(first_group.items()) == [tuple(x) for x in g["sub_allele_group"]]
+    pairs = [(new[int(a)], new[int(b)]) for a, b in g["allele_pairs"] if int(a) in new and int(b) in new]
+    al, wk = orc.kprune_hypergraph(A, pairs, first_group=first_group)
+    assert al == [tuple(x) for x in g["sub_allelic"]]
+    assert wk == [tuple(x) for x in g["sub_weak"]]
+    # and the shortcut the drop-in used to take (first SURVIVING partner) is NOT what the reference does
+    assert sorted(orc.allele_group_first(pairs).items()) != sorted(first_group.items())
