@@ -15,6 +15,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libcph.so")
 
 CPH_OK = 0
+ERR_TOO_LARGE = 4      # CPH_ERR_TOO_LARGE (include/cph.h)
 HEAD_BIT = 0x80000000
 ROW_MASK = 0x7FFFFFFF
 COUNT_MASK = 0x00FFFFFF
@@ -68,6 +69,7 @@ _SIGS = {
     "cph_diag_terms": (_I, [_P, _P, _P, _U32, _I, _I, _P, _P]),
     "cph_expand_accumulate": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _I, _P, _P]),
     "cph_expand_accumulate_diag": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P]),
+    "cph_expand_accumulate_banded": (_I, [_I, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_expand_accumulate_binned": (_I, [_I, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_expand_count": (_I, [_P, _P, _U32, _I, _F, C.POINTER(_U64)] + _WS),
     "cph_expand_emit": (_I, [_P, _P, _U32, _I, _F, _P, _P, _P, _P, _P, _P, _P]),

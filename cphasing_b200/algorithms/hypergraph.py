@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import gc
 import logging
+import os
 
 import msgspec
 import numpy as np
@@ -109,8 +110,16 @@ class LazyTriplets:
 # scipy CSR that is filled from the device on first touch and remembers its device twin
 # ------------------------------------------------------------------------------------------------
 class DeviceBackedCSR(csr_matrix):
+    """scipy CSR whose three arrays are fetched from the device on first touch and that remembers its device twin.
+
+    While the twin is attached the host arrays are READ-ONLY views: an in-place edit through numpy
+    (``A.data[mask] = 0``, ``A.data *= f`` -- idioms the reference uses on its own matrices, algorithms/hypergraph.py:1165,
+    kprune.py:419) raises instead of silently leaving the device copy, which the next stage would read, out of date.
+    scipy's own in-place methods (setdiag, eliminate_zeros, sum_duplicates, sort_indices, prune, item assignment, *=, /=)
+    first DETACH the matrix -- private writable host arrays, device twin dropped -- and then behave as usual; so does
+    re-assigning ``.data`` / ``.indices`` / ``.indptr``.  ``A.copy()`` is a plain, writable matrix."""
     _loader = None
-    _cph = None      # DeviceH (incidence) or DeviceCSR (adjacency) twin; dropped when the host copy is re-assigned
+    _cph = None      # DeviceH (incidence) or DeviceCSR (adjacency) twin; dropped when the host copy is detached
 
     def __init__(self, *args, loader=None, lazy_shape=None, handle=None, **kw):
         self._parts = [None, None, None]
@@ -126,7 +135,54 @@ class DeviceBackedCSR(csr_matrix):
         if self._loader is not None:
             ld, self._loader = self._loader, None
             self._parts = list(ld())
+            if self._cph is not None:
+                for a in self._parts:
+                    a.setflags(write=False)
         return self._parts[i]
+
+    def _detach(self):
+        """private writable host arrays; the device twin no longer describes this matrix"""
+        if self._loader is not None:
+            self._get(0)
+        if self._cph is not None:
+            self._cph = None
+            self._parts = [a if a.flags.writeable else a.copy() for a in self._parts]
+
+    def setdiag(self, *a, **k):
+        self._detach()
+        return csr_matrix.setdiag(self, *a, **k)
+
+    def eliminate_zeros(self):
+        self._detach()
+        return csr_matrix.eliminate_zeros(self)
+
+    def sum_duplicates(self):
+        if self._cph is not None and self.has_canonical_format:      # nothing to change: stay attached
+            return
+        self._detach()
+        return csr_matrix.sum_duplicates(self)
+
+    def sort_indices(self):
+        if self._cph is not None and self.has_sorted_indices:
+            return
+        self._detach()
+        return csr_matrix.sort_indices(self)
+
+    def prune(self):
+        self._detach()
+        return csr_matrix.prune(self)
+
+    def __setitem__(self, key, x):
+        self._detach()
+        return csr_matrix.__setitem__(self, key, x)
+
+    def __imul__(self, other):
+        self._detach()
+        return csr_matrix.__imul__(self, other)
+
+    def __itruediv__(self, other):
+        self._detach()
+        return csr_matrix.__itruediv__(self, other)
 
     def _set(self, i, v):
         if self._loader is not None:
@@ -405,7 +461,7 @@ class HyperGraph:
     @staticmethod
     def filter_by_weight(A, min_weight=0.1):
         if min_weight > 0:
-            A = csr_matrix(A)
+            A = csr_matrix(A, copy=True)          # the caller's matrix (and its device twin) stays as it was
             A.data[A.data < min_weight] = 0
             A.eliminate_zeros()
         return A
@@ -550,9 +606,12 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
     Graph preparation (:1120-1178) and the clustering (:1239-1252) run on the device; ``cluster_assignments`` offers
     ``.membership`` and iterates over groups like igraph's VertexClustering.  Deviations, all deliberate:
       * the clustering is deterministic (no RNG), so CPHASING_RANDOM_SEED has no effect;
-      * the caller's A is NOT modified in place (the reference multiplies ``A.data`` by allelic_factor in place on every
-        call, :1160-1164, so repeated calls in the resolution search flip the sign of allelic entries when
-        allelic_factor < 0);
+      * by default the caller's A is NOT modified.  The reference re-weights the caller's matrix in place (``A.data[...]
+        *= allelic_factor``, ``A.data[weak] = 0``, ``setdiag(0)``, :1157-1172), and its resolution auto-search hands the
+        same A to every call (hyperpartition.py:1049-1104): with allelic_factor = -1 the allelic entries change sign on
+        every call (pinned by three consecutive calls of the reference, tests/golden/ref_irmm_rounds.npz ``inplace_*``).
+        ``REFERENCE_INPLACE_A = True`` (or env CPHASING_B200_INPLACE_IRMM=1) reproduces that: the caller's matrix then
+        carries the re-weighted values after the call.  Identical either way at the CLI default ``-af 0``;
       * ``max_round > 1`` (iterative hyperedge re-weighting, :1258-1397; CLI default 1) keeps W, the suppressed
         monomers and A on the device between rounds (csrc/irmm.cu); the matrix arithmetic of rounds >= 2 is fp64, as
         in the reference (its A_new is a float64 product).
@@ -562,6 +621,10 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
         # A = H W D_e^-1 H^T, threshold, normalise, zero diagonal (:1120-1150)
         A = HyperGraph.clique_expansion_init(H, NW=NW, min_weight=float(min_weight) if min_weight > 0 else 0.0)
     raw_A = A
+    inplace = REFERENCE_INPLACE_A or os.environ.get("CPHASING_B200_INPLACE_IRMM", "0") == "1"
+    if inplace and max_round <= 1:
+        raw_A = wrap_adjacency(graphops.clone_adjacency(graphops.upload_adjacency(A)),
+                               dtype=A.dtype if A.dtype in (np.float32, np.float64) else np.float32)     # :1157 raw_A = A.copy()
     a = graphops.clone_adjacency(graphops.upload_adjacency(A))
     if P_allelic_idx or P_weak_idx:
         dev = a.indptr.device
@@ -578,7 +641,26 @@ def IRMM(H, A=None, NW=None, P_allelic_idx=None, P_weak_idx=None, allelic_factor
         return _irmm_rounds(H, raw_A, a, NW, P_allelic_idx, P_weak_idx, allelic_factor, resolution, min_weight, threshold,
                             max_round, use_leiden, cluster_assignments)
     A_out = wrap_adjacency(a, dtype=A.dtype if A.dtype in (np.float32, np.float64) else np.float32)
+    if inplace:
+        _adopt(A, a)
     return raw_A, A_out, cluster_assignments, cluster_results
+
+
+REFERENCE_INPLACE_A = False      # see IRMM: reproduce the reference's in-place re-weighting of the caller's A
+
+
+def _adopt(A, a: D.DeviceCSR):
+    """make the caller's matrix A carry the values of the device matrix `a` (same sparsity pattern): what the reference's
+    in-place edits of algorithms/hypergraph.py:1157-1172 leave behind in the caller's object"""
+    dt = A.dtype if A.dtype in (np.float32, np.float64) else np.float32
+    if isinstance(A, DeviceBackedCSR):
+        fresh = wrap_adjacency(a, dtype=dt)
+        A._loader, A._cph, A._parts = fresh._loader, fresh._cph, [None, None, None]
+    else:
+        if not A.has_sorted_indices:
+            A.sort_indices()          # the device copy was built from the sorted form: same entry order
+        d = a.data32 if (dt == np.float32 and a.data32 is not None) else a.data64
+        A.data[:] = D.to_host(d).astype(dt, copy=False)
 
 
 def _irmm_rounds(H, raw_A, a, NW, P_allelic_idx, P_weak_idx, allelic_factor, resolution, min_weight, threshold, max_round,

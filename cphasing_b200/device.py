@@ -465,6 +465,7 @@ class Accumulator:
 BINNED_MIN_N = 5600          # n (n + 1) / 2 x 8 B beyond ~126 MB: the accumulator no longer stays in L2
 BINNED_MAX_N = 46 * 2508     # 46 block rows of the binned kernels
 BINNED_MAX_RECORD_BYTES = 16 << 30   # scratch of 8 B per pair; beyond this the direct kernel runs instead
+BANDED_MAX_N = 36000         # row bands of <= 4096 rows and <= 100 MB (expand.cu band_geometry)
 BINNED_MIN_NNZ = 1 << 22     # small inputs: the three extra passes cost more than the DRAM read-modify-writes they avoid
 
 
@@ -485,19 +486,28 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     if acc is None:
         acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    if entry_w is None and BINNED_MIN_N <= n <= BINNED_MAX_N and H.nnz >= BINNED_MIN_NNZ:
-        # the packed triangle does not fit in L2: group the pair updates by accumulator block first (expand.cu, "binned")
-        fn = lib().cph_expand_accumulate_binned
-        need = C.c_size_t(0)
-        hp = C.c_uint64(0)
+    form = os.environ.get("CPH_EXPAND_FORM", "")          # "", "banded", "binned", "direct": A/B switch for measurements
+    if entry_w is None and BINNED_MIN_N <= n <= BINNED_MAX_N and H.nnz >= BINNED_MIN_NNZ and form != "direct":
+        # the packed triangle does not fit in L2: group the pair updates by accumulator region first (expand.cu:
+        # "banded" = row bands with staged 256-byte record lines; "binned" = the round-1 2-D blocks, kept for larger n)
         args = (ptr(H.pem_row), ptr(H.pem_pk), H.nnz, n, int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag))
-        check(fn(1, *args, None, C.byref(hp), None, 0, C.byref(need), None))
-        ws = _lib.workspace(need.value, dev)
-        check(fn(1, *args, None, C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
-        if int(hp.value) * 8 <= BINNED_MAX_RECORD_BYTES:
-            rec = torch.empty(max(int(hp.value), 1), dtype=torch.int64, device=dev)
-            check(fn(2, *args, ptr(rec), C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
-            return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
+        fns = [lib().cph_expand_accumulate_banded] if n <= BANDED_MAX_N and form != "binned" else []
+        if form != "banded":
+            fns.append(lib().cph_expand_accumulate_binned)
+        for fn in fns:
+            need = C.c_size_t(0)
+            hp = C.c_uint64(0)
+            rc = fn(1, *args, None, C.byref(hp), None, 0, C.byref(need), None)
+            if rc == _lib.ERR_TOO_LARGE and fn is not fns[-1]:
+                continue
+            check(rc)
+            ws = _lib.workspace(need.value, dev)
+            check(fn(1, *args, None, C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
+            if int(hp.value) * 8 <= BINNED_MAX_RECORD_BYTES:
+                rec = torch.empty(max(int(hp.value), 1), dtype=torch.int64, device=dev)
+                check(fn(2, *args, ptr(rec), C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
+                return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
+            break
         # too many pairs for the record scratch: the direct kernel below redoes the (cheap) zeroing and the diagonal
     check(lib().cph_expand_accumulate_diag(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, max(n, 1),
                                            int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))

@@ -121,8 +121,7 @@ def _self_pairs(a: D.DeviceCSR, allele_pairs, first=None):
             x = int(x); y = int(y)
             if x not in first:
                 first[x] = y
-    cs = np.array([c for c, al in first.items() if al in first and 0 <= c < a.n and 0 <= al < a.n and c != al],
-                  dtype=np.int64)
+    cs = np.array([c for c, al in first.items() if 0 <= c < a.n and 0 <= al < a.n and c != al], dtype=np.int64)
     if cs.size == 0:
         return []
     als = np.array([first[int(c)] for c in cs], dtype=np.int64)

@@ -221,6 +221,14 @@ int cph_expand_accumulate_diag(const uint32_t* pem_row, const uint32_t* pem_pk, 
  * returns the number of records in *h_pairs; the caller allocates pair_records (u64 each) and calls phase 2, which
  * writes and applies them.  n <= 115368 (46 block rows of <= 50 MB blocks).
  * phase 3 / 4 run the two halves of phase 2 apart (record fill only / apply only) for timing. */
+/* Banded form (round 2) for the same regime: the packed triangle is cut into <= 64 row bands of equal area (<= ~44 MB);
+ * pair records (8 B) are staged per warp and band in shared memory and leave as 256-byte lines, then applied band after
+ * band (the band stays in L2).  Same two-phase protocol and bit-identical results; *h_records = u64 records to allocate.
+ * Supported while every band holds <= 4096 rows and <= 100 MB (n <= ~36k); CPH_ERR_TOO_LARGE otherwise. */
+int cph_expand_accumulate_banded(int phase, const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n,
+                                 int use_high_order, int frac_bits, int zero_first, uint64_t* acc, uint64_t* diag_fx,
+                                 uint64_t* pair_records, uint64_t* h_records, void* ws, size_t ws_bytes, size_t* h_ws_need,
+                                 cph_stream_t stream);
 int cph_expand_accumulate_binned(int phase, const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n,
                                  int use_high_order, int frac_bits, int zero_first, uint64_t* acc, uint64_t* diag_fx,
                                  uint64_t* pair_records, uint64_t* h_pairs, void* ws, size_t ws_bytes,

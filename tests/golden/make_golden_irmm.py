@@ -114,6 +114,24 @@ def main():
                 out[f"{tag}_call{i}_w"] = call["w"]
                 out[f"{tag}_call{i}_membership"] = call["membership"].astype(np.int64)
             print(tag, "clustering calls:", len(CALLS), "groups:", len(K), "nnz(A):", csr_matrix(A).nnz)
+    # ---- what repeated calls on the SAME A do (the resolution auto-search, hyperpartition.py:1049-1104, passes one A to
+    # every IRMM call): the reference re-weights the caller's matrix IN PLACE (:1157-1172), so with allelic_factor = -1 the
+    # allelic entries change sign on every call and weak entries stay zero.  Three consecutive calls, one matrix.
+    A_shared = ah.HyperGraph.clique_expansion_init(H.copy(), min_weight=1.0)
+    out.update(mg.csr_parts("inplace_A0", csr_matrix(A_shared).copy()))
+    wk = pa[::7][:40]                                                   # a few weak pairs as well
+    out["inplace_weak_pairs"] = wk
+    P_al = [pd.Series(pa[:, 0]), pd.Series(pa[:, 1])]
+    P_wk = [pd.Series(np.concatenate([wk[:, 0], wk[:, 1]])), pd.Series(np.concatenate([wk[:, 1], wk[:, 0]]))]
+    for i, res in enumerate((1.0, 1.2, 1.4)):
+        CALLS.clear()
+        raw_A, A_ret, ca, K = ah.IRMM(None, A_shared, None, P_al, P_wk, -1, 0.3, res, 1.0, 0.01, 1, method="leiden")
+        assert len(CALLS) == 1
+        out[f"inplace_call{i}_edges"] = CALLS[0]["edges"].astype(np.int32)
+        out[f"inplace_call{i}_w"] = CALLS[0]["w"]
+        out.update(mg.csr_parts(f"inplace_call{i}_rawA", csr_matrix(raw_A)))
+        out.update(mg.csr_parts(f"inplace_call{i}_callerA", csr_matrix(A_shared).copy()))
+        print("inplace call", i, "edges", len(CALLS[0]["w"]), "negative weights", int((CALLS[0]["w"] < 0).sum()))
     out["params"] = np.array([1.6, 1.0, 0.01], dtype=np.float64)      # resolution, min_weight, threshold
     path = os.path.join(HERE, "ref_irmm_rounds.npz")
     np.savez_compressed(path, **out)

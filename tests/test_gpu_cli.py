@@ -82,9 +82,12 @@ def test_cli_files_end_to_end(tmp_path):
     assert got_al == al and got_wk == wk
     # -fc: only contacts inside one first-round group are candidates -> a subset of the pairs above, none across groups
     pt2 = tmp_path / "prune.fc.table"
-    run("kprune", str(at), str(contacts), "-o", str(pt2), "-m", "fast", "-fc", str(out1))
+    chrom = tmp_path / "first.clusters.txt"                 # chromosome-level groups: the 4 haplotypes of a chromosome together
+    run("hyperpartition", str(hgf), str(sizes), str(chrom), "-n", "5", "-ir1", "0.3", "-r1", "0.3")
+    lc = chrom.read_text().strip().split("\n")
+    run("kprune", str(at), str(contacts), "-o", str(pt2), "-m", "fast", "-fc", str(chrom))
     grp_of = {}
-    for gi, l in enumerate(l1):
+    for gi, l in enumerate(lc):
         for m in l.split("\t")[2].split(" "):
             grp_of[m] = gi
     rows2 = [l.split("\t") for l in pt2.read_text().strip().split("\n")]

@@ -455,10 +455,11 @@ def test_extract_rows_with_explicit_zero_counts(api):
         assert np.array_equal(x, y)
 
 
+@pytest.mark.parametrize("form", ["banded", "binned"])
 @pytest.mark.parametrize("use_high_order", [True, False])
-def test_binned_expansion_is_bit_identical(api, use_high_order, monkeypatch):
-    """Accumulators beyond L2 (n > 5.6k) take the binned kernels (pairs grouped by accumulator block, then applied block
-    by block).  Integer fixed-point sums do not depend on the order of addition, so triangle and diagonal must equal the
+def test_binned_expansion_is_bit_identical(api, use_high_order, form, monkeypatch):
+    """Accumulators beyond L2 (n > 5.6k) take the banded kernels (pair records grouped by row band of the triangle, then
+    applied band by band) or, for larger n, the binned ones (2-D blocks).  Integer fixed-point sums do not depend on the order of addition, so triangle and diagonal must equal the
     direct kernel's bit for bit -- including pairs whose count product does not fit the 34-bit record field."""
     _, _, D, synth = api
     import torch
@@ -472,12 +473,15 @@ def test_binned_expansion_is_bit_identical(api, use_high_order, monkeypatch):
     pk[big] = (pk[big] & ~0x00FFFFFF) | 200_000          # products above 2^34 with one another are unlikely; with
     pk[big + 1] = (pk[big + 1] & ~0x00FFFFFF) | 150_000  # the neighbour entry (same hyperedge most of the time) they occur
     H._bound = None
+    monkeypatch.setenv("CPH_EXPAND_FORM", form)
+    if form == "banded":
+        monkeypatch.setenv("CPH_BAND_MB", "3")          # 48 bands at this n: exercises many bands and the padded tails
     l0 = __import__("cphasing_b200")._lib.launches()
     a1 = D.expand_accumulate(H, use_high_order=use_high_order)
     binned_launches = __import__("cphasing_b200")._lib.launches() - l0
     monkeypatch.setattr(D, "BINNED_MIN_N", 1 << 30)
     a2 = D.expand_accumulate(H, use_high_order=use_high_order)
-    assert binned_launches >= 4                          # count, scan.., fill, apply
+    assert binned_launches >= 3                          # count, (scan..,) fill, apply
     assert a1.frac_bits == a2.frac_bits
     assert torch.equal(a1.diag, a2.diag)
     assert torch.equal(a1.acc, a2.acc)

@@ -464,6 +464,42 @@ def test_irmm_against_reference_run(name, max_round):
         assert (~close).sum() <= 40, (~close).sum()          # threshold ties of A_new (0.5 / 0.25 steps after damping)
 
 
+@pytest.mark.parametrize("inplace", [True, False])
+def test_irmm_repeated_calls_on_one_matrix(inplace, monkeypatch):
+    """The resolution search hands ONE matrix to every IRMM call (hyperpartition.py:1049-1104) and the reference re-weights it
+    in place (:1157-1172): at allelic_factor = -1 the allelic entries change sign on every call.  Pinned by three
+    consecutive calls of the reference's IRMM (ref_irmm_rounds.npz `inplace_*`).  REFERENCE_INPLACE_A = True reproduces the
+    graphs of all three calls and what the caller's matrix holds afterwards; the default leaves the caller's matrix alone,
+    so every call sees the graph of the reference's FIRST call (deliberate deviations)."""
+    import cphasing_b200.algorithms.hypergraph as ah
+    from scipy.sparse import triu
+    from helpers import load_golden, csr_from
+    g = load_golden("irmm_rounds")
+    monkeypatch.setattr(ah, "REFERENCE_INPLACE_A", inplace)
+    pa, wk = g["allelic_pairs"], g["inplace_weak_pairs"]
+    P_al = [pa[:, 0], pa[:, 1]]
+    P_wk = [np.concatenate([wk[:, 0], wk[:, 1]]), np.concatenate([wk[:, 1], wk[:, 0]])]
+    for plain in (True, False):                    # a plain scipy matrix and a device-backed one
+        A0 = csr_from(g, "inplace_A0")
+        A = A0.copy() if plain else ah.wrap_adjacency(__import__("cphasing_b200.graphops", fromlist=["x"]).upload_adjacency(A0))
+        for i, res in enumerate((1.0, 1.2, 1.4)):
+            raw_A, A_ret, ca, K = ah.IRMM(None, A, None, P_al, P_wk, -1, 0.3, res, 1.0, 0.01, 1, method="leiden")
+            ref_call = i if inplace else 0
+            n = A0.shape[0]
+            want = csr_matrix((g[f"inplace_call{ref_call}_w"], (g[f"inplace_call{ref_call}_edges"][:, 0],
+                                                                g[f"inplace_call{ref_call}_edges"][:, 1])), shape=(n, n))
+            got = triu(csr_matrix(A_ret), k=1).tocsr()
+            got.eliminate_zeros()
+            d = abs(got - want)
+            assert d.nnz == 0 or d.max() <= 1e-5 * abs(want).max()
+            assert (got.data < 0).sum() == (want.data < 0).sum()
+            caller = csr_matrix(A).toarray()
+            ref_caller = csr_from(g, f"inplace_call{i}_callerA").toarray() if inplace else A0.toarray()
+            assert np.allclose(caller, ref_caller, rtol=1e-5, atol=1e-7)
+            assert np.allclose(csr_matrix(raw_A).toarray(), csr_from(g, f"inplace_call{ref_call}_rawA").toarray() if inplace
+                               else A0.toarray(), rtol=1e-5, atol=1e-7)
+
+
 def test_kprune_against_reference_run():
     """KPruneHyperGraph on the device against the lists of the REFERENCE's own KPruneHyperGraph.run()
     (tests/golden/ref_kprune.npz), identical including the (c, c) entries of the weak list."""
