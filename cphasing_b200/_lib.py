@@ -69,7 +69,8 @@ _SIGS = {
     "cph_diag_terms": (_I, [_P, _P, _P, _U32, _I, _I, _P, _P]),
     "cph_expand_accumulate": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _I, _P, _P]),
     "cph_expand_accumulate_diag": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P]),
-    "cph_expand_accumulate_banded": (_I, [_I, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P, C.POINTER(_U64)] + _WS),
+    "cph_expand_sweep_prep": (_I, [_P, _P, _U64, _U32, _I, _P, _P, _P]),
+    "cph_expand_sweep_band": (_I, [_P, _U64, _U32, _U32, _U32, _I, _I, _P, _P, _P]),
     "cph_expand_accumulate_binned": (_I, [_I, _P, _P, _U64, _U32, _I, _I, _I, _P, _P, _P, C.POINTER(_U64)] + _WS),
     "cph_expand_count": (_I, [_P, _P, _U32, _I, _F, C.POINTER(_U64)] + _WS),
     "cph_expand_emit": (_I, [_P, _P, _U32, _I, _F, _P, _P, _P, _P, _P, _P, _P]),

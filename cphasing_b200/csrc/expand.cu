@@ -296,201 +296,190 @@ __global__ void __launch_bounds__(XB_T) bin_apply_kernel(const u64* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------------
-// Banded expansion (round 2) for accumulators beyond L2: the row-band form of the binned idea, built from what the first
-// one measured (profiles/red_ceiling.txt, scripts/diag_binned.py):
-//   * scattered 64-bit REDs run at ~190 G/s into an L2-resident region and at ~21 G/s into HBM -> apply per region;
-//   * the 2-D block bins (1 081 of them) forced one 8-byte scattered store per pair (a 32-byte sector each in DRAM) and a
-//     per-CTA count matrix; the apply pass spent its time in two 64-bit divisions per record, not in the REDs.
-// Here the packed triangle is cut into <= 64 ROW BANDS of equal area (<= ~44 MB each, rows [r0[b], r0[b+1])).  A pair
-// (lo, hi) belongs to the band of its smaller row.  Records are 8 bytes:  lrow(12) | col(17) | D(7) | c_a*c_b(28).
-//   band_count_kernel : pairs per band (per-warp shared-memory counters) + the diagonal terms
-//   band_fill_kernel  : every WARP keeps a 32-record staging line per band in shared memory; lanes that produce a pair
-//                       for the same band find each other with MATCH.ANY, a full line leaves as ONE 256-byte store at a
-//                       cursor taken by one global atomic -> coalesced record stream, no count matrix
-//   band_apply_kernel : band after band, field extraction by shifts, one RED per record into the L2-resident band
-// Pairs whose count product needs more than 28 bits, and records that overflow a band's region, are added directly.
-// Integer sums are order-free: acc / diag come out bit-identical to the direct kernel.
+// Swept expansion (round 2) for accumulators beyond L2.  What the measurements said (profiles/red_ceiling.txt,
+// profiles/r2a_bench_C.json): scattered 64-bit REDs run at ~190 G/s into an L2-resident region and at ~21 G/s into HBM;
+// every form that MATERIALISES the pairs (binned: 13.5 ms, banded pair records: 23 ms on the workload-D shard) pays 16 B of
+// scattered traffic per pair.  This form materialises nothing:
+//   sw_prep_kernel : ONE pass that sorts every hyperedge run by contig (stable rank inside the run, runs <= 64 entries)
+//                    and packs the entry to 4 bytes:  head(1) | D_e(7) | count(24 - rb) | row(rb),  rb = bits(n - 1).
+//                    With sorted runs the pairs (a, b > a) owned by entry a all lie in row(a) of the upper triangle.
+//   sw_band_kernel : the packed triangle is cut into row bands of <= ~64 MB; for one band [r0, r1) the kernel streams the
+//                    4-byte entries (coalesced, evict-first), keeps the entries whose row is in the band in a shared-memory
+//                    queue, and walks their run suffix out of the shared-memory tile -- one RED per pair into a band that
+//                    was zeroed just before and stays L2 resident.  The diagonal terms of the band's rows go to
+//                    shared-memory bins (two 32-bit atomics with carry) and are flushed once per CTA.
+// DRAM traffic: 12 B per entry for the preparation + 4 B per entry and band.  Integer sums are order-free: acc / diag come
+// out bit-identical to the direct kernel.  Entries whose count does not fit the field, or runs longer than 64, raise a
+// device flag and the caller falls back to the direct kernel.
 // ------------------------------------------------------------------------------------------------
-constexpr int BD_T = 128;                 // 4 warps per CTA
-constexpr int BD_WARPS = BD_T / 32;
-constexpr u32 BD_MAXB = 64;
-constexpr u32 BD_CAP = 32;                // records per staging line = one 256-byte store
-constexpr u64 BD_PROD_MAX = (1ull << 28) - 1;
-constexpr u32 BD_MAX_ROWS = 4096;         // lrow field
-constexpr u32 BD_MAX_N = 1u << 17;        // col field
+constexpr int SW_T = 256;
+constexpr int SW_PER = 8;
+constexpr u32 SW_TILE = SW_T * SW_PER;        // 2048 entries per tile
+constexpr u32 SW_HALO = 64;                   // longest run
+constexpr u32 SW_BINS_MAX = 7168;             // band rows whose diagonal lives in shared-memory bins (56 KB)
 
-struct BandGeom {
-    u32 n, nb;
-    const u32* r0;          // [nb + 1] first row of each band
-    const u8* band_of;      // [n]
-};
-
-__device__ __forceinline__ u64 bd_pack(u32 lrow, u32 col, u32 D, u64 prod) {
-    return ((u64)lrow << 52) | ((u64)col << 35) | ((u64)D << 28) | prod;
-}
-
-// entries [lo, hi) of a CTA: f(i, j, ca, cb, D) for every pair owned by an entry (the entry and a later one of its run)
-template <class F>
-__device__ __forceinline__ void bd_for_pairs(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz, size_t a,
-                                             F f) {
-    size_t b = a + 1;
-    if (b >= nnz) return;
-    u32 rb = pem_row[b];
-    if (rb & CPH_HEAD) return;
-    const u32 pa = pem_pk[a];
-    const u32 i = pem_row[a] & CPH_ROWM;
-    for (;;) {
-        f(i, rb & CPH_ROWM, (u64)(pa & CPH_CNTM), (u64)(pem_pk[b] & CPH_CNTM), pa >> 24);
-        if (++b >= nnz) break;
-        rb = pem_row[b];
-        if (rb & CPH_HEAD) break;
-    }
-}
-
-__global__ void __launch_bounds__(BD_T) band_count_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
-                                                          BandGeom g, int use_high_order, int frac_bits,
-                                                          unsigned long long* __restrict__ cnt,
-                                                          unsigned long long* __restrict__ diag) {
-    __shared__ u32 c[BD_WARPS][BD_MAXB];
-    __shared__ double scale[128];
-    fill_scale(scale, frac_bits);
-    for (int k = threadIdx.x; k < BD_WARPS * (int)BD_MAXB; k += BD_T) (&c[0][0])[k] = 0;
-    __syncthreads();
-    const int w = threadIdx.x >> 5;
-    const size_t stride = (size_t)gridDim.x * BD_T;
-    for (size_t a = gtid(); a < nnz; a += stride) {
-        const u32 pa = pem_pk[a];
-        const u64 ca = pa & CPH_CNTM;
-        atomicAdd(&diag[pem_row[a] & CPH_ROWM], __double2ull_rn((double)(ca * ca) * scale[use_high_order ? (pa >> 24) : 1u]));
-        bd_for_pairs(pem_row, pem_pk, nnz, a, [&](u32 i, u32 j, u64 x, u64 y, u32) {
-            if (x * y > BD_PROD_MAX) return;
-            atomicAdd(&c[w][g.band_of[i < j ? i : j]], 1u);
-        });
-    }
-    __syncthreads();
-    for (u32 k = threadIdx.x; k < g.nb; k += BD_T) {
-        u32 t = 0;
+// A tile owns the runs that START in it (a run crossing the end of the tile is finished out of the halo, a run that started
+// in the previous tile is left to that tile), so its output range [first head in the tile, first head at or after the end
+// of the tile) is contiguous: the sorted entries are staged in shared memory and leave with coalesced stores.
+__global__ void __launch_bounds__(SW_T) sw_prep_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
+                                                       u32 rb, int use_high_order, u32* __restrict__ pe4, u32* __restrict__ flag) {
+    constexpr u32 L = SW_TILE + SW_HALO;
+    constexpr int NQ = (L + SW_T - 1) / SW_T;
+    __shared__ u32 rows[L];
+    __shared__ u32 outs[L];
+    __shared__ u32 lohi[2];
+    const u64 t0 = (u64)blockIdx.x * SW_TILE;
+    u32 pkr[NQ];
 #pragma unroll
-        for (int q = 0; q < BD_WARPS; ++q) t += c[q][k];
-        if (t) atomicAdd(&cnt[k], (unsigned long long)t);
+    for (int q = 0; q < NQ; ++q) {           // all global loads of the tile are in flight together
+        const u32 x = q * SW_T + threadIdx.x;
+        const bool ok = x < L && t0 + x < nnz;
+        if (x < L) rows[x] = ok ? pem_row[t0 + x] : CPH_HEAD;
+        pkr[q] = ok ? pem_pk[t0 + x] : 0u;
     }
+    if (threadIdx.x == 0) {
+        lohi[0] = L;
+        lohi[1] = L;
+    }
+    __syncthreads();
+    const u32 cmax = 1u << (24 - rb);
+    bool bad = false;
+#pragma unroll
+    for (int q = 0; q < NQ; ++q) {
+        const u32 x = q * SW_T + threadIdx.x;
+        if (x >= L) break;
+        const u32 rx = rows[x];
+        // the first head of the tile is within its first 64 entries, the first head at or after its end within the halo
+        if ((rx & CPH_HEAD) && (x < SW_HALO || x >= SW_TILE)) atomicMin(&lohi[x < SW_TILE ? 0 : 1], x);
+        if (t0 + x >= nnz) continue;
+        u32 s = x;
+        while (!(rows[s] & CPH_HEAD) && s > 0 && x - s < SW_HALO) --s;
+        if (!(rows[s] & CPH_HEAD)) {
+            if (s != 0) bad = true;          // run longer than the halo
+            continue;                        // (s == 0: the run started in the previous tile, which sorts it)
+        }
+        if (s >= SW_TILE) continue;          // starts in the next tile
+        const u32 ra = rx & CPH_ROWM;
+        u32 rank = 0, b = s;
+        do {
+            const u32 r = rows[b] & CPH_ROWM;
+            rank += (r < ra || (r == ra && b < x)) ? 1u : 0u;
+            ++b;
+        } while (b < L && !(rows[b] & CPH_HEAD) && b - s < SW_HALO);
+        if (b < L && !(rows[b] & CPH_HEAD)) bad = true;
+        const u32 pk = pkr[q];
+        const u32 c = pk & CPH_CNTM;
+        if (c >= cmax) bad = true;
+        const u32 D = use_high_order ? (pk >> 24) & 127u : 1u;
+        outs[s + rank] = (rank == 0 ? CPH_HEAD : 0u) | (D << 24) | (c << rb) | ra;
+    }
+    if (bad) atomicOr(flag, 1u);
+    __syncthreads();
+    const u32 lo = lohi[0], hi = lohi[1];
+    if (lo >= SW_TILE) return;               // no run starts here (only when a run is too long: flagged)
+    for (u32 x = lo + threadIdx.x; x < hi && t0 + x < nnz; x += SW_T) pe4[t0 + x] = outs[x];
 }
 
-__global__ void __launch_bounds__(BD_T) band_fill_kernel(const u32* __restrict__ pem_row, const u32* __restrict__ pem_pk, u64 nnz,
-                                                         BandGeom g, int use_high_order, int frac_bits,
-                                                         const u64* __restrict__ base, const u64* __restrict__ cap,
-                                                         unsigned long long* __restrict__ cursor, u64* __restrict__ rec,
-                                                         unsigned long long* __restrict__ acc) {
-    extern __shared__ __align__(16) unsigned char bd_raw[];
-    u64* line = reinterpret_cast<u64*>(bd_raw);                       // [warp][band][BD_CAP]
-    u32* fill = reinterpret_cast<u32*>(line + (size_t)BD_WARPS * g.nb * BD_CAP);   // [warp][band]
-    __shared__ double scale[128];
-    fill_scale(scale, frac_bits);
-    for (u32 k = threadIdx.x; k < BD_WARPS * g.nb; k += BD_T) fill[k] = 0;
-    __syncthreads();
-    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const u32 lt = lanemask_lt();
-    u64* my_line = line + (size_t)w * g.nb * BD_CAP;
-    u32* my_fill = fill + (size_t)w * g.nb;
-    // one full staging line of band k leaves as a 256-byte store (or, past the band's region, as direct REDs)
-    auto flush = [&](u32 k, u32 count) {
-        u64 at = 0;
-        if (lane == 0) at = atomicAdd(&cursor[k], (unsigned long long)BD_CAP);
-        at = __shfl_sync(0xffffffffu, at, 0);
-        const u64 r = (u32)lane < count ? my_line[(size_t)k * BD_CAP + lane] : 0ull;
-        if (at + BD_CAP <= cap[k]) {
-            rec[base[k] + at + lane] = r;
-        } else if (r & BD_PROD_MAX) {
-            const u64 i = (u64)g.r0[k] + (r >> 52), j = (r >> 35) & (BD_MAX_N - 1);
-            unsigned long long v = __double2ull_rn((double)(r & BD_PROD_MAX) * scale[(r >> 28) & 127u]);
-            if (i == j) v += v;
-            atomicAdd(&acc[tri_index(i, j, g.n)], v);
-        }
-    };
-    const size_t stride = (size_t)gridDim.x * BD_T;
-    const size_t rounds = (nnz + stride - 1) / stride;
-    for (size_t it = 0; it < rounds; ++it) {
-        const size_t a = it * stride + gtid();
-        size_t b = a + 1;
-        u32 rb = CPH_HEAD, pa = 0, i = 0;
-        if (a < nnz && b < nnz) {
-            rb = pem_row[b];
-            pa = pem_pk[a];
-            i = pem_row[a] & CPH_ROWM;
-        }
-        bool has = !(rb & CPH_HEAD);
-        const u64 ca = pa & CPH_CNTM;
-        const u32 D = use_high_order ? (pa >> 24) : 1u;
-        while (__any_sync(0xffffffffu, has)) {
-            u32 band = 0xffff0000u | (u32)lane;           // lanes without a pair: unique keys
-            u64 r = 0;
-            bool stage = false;
-            if (has) {
-                const u32 j = rb & CPH_ROWM;
-                const u64 prod = ca * (u64)(pem_pk[b] & CPH_CNTM);
-                const u32 l = i < j ? i : j, h = i < j ? j : i;
-                if (prod > BD_PROD_MAX) {                   // does not fit the record: straight to the accumulator
-                    unsigned long long v = __double2ull_rn((double)prod * scale[D]);
-                    if (i == j) v += v;
-                    atomicAdd(&acc[tri_index(l, h, g.n)], v);
-                } else {
-                    band = g.band_of[l];
-                    r = bd_pack(l - g.r0[band], h, D, prod);
-                    stage = true;
-                }
-                ++b;
-                rb = b < nnz ? pem_row[b] : CPH_HEAD;
-                has = !(rb & CPH_HEAD);
-            }
-            const u32 peers = __match_any_sync(0xffffffffu, band);
-            u32 c0 = 0, tot = 0, pos = 0;
-            if (stage) {
-                c0 = my_fill[band];
-                tot = (u32)__popc(peers);
-                pos = c0 + (u32)__popc(peers & lt);
-                if (pos < BD_CAP) my_line[(size_t)band * BD_CAP + pos] = r;
-            }
-            __syncwarp();
-            const bool lead = stage && (peers & lt) == 0u;
-            u32 fm = __ballot_sync(0xffffffffu, lead && c0 + tot >= BD_CAP);      // leaders whose line is full now
-            while (fm) {
-                const int src = __ffs(fm) - 1;
-                fm &= fm - 1u;
-                const u32 k = __shfl_sync(0xffffffffu, band, src);
-                flush(k, BD_CAP);
-            }
-            __syncwarp();
-            if (stage) {
-                if (pos >= BD_CAP) my_line[(size_t)band * BD_CAP + (pos - BD_CAP)] = r;
-                if (lead) my_fill[band] = c0 + tot >= BD_CAP ? c0 + tot - BD_CAP : c0 + tot;
-            }
-            __syncwarp();
-        }
+// Band pass, warp-autonomous: every warp streams its own 512-entry tiles (4 x uint4 per lane + a 64-entry halo), keeps the
+// NEXT tile's loads in flight in registers while it works, and only needs __syncwarp; the CTA meets twice (bins).
+constexpr int SWB_T = 512;
+constexpr int SWB_WARPS = SWB_T / 32;
+constexpr u32 SWB_WT = 512;                   // entries per warp tile
+constexpr u32 SWB_EMPTY = 0xffffffffu;        // never a real entry (D_e <= 126)
+
+__device__ __forceinline__ uint4 sw_load4(const u32* __restrict__ pe4, u64 g, u64 nnz) {
+    uint4 x;
+    if (g + 3 < nnz) {
+        x = __ldcs(reinterpret_cast<const uint4*>(pe4 + g));       // evict-first: the band must stay in L2
+    } else {
+        x.x = g < nnz ? pe4[g] : SWB_EMPTY;
+        x.y = g + 1 < nnz ? pe4[g + 1] : SWB_EMPTY;
+        x.z = g + 2 < nnz ? pe4[g + 2] : SWB_EMPTY;
+        x.w = SWB_EMPTY;
     }
-    for (u32 k = 0; k < g.nb; ++k) {          // what is left in the lines, padded with empty records
-        const u32 c = my_fill[k];
-        if (c) flush(k, c);
-    }
+    return x;
 }
 
-__global__ void __launch_bounds__(256) band_apply_kernel(const u64* __restrict__ rec, const u64* __restrict__ base,
-                                                         const u64* __restrict__ cap, const unsigned long long* __restrict__ cursor,
-                                                         BandGeom g, int frac_bits, unsigned long long* __restrict__ acc) {
+template <bool IDX32>
+__global__ void __launch_bounds__(SWB_T, 2) sw_band_kernel(const u32* __restrict__ pe4, u64 nnz, u32 n, u32 rb, u32 r0, u32 r1,
+                                                           int frac_bits, int smem_bins, unsigned long long* __restrict__ acc,
+                                                           unsigned long long* __restrict__ diag) {
+    extern __shared__ __align__(16) u32 sw_bins[];            // [2 * (r1 - r0)] lo / hi words of the diagonal terms
+    __shared__ __align__(16) u32 wtiles[SWB_WARPS][SWB_WT + SW_HALO];
     __shared__ double scale[128];
     fill_scale(scale, frac_bits);
+    const u32 nrows = r1 - r0;
+    if (smem_bins)
+        for (u32 x = threadIdx.x; x < 2 * nrows; x += SWB_T) sw_bins[x] = 0u;
     __syncthreads();
-    const size_t stride = (size_t)gridDim.x * 256;
-    for (u32 k = 0; k < g.nb; ++k) {
-        const u64 end = min((u64)cursor[k], cap[k]);
-        const u64* __restrict__ rk = rec + base[k];
-        const u64 row0 = g.r0[k];
-        for (u64 p = gtid(); p < end; p += stride) {
-            const u64 r = __ldcs(&rk[p]);               // evict-first: the band being updated must stay in L2
-            if (!(r & BD_PROD_MAX)) continue;           // padding
-            const u64 i = row0 + (r >> 52), j = (r >> 35) & (BD_MAX_N - 1);
-            unsigned long long v = __double2ull_rn((double)(r & BD_PROD_MAX) * scale[(r >> 28) & 127u]);
-            if (i == j) v += v;
-            atomicAdd(&acc[tri_index(i, j, g.n)], v);
+    const u32 rmask = (1u << rb) - 1u, cmask = (1u << (24 - rb)) - 1u;
+    const u32 lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    u32* __restrict__ wt = wtiles[w];
+    const u64 ntiles = (nnz + SWB_WT - 1) / SWB_WT;
+    const u64 nwarps = (u64)gridDim.x * SWB_WARPS;
+    u64 t = (u64)blockIdx.x * SWB_WARPS + w;
+    uint4 r[4], h = make_uint4(SWB_EMPTY, SWB_EMPTY, SWB_EMPTY, SWB_EMPTY);
+    if (t < ntiles) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) r[k] = sw_load4(pe4, t * SWB_WT + 4ull * (k * 32 + lane), nnz);
+        if (lane < SW_HALO / 4) h = sw_load4(pe4, t * SWB_WT + SWB_WT + 4ull * lane, nnz);
+    }
+    for (; t < ntiles; t += nwarps) {
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 4; ++k) reinterpret_cast<uint4*>(wt)[k * 32 + lane] = r[k];
+        if (lane < SW_HALO / 4) reinterpret_cast<uint4*>(wt)[128 + lane] = h;
+        __syncwarp();
+        // which of my 16 entries lie in the band
+        u32 m = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const u32 ee[4] = {r[k].x, r[k].y, r[k].z, r[k].w};
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+                if ((u32)((ee[c] & rmask) - r0) < nrows && ee[c] != SWB_EMPTY) m |= 1u << (k * 4 + c);
+        }
+        const u64 tn = t + nwarps;
+        if (tn < ntiles) {                    // next tile in flight while this one is worked on
+#pragma unroll
+            for (int k = 0; k < 4; ++k) r[k] = sw_load4(pe4, tn * SWB_WT + 4ull * (k * 32 + lane), nnz);
+            if (lane < SW_HALO / 4) h = sw_load4(pe4, tn * SWB_WT + SWB_WT + 4ull * lane, nnz);
+        }
+        while (m) {
+            const u32 bit = (u32)__ffs(m) - 1u;
+            m &= m - 1u;
+            u32 x = ((bit >> 2) * 32u + lane) * 4u + (bit & 3u);
+            const u32 e = wt[x];
+            const u32 i = e & rmask;
+            const u64 ca = (e >> rb) & cmask;
+            const double sc = scale[(e >> 24) & 127u];
+            const unsigned long long dv = __double2ull_rn((double)(ca * ca) * sc);
+            if (smem_bins) {
+                const u32 lo = (u32)dv, hi = (u32)(dv >> 32);
+                const u32 old = atomicAdd(&sw_bins[2 * (i - r0)], lo);
+                const u32 carry = (old + lo < old) ? 1u : 0u;
+                if (hi + carry) atomicAdd(&sw_bins[2 * (i - r0) + 1], hi + carry);
+            } else {
+                atomicAdd(&diag[i], dv);
+            }
+            unsigned long long* __restrict__ arow;
+            if (IDX32) arow = acc + ((i * (2u * n + 1u - i)) / 2u - i);
+            else arow = acc + (((u64)i * (2ull * n + 1ull - i)) / 2ull - i);
+            u32 eb = wt[++x];
+            while (!(eb & CPH_HEAD)) {
+                const u32 j = eb & rmask;
+                unsigned long long v = __double2ull_rn((double)(ca * (u64)((eb >> rb) & cmask)) * sc);
+                if (j == i) v += v;     // duplicated (row, col): both orders land on the diagonal cell
+                atomicAdd(arow + j, v);
+                eb = wt[++x];
+            }
+        }
+    }
+    if (smem_bins) {
+        __syncthreads();
+        for (u32 x = threadIdx.x; x < nrows; x += SWB_T) {
+            const unsigned long long v = (unsigned long long)sw_bins[2 * x] | ((unsigned long long)sw_bins[2 * x + 1] << 32);
+            if (v) atomicAdd(&diag[r0 + x], v);
         }
     }
 }
@@ -716,112 +705,64 @@ extern "C" int cph_expand_accumulate_binned(int phase, const u32* pem_row, const
     return CPH_OK;
 }
 
-// bands of equal triangle area; returns the number of bands (0: the geometry does not fit the record format)
-static u32 band_geometry(u32 n, std::vector<u32>& r0, std::vector<u8>& band_of) {
-    const double tri_bytes = (double)n * ((double)n + 1.0) * 4.0;
-    double band_bytes = 44.0 * 1024 * 1024;
-    if (const char* e = getenv("CPH_BAND_MB")) {
-        const double v = atof(e);
-        if (v >= 1.0 && v <= 4096.0) band_bytes = v * 1024 * 1024;
-    }
-    u32 nb = (u32)ceil(tri_bytes / band_bytes);
-    if (nb < 1) nb = 1;
-    if (nb > BD_MAXB) nb = BD_MAXB;
-    if (tri_bytes / nb > 100.0 * 1024 * 1024 || n >= BD_MAX_N) return 0;       // bands would not stay in L2 / col field
-    r0.assign(nb + 1, 0);
-    band_of.assign(n, 0);
-    const double per = tri_bytes / 8.0 / nb;
-    double area = 0;
-    u32 k = 0;
-    for (u32 i = 0; i < n; ++i) {
-        if (k + 1 < nb && area >= per * (k + 1)) r0[++k] = i;
-        band_of[i] = (u8)k;
-        area += (double)(n - i);
-    }
-    nb = k + 1;
-    r0.resize(nb + 1);
-    r0[nb] = n;
-    for (u32 q = 0; q < nb; ++q)
-        if (r0[q + 1] - r0[q] > BD_MAX_ROWS) return 0;
-    return nb;
-}
-
-extern "C" int cph_expand_accumulate_banded(int phase, const u32* pem_row, const u32* pem_pk, u64 nnz, u32 n, int use_high_order,
-                                            int frac_bits, int zero_first, u64* acc, u64* diag_fx, u64* pair_records,
-                                            u64* h_records, void* ws, size_t ws_bytes, size_t* h_ws_need, void* stream) {
+// Swept form, step 1: sorted + packed entries (4 B each) for cph_expand_sweep_band.  *flag (device u32, zeroed here) becomes
+// non-zero when an entry does not fit the packed form (count >= 2^(24 - bits(n-1)) or a run longer than 64).
+extern "C" int cph_expand_sweep_prep(const u32* pem_row, const u32* pem_pk, u64 nnz, u32 n, int use_high_order, u32* pe4, u32* flag,
+                                     void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
-    ARG_CHECK(n > 0);
-    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
-    std::vector<u32> r0;
-    std::vector<u8> band_of;
-    const u32 nb = band_geometry(n, r0, band_of);
-    if (nb == 0) {
-        cph_set_error(__FILE__, __LINE__, "banded expansion: n outside the supported range (use the binned or the direct form)");
+    ARG_CHECK(n > 0 && flag && (nnz == 0 || (pem_row && pem_pk && pe4)));
+    const u32 rb = (u32)bits_for(n > 1 ? n - 1 : 1);
+    if (rb > 20) {
+        cph_set_error(__FILE__, __LINE__, "swept expansion: more than 2^20 contigs (use the binned or the direct form)");
         return CPH_ERR_TOO_LARGE;
     }
+    CUDA_TRY(cudaMemsetAsync(flag, 0, sizeof(u32), st));
+    if (nnz == 0) return CPH_OK;
+    sw_prep_kernel<<<grid_for(nnz, SW_TILE), SW_T, 0, st>>>(pem_row, pem_pk, nnz, rb, use_high_order, pe4, flag);
+    KERNEL_CHECK();
+    return CPH_OK;
+}
+
+// Swept form, step 2: one row band [row_lo, row_hi) of the packed triangle.  Zeroes the band's cells and diag_fx[row_lo:row_hi)
+// first when zero_first != 0, then adds every pair whose smaller contig lies in the band and the diagonal terms of its rows.
+extern "C" int cph_expand_sweep_band(const u32* pe4, u64 nnz, u32 n, u32 row_lo, u32 row_hi, int frac_bits, int zero_first, u64* acc,
+                                     u64* diag_fx, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    ARG_CHECK(acc && diag_fx && n > 0 && row_lo < row_hi && row_hi <= n);
+    ARG_CHECK(frac_bits >= 0 && frac_bits <= 52);
+    const u32 rb = (u32)bits_for(n > 1 ? n - 1 : 1);
+    ARG_CHECK(rb <= 20);
+    auto tri0 = [&](u64 i) { return (i * (2ull * n - i + 1ull)) / 2ull; };
+    if (zero_first) {
+        CUDA_TRY(cudaMemsetAsync(acc + tri0(row_lo), 0, (tri0(row_hi) - tri0(row_lo)) * sizeof(u64), st));
+        CUDA_TRY(cudaMemsetAsync(diag_fx + row_lo, 0, (size_t)(row_hi - row_lo) * sizeof(u64), st));
+    }
+    if (nnz == 0) return CPH_OK;
+    ARG_CHECK(pe4);
     static int sms = 0;
     if (!sms) {
         int dev = 0;
         CUDA_TRY(cudaGetDevice(&dev));
         CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     }
-    const size_t smem = (size_t)BD_WARPS * nb * (BD_CAP * sizeof(u64) + sizeof(u32));
-    int per_sm = (int)((200u * 1024u) / (smem + 2048));
-    per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
-    const unsigned grid_fill = (unsigned)(sms * per_sm);
-    const u64 pad = (u64)grid_fill * BD_WARPS * BD_CAP;         // every warp may leave one partly filled line per band
-    WS_BEGIN(ar);
-    u32* d_r0 = ar.take<u32>(BD_MAXB + 1);
-    u8* d_band_of = ar.take<u8>(n);
-    u64* d_cnt = ar.take<u64>(BD_MAXB);
-    u64* d_base = ar.take<u64>(BD_MAXB);
-    u64* d_cap = ar.take<u64>(BD_MAXB);
-    u64* d_cursor = ar.take<u64>(BD_MAXB);
-    WS_QUERY_RETURN(ar);
-    BandGeom g{n, nb, d_r0, d_band_of};
-    if (phase == 1) {
-        ARG_CHECK(acc && diag_fx && h_records && (nnz == 0 || (pem_row && pem_pk)));
-        const size_t tri = (size_t)n * ((size_t)n + 1) / 2;
-        if (zero_first) CUDA_TRY(cudaMemsetAsync(acc, 0, tri * sizeof(u64), st));
-        CUDA_TRY(cudaMemsetAsync(diag_fx, 0, (size_t)n * sizeof(u64), st));
-        CUDA_TRY(cudaMemsetAsync(d_cnt, 0, BD_MAXB * sizeof(u64), st));
-        CUDA_TRY(cudaMemsetAsync(d_cursor, 0, BD_MAXB * sizeof(u64), st));
-        CUDA_TRY(cudaMemcpyAsync(d_r0, r0.data(), (nb + 1) * sizeof(u32), cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(d_band_of, band_of.data(), n, cudaMemcpyHostToDevice, st));
-        u64 h_cnt[BD_MAXB] = {0};
-        if (nnz > 0) {
-            band_count_kernel<<<sms * 8, BD_T, 0, st>>>(pem_row, pem_pk, nnz, g, use_high_order, frac_bits,
-                                                        (unsigned long long*)d_cnt, (unsigned long long*)diag_fx);
-            KERNEL_CHECK();
-            CUDA_TRY(cudaMemcpyAsync(h_cnt, d_cnt, nb * sizeof(u64), cudaMemcpyDeviceToHost, st));
-        }
-        CUDA_TRY(cudaStreamSynchronize(st));          // (also keeps r0 / band_of alive until the copies are done)
-        u64 h_base[BD_MAXB], h_cap[BD_MAXB], total = 0;
-        for (u32 k = 0; k < nb; ++k) {
-            h_base[k] = total;
-            h_cap[k] = (h_cnt[k] + pad + BD_CAP - 1) / BD_CAP * BD_CAP;
-            total += h_cap[k];
-        }
-        CUDA_TRY(cudaMemcpyAsync(d_base, h_base, nb * sizeof(u64), cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaMemcpyAsync(d_cap, h_cap, nb * sizeof(u64), cudaMemcpyHostToDevice, st));
-        CUDA_TRY(cudaStreamSynchronize(st));
-        *h_records = total;
-        return CPH_OK;
+    const u32 nrows = row_hi - row_lo;
+    const int smem_bins = nrows <= SW_BINS_MAX;
+    const size_t smem = smem_bins ? (size_t)nrows * 8 : 0;
+    const int per_sm = smem + 39 * 1024 <= 100 * 1024 ? 2 : 1;
+    const u64 nwt = ceil_div(nnz, (size_t)SWB_WT * SWB_WARPS);
+    const unsigned grid = (unsigned)(nwt < (u64)sms * per_sm ? nwt : (u64)sms * per_sm);
+    unsigned long long* A = (unsigned long long*)acc;
+    unsigned long long* Dg = (unsigned long long*)diag_fx;
+    if (n <= 65535) {
+        if (smem > 8 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(sw_band_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sw_band_kernel<true><<<grid, SWB_T, smem, st>>>(pe4, nnz, n, rb, row_lo, row_hi, frac_bits, smem_bins, A, Dg);
+    } else {
+        if (smem > 8 * 1024)
+            CUDA_TRY(cudaFuncSetAttribute(sw_band_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sw_band_kernel<false><<<grid, SWB_T, smem, st>>>(pe4, nnz, n, rb, row_lo, row_hi, frac_bits, smem_bins, A, Dg);
     }
-    ARG_CHECK(phase >= 2 && phase <= 4 && acc);          // 3 / 4: fill only / apply only (timing the two halves apart)
-    if (nnz == 0) return CPH_OK;
-    ARG_CHECK(pem_row && pem_pk && pair_records);
-    if (phase != 4) {
-        CUDA_TRY(cudaFuncSetAttribute(band_fill_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        band_fill_kernel<<<grid_fill, BD_T, smem, st>>>(pem_row, pem_pk, nnz, g, use_high_order, frac_bits, d_base, d_cap,
-                                                        (unsigned long long*)d_cursor, pair_records, (unsigned long long*)acc);
-        KERNEL_CHECK();
-    }
-    if (phase != 3) {
-        band_apply_kernel<<<sms * 8, 256, 0, st>>>(pair_records, d_base, d_cap, (unsigned long long*)d_cursor, g, frac_bits,
-                                                   (unsigned long long*)acc);
-        KERNEL_CHECK();
-    }
+    KERNEL_CHECK();
     return CPH_OK;
 }
 

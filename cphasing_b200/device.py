@@ -465,12 +465,48 @@ class Accumulator:
 BINNED_MIN_N = 5600          # n (n + 1) / 2 x 8 B beyond ~126 MB: the accumulator no longer stays in L2
 BINNED_MAX_N = 46 * 2508     # 46 block rows of the binned kernels
 BINNED_MAX_RECORD_BYTES = 16 << 30   # scratch of 8 B per pair; beyond this the direct kernel runs instead
-BANDED_MAX_N = 36000         # row bands of <= 4096 rows and <= 100 MB (expand.cu band_geometry)
-BINNED_MIN_NNZ = 1 << 22     # small inputs: the three extra passes cost more than the DRAM read-modify-writes they avoid
+SWEEP_MAX_N = 1 << 20        # row field of the 4-byte packed entry (expand.cu sw_prep_kernel)
+BINNED_MIN_NNZ = 1 << 22     # small inputs: the extra passes cost more than the DRAM read-modify-writes they avoid
+
+
+def sweep_bands(n, band_bytes=None):
+    """row bands [r0[k], r0[k+1]) of the packed upper triangle with at most ~band_bytes of u64 cells each."""
+    if band_bytes is None:
+        band_bytes = int(float(os.environ.get("CPH_BAND_MB", "96")) * (1 << 20))
+    cells = max(band_bytes // 8, n)          # at least one row
+    # cells before row i: i (2n - i + 1) / 2; walk the rows with numpy (n <= 2^20)
+    i = np.arange(n + 1, dtype=np.int64)
+    before = i * (2 * n - i + 1) // 2
+    r0 = [0]
+    while r0[-1] < n:
+        nxt = int(np.searchsorted(before, before[r0[-1]] + cells, side="right")) - 1
+        r0.append(min(n, max(nxt, r0[-1] + 1)))
+    return r0
+
+
+def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, zero, band_hook=None):
+    """sorted 4-byte entries + one pass per L2-sized row band (expand.cu, swept form).  `band_hook(k, lo, hi, cell_lo,
+    cell_hi)` runs after band k was launched (multi-GPU: start that band's exchange).  -> False when the packed form
+    does not fit (the caller falls back)."""
+    dev = H.device
+    n = H.n_rows
+    pe4 = torch.empty(max(H.nnz, 1), dtype=torch.int32, device=dev)
+    flag = torch.empty(1, dtype=torch.int32, device=dev)
+    rc = lib().cph_expand_sweep_prep(ptr(H.pem_row), ptr(H.pem_pk), H.nnz, n, int(use_high_order), ptr(pe4), ptr(flag), stream())
+    if rc == _lib.ERR_TOO_LARGE:
+        return False
+    check(rc)
+    r0 = sweep_bands(n)
+    for k in range(len(r0) - 1):
+        lo, hi = r0[k], r0[k + 1]
+        check(lib().cph_expand_sweep_band(ptr(pe4), H.nnz, n, lo, hi, int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))
+        if band_hook is not None:
+            band_hook(k, lo, hi, lo * (2 * n - lo + 1) // 2, hi * (2 * n - hi + 1) // 2)
+    return int(flag.item()) == 0
 
 
 def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w=None, frac_bits=None,
-                      acc=None) -> Accumulator:
+                      acc=None, band_hook=None) -> Accumulator:
     """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446)."""
     dev = H.device
     n = H.n_rows
@@ -486,29 +522,33 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     if acc is None:
         acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
-    form = os.environ.get("CPH_EXPAND_FORM", "")          # "", "banded", "binned", "direct": A/B switch for measurements
-    if entry_w is None and BINNED_MIN_N <= n <= BINNED_MAX_N and H.nnz >= BINNED_MIN_NNZ and form != "direct":
-        # the packed triangle does not fit in L2: group the pair updates by accumulator region first (expand.cu:
-        # "banded" = row bands with staged 256-byte record lines; "binned" = the round-1 2-D blocks, kept for larger n)
-        args = (ptr(H.pem_row), ptr(H.pem_pk), H.nnz, n, int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag))
-        fns = [lib().cph_expand_accumulate_banded] if n <= BANDED_MAX_N and form != "binned" else []
-        if form != "banded":
-            fns.append(lib().cph_expand_accumulate_binned)
-        for fn in fns:
+    form = os.environ.get("CPH_EXPAND_FORM", "")          # "", "swept", "binned", "direct": A/B switch for measurements
+    big = entry_w is None and n >= BINNED_MIN_N and H.nnz >= BINNED_MIN_NNZ
+    if form == "swept" and entry_w is None:
+        big = True
+    if big and form != "direct":
+        # the packed triangle does not fit in L2: update it region by region (expand.cu: "swept" = sorted 4-byte entries,
+        # one streaming pass per row band; "binned" = the round-1 pair records grouped by 2-D block)
+        if form != "binned" and n <= SWEEP_MAX_N:
+            if not zero:
+                diag.zero_()
+            if expand_accumulate_swept(H, use_high_order, frac_bits, acc, diag, zero, band_hook):
+                return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
+            if not zero:
+                raise _lib.CphError("swept expansion on top of an existing accumulator: entries do not fit the packed form")
+        elif n <= BINNED_MAX_N:
+            args = (ptr(H.pem_row), ptr(H.pem_pk), H.nnz, n, int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag))
+            fn = lib().cph_expand_accumulate_binned
             need = C.c_size_t(0)
             hp = C.c_uint64(0)
-            rc = fn(1, *args, None, C.byref(hp), None, 0, C.byref(need), None)
-            if rc == _lib.ERR_TOO_LARGE and fn is not fns[-1]:
-                continue
-            check(rc)
+            check(fn(1, *args, None, C.byref(hp), None, 0, C.byref(need), None))
             ws = _lib.workspace(need.value, dev)
             check(fn(1, *args, None, C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
             if int(hp.value) * 8 <= BINNED_MAX_RECORD_BYTES:
                 rec = torch.empty(max(int(hp.value), 1), dtype=torch.int64, device=dev)
                 check(fn(2, *args, ptr(rec), C.byref(hp), ws.data_ptr(), ws.numel(), C.byref(need), stream()))
                 return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
-            break
-        # too many pairs for the record scratch: the direct kernel below redoes the (cheap) zeroing and the diagonal
+        # the packed / record form does not fit: the direct kernel below redoes the (cheap) zeroing and the diagonal
     check(lib().cph_expand_accumulate_diag(ptr(H.pem_row), ptr(H.pem_pk), ptr(entry_w), H.nnz, max(n, 1),
                                            int(use_high_order), int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))
     return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))

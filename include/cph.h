@@ -221,14 +221,18 @@ int cph_expand_accumulate_diag(const uint32_t* pem_row, const uint32_t* pem_pk, 
  * returns the number of records in *h_pairs; the caller allocates pair_records (u64 each) and calls phase 2, which
  * writes and applies them.  n <= 115368 (46 block rows of <= 50 MB blocks).
  * phase 3 / 4 run the two halves of phase 2 apart (record fill only / apply only) for timing. */
-/* Banded form (round 2) for the same regime: the packed triangle is cut into <= 64 row bands of equal area (<= ~44 MB);
- * pair records (8 B) are staged per warp and band in shared memory and leave as 256-byte lines, then applied band after
- * band (the band stays in L2).  Same two-phase protocol and bit-identical results; *h_records = u64 records to allocate.
- * Supported while every band holds <= 4096 rows and <= 100 MB (n <= ~36k); CPH_ERR_TOO_LARGE otherwise. */
-int cph_expand_accumulate_banded(int phase, const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n,
-                                 int use_high_order, int frac_bits, int zero_first, uint64_t* acc, uint64_t* diag_fx,
-                                 uint64_t* pair_records, uint64_t* h_records, void* ws, size_t ws_bytes, size_t* h_ws_need,
-                                 cph_stream_t stream);
+/* Swept form (round 2) for the same regime, nothing materialised per pair.  cph_expand_sweep_prep sorts every hyperedge
+ * run by contig (stable) and packs each entry to 4 bytes -- head(1) | D_e(7) | count(24 - rb) | row(rb), rb = bits(n - 1)
+ * -- into pe4[nnz]; *flag (device u32) becomes non-zero when a count does not fit its field or a run is longer than 64
+ * entries (the caller then falls back to the direct kernel).  cph_expand_sweep_band handles ONE row band
+ * [row_lo, row_hi) of the packed triangle: it zeroes the band (zero_first), streams pe4 once, and adds every pair whose
+ * smaller contig lies in the band with one RED into the (L2-resident) band, plus the diagonal terms of the band's rows.
+ * Calling it for a partition of [0, n) into bands gives acc / diag_fx bit-identical to cph_expand_accumulate_diag.
+ * Between two band calls the caller may start the exchange of the finished band (multi-GPU). n <= 2^20. */
+int cph_expand_sweep_prep(const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n, int use_high_order,
+                          uint32_t* pe4, uint32_t* flag, cph_stream_t stream);
+int cph_expand_sweep_band(const uint32_t* pe4, uint64_t nnz, uint32_t n, uint32_t row_lo, uint32_t row_hi, int frac_bits,
+                          int zero_first, uint64_t* acc, uint64_t* diag_fx, cph_stream_t stream);
 int cph_expand_accumulate_binned(int phase, const uint32_t* pem_row, const uint32_t* pem_pk, uint64_t nnz, uint32_t n,
                                  int use_high_order, int frac_bits, int zero_first, uint64_t* acc, uint64_t* diag_fx,
                                  uint64_t* pair_records, uint64_t* h_pairs, void* ws, size_t ws_bytes,

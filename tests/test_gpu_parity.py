@@ -455,12 +455,14 @@ def test_extract_rows_with_explicit_zero_counts(api):
         assert np.array_equal(x, y)
 
 
-@pytest.mark.parametrize("form", ["banded", "binned"])
+@pytest.mark.parametrize("form", ["swept", "swept-fallback", "binned"])
 @pytest.mark.parametrize("use_high_order", [True, False])
 def test_binned_expansion_is_bit_identical(api, use_high_order, form, monkeypatch):
-    """Accumulators beyond L2 (n > 5.6k) take the banded kernels (pair records grouped by row band of the triangle, then
-    applied band by band) or, for larger n, the binned ones (2-D blocks).  Integer fixed-point sums do not depend on the order of addition, so triangle and diagonal must equal the
-    direct kernel's bit for bit -- including pairs whose count product does not fit the 34-bit record field."""
+    """Accumulators beyond L2 (n > 5.6k) take the swept kernels (runs sorted by contig and packed to 4 bytes, then one
+    streaming pass per L2-sized row band of the triangle) or the binned ones (pair records grouped by 2-D block).  Integer
+    fixed-point sums do not depend on the order of addition, so triangle and diagonal must equal the direct kernel's bit
+    for bit -- including large counts (swept: up to its count field; beyond it the device flag sends the call to the
+    direct kernel; binned: pairs whose count product does not fit the 34-bit record field)."""
     _, _, D, synth = api
     import torch
     g = synth.make_genome(6000, 10, 4, seed=91)
@@ -470,18 +472,20 @@ def test_binned_expansion_is_bit_identical(api, use_high_order, form, monkeypatc
     assert H.n_rows > D.BINNED_MIN_N and H.nnz >= D.BINNED_MIN_NNZ
     pk = H.pem_pk.view(torch.int32)
     big = torch.arange(0, H.nnz, 100_003, device=pk.device)
-    pk[big] = (pk[big] & ~0x00FFFFFF) | 200_000          # products above 2^34 with one another are unlikely; with
-    pk[big + 1] = (pk[big + 1] & ~0x00FFFFFF) | 150_000  # the neighbour entry (same hyperedge most of the time) they occur
+    hi, lo = (2_000, 1_500) if form == "swept" else (200_000, 150_000)   # n ~ 6k: 13 row bits, counts < 2^11 fit the field
+    pk[big] = (pk[big] & ~0x00FFFFFF) | hi               # products above 2^34 with one another are unlikely; with
+    pk[big + 1] = (pk[big + 1] & ~0x00FFFFFF) | lo       # the neighbour entry (same hyperedge most of the time) they occur
     H._bound = None
-    monkeypatch.setenv("CPH_EXPAND_FORM", form)
-    if form == "banded":
-        monkeypatch.setenv("CPH_BAND_MB", "3")          # 48 bands at this n: exercises many bands and the padded tails
+    monkeypatch.setenv("CPH_EXPAND_FORM", "binned" if form == "binned" else "swept")
+    monkeypatch.setenv("CPH_BAND_MB", "3")              # ~48 bands at this n
     l0 = __import__("cphasing_b200")._lib.launches()
     a1 = D.expand_accumulate(H, use_high_order=use_high_order)
     binned_launches = __import__("cphasing_b200")._lib.launches() - l0
     monkeypatch.setattr(D, "BINNED_MIN_N", 1 << 30)
     a2 = D.expand_accumulate(H, use_high_order=use_high_order)
-    assert binned_launches >= 3                          # count, (scan..,) fill, apply
+    assert binned_launches >= 3                          # binned: count, (scan..,) fill, apply; swept: prep + one per band
+    if form == "swept":
+        assert binned_launches >= 40                     # it really took the band passes (no fallback)
     assert a1.frac_bits == a2.frac_bits
     assert torch.equal(a1.diag, a2.diag)
     assert torch.equal(a1.acc, a2.acc)
