@@ -147,12 +147,11 @@ def device_step(D, cfg, g, t, ev, world, rank):
     H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0,
                     rowsum_hook=par.allreduce_rowsums if world > 1 else None)
     mark("incidence")
-    # the fixed-point scale derives from the (all-reduced) row sums, so every rank picks the same one
-    acc = D.expand_accumulate(H, use_high_order=True)
-    mark("accumulate")
+    # the fixed-point scale derives from the (all-reduced) row sums, so every rank picks the same one.  Exchange 2
+    # (world > 1): the partial accumulators are summed over the ranks (NCCL) -- band by band under the kernels of the next
+    # band when the triangle is swept (n >= 5.6k), so "exchange" is what stays exposed after the last local kernel.
+    acc = par.expand_accumulate_sum(H, use_high_order=True, on_local_done=lambda: mark("accumulate"))
     if world > 1:
-        par.sum_triangle(acc.acc, acc.n)     # exchange 2: reduce-scatter over contig row blocks + all-gather (NCCL)
-        par.sum_vector(acc.diag)
         mark("exchange")
     A = D.expand_emit(acc, min_weight=PARAMS["min_weight"], want32=True, want64=True)
     mark("emit")
@@ -177,9 +176,7 @@ def partition_tail(D, cfg, g, H, A, reps=3, world=1, rank=0):
         torch.cuda.synchronize(); t0 = time.perf_counter()
         if world > 1:       # H is this rank's column shard: the unweighted counts need the same exchange as A
             from cphasing_b200 import parallel as par
-            accu = D.expand_accumulate(H, use_high_order=False)
-            par.sum_triangle(accu.acc, accu.n)
-            par.sum_vector(accu.diag)
+            accu = par.expand_accumulate_sum(H, use_high_order=False)
             Au = D.expand_emit(accu, min_weight=1.0, want32=False, want64=True)
             del accu
             if rank != 0:   # kprune and the clustering run on one GPU (latency-bound at n <= 2e4)

@@ -325,21 +325,22 @@ __global__ void __launch_bounds__(SW_T) sw_prep_kernel(const u32* __restrict__ p
                                                        u32 rb, int use_high_order, u32* __restrict__ pe4, u32* __restrict__ flag) {
     constexpr u32 L = SW_TILE + SW_HALO;
     constexpr int NQ = (L + SW_T - 1) / SW_T;
-    __shared__ u32 rows[L];
+    constexpr int NW = NQ * SW_T / 32;
+    __shared__ u32 keys[L];                  // (row << 12) | position in the tile: distinct, ordered by (row, position)
     __shared__ u32 outs[L];
-    __shared__ u32 lohi[2];
+    __shared__ u32 hm[NW];                   // head bits; positions past the input count as heads
     const u64 t0 = (u64)blockIdx.x * SW_TILE;
+    const u32 lane = threadIdx.x & 31;
     u32 pkr[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {           // all global loads of the tile are in flight together
         const u32 x = q * SW_T + threadIdx.x;
         const bool ok = x < L && t0 + x < nnz;
-        if (x < L) rows[x] = ok ? pem_row[t0 + x] : CPH_HEAD;
+        const u32 v = ok ? pem_row[t0 + x] | (t0 + x == 0 ? CPH_HEAD : 0u) : CPH_HEAD;
         pkr[q] = ok ? pem_pk[t0 + x] : 0u;
-    }
-    if (threadIdx.x == 0) {
-        lohi[0] = L;
-        lohi[1] = L;
+        if (x < L) keys[x] = ((v & CPH_ROWM) << 12) | x;
+        const u32 mh = __ballot_sync(0xffffffffu, (v & CPH_HEAD) != 0u);
+        if (lane == 0) hm[x >> 5] = mh;
     }
     __syncthreads();
     const u32 cmax = 1u << (24 - rb);
@@ -347,35 +348,45 @@ __global__ void __launch_bounds__(SW_T) sw_prep_kernel(const u32* __restrict__ p
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
         const u32 x = q * SW_T + threadIdx.x;
-        if (x >= L) break;
-        const u32 rx = rows[x];
-        // the first head of the tile is within its first 64 entries, the first head at or after its end within the halo
-        if ((rx & CPH_HEAD) && (x < SW_HALO || x >= SW_TILE)) atomicMin(&lohi[x < SW_TILE ? 0 : 1], x);
-        if (t0 + x >= nnz) continue;
-        u32 s = x;
-        while (!(rows[s] & CPH_HEAD) && s > 0 && x - s < SW_HALO) --s;
-        if (!(rows[s] & CPH_HEAD)) {
-            if (s != 0) bad = true;          // run longer than the halo
-            continue;                        // (s == 0: the run started in the previous tile, which sorts it)
+        if (x >= L || t0 + x >= nnz) continue;
+        // start of my run: last head at or before x, at most 63 back
+        u32 wi = x >> 5;
+        u32 mk = hm[wi] & (0xffffffffu >> (31u - (x & 31u)));
+        for (int st = 0; st < 2 && mk == 0u && wi > 0u; ++st) mk = hm[--wi];
+        if (mk == 0u) {
+            if (x >= SW_HALO) bad = true;     // run longer than the halo
+            continue;                         // (x < 64: the run started in the previous tile, which sorts it)
         }
-        if (s >= SW_TILE) continue;          // starts in the next tile
-        const u32 ra = rx & CPH_ROWM;
-        u32 rank = 0, b = s;
-        do {
-            const u32 r = rows[b] & CPH_ROWM;
-            rank += (r < ra || (r == ra && b < x)) ? 1u : 0u;
-            ++b;
-        } while (b < L && !(rows[b] & CPH_HEAD) && b - s < SW_HALO);
-        if (b < L && !(rows[b] & CPH_HEAD)) bad = true;
+        const u32 s = wi * 32u + 31u - (u32)__clz(mk);
+        if (x - s >= SW_HALO) {
+            bad = true;
+            continue;
+        }
+        if (s >= SW_TILE) continue;           // starts in the next tile
+        // end of my run: first head after x
+        wi = x >> 5;
+        mk = (x & 31u) == 31u ? 0u : hm[wi] & (0xffffffffu << ((x & 31u) + 1u));
+        while (mk == 0u) mk = hm[++wi];       // the words past the window are all heads
+        const u32 e = wi * 32u + (u32)__ffs(mk) - 1u;
+        if (e - s > SW_HALO) {
+            bad = true;
+            continue;
+        }
+        const u32 ka = keys[x];
+        u32 rank = 0;
+        for (u32 b = s; b < e; ++b) rank += keys[b] < ka ? 1u : 0u;
         const u32 pk = pkr[q];
         const u32 c = pk & CPH_CNTM;
         if (c >= cmax) bad = true;
         const u32 D = use_high_order ? (pk >> 24) & 127u : 1u;
-        outs[s + rank] = (rank == 0 ? CPH_HEAD : 0u) | (D << 24) | (c << rb) | ra;
+        outs[s + rank] = (rank == 0 ? CPH_HEAD : 0u) | (D << 24) | (c << rb) | (ka >> 12);
     }
     if (bad) atomicOr(flag, 1u);
     __syncthreads();
-    const u32 lo = lohi[0], hi = lohi[1];
+    // my output range: [first head of the tile, first head at or after its end)
+    const u32 h0 = hm[0], h1 = hm[1], e0 = hm[SW_TILE / 32], e1 = hm[SW_TILE / 32 + 1];
+    const u32 lo = h0 ? (u32)__ffs(h0) - 1u : (h1 ? 32u + (u32)__ffs(h1) - 1u : L);
+    const u32 hi = e0 ? SW_TILE + (u32)__ffs(e0) - 1u : (e1 ? SW_TILE + 32u + (u32)__ffs(e1) - 1u : L);
     if (lo >= SW_TILE) return;               // no run starts here (only when a run is too long: flagged)
     for (u32 x = lo + threadIdx.x; x < hi && t0 + x < nnz; x += SW_T) pe4[t0 + x] = outs[x];
 }

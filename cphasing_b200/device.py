@@ -469,10 +469,14 @@ SWEEP_MAX_N = 1 << 20        # row field of the 4-byte packed entry (expand.cu s
 BINNED_MIN_NNZ = 1 << 22     # small inputs: the extra passes cost more than the DRAM read-modify-writes they avoid
 
 
-def sweep_bands(n, band_bytes=None):
-    """row bands [r0[k], r0[k+1]) of the packed upper triangle with at most ~band_bytes of u64 cells each."""
+def sweep_bands(n, band_bytes=None, mean_order=4.0):
+    """row bands [r0[k], r0[k+1]) of the packed upper triangle with at most ~band_bytes of u64 cells each.
+    Measured on B200 (scripts/diag_swept.py, profiles/r2f_swept_*.txt): with few pairs per pass (workload D, mean order 4)
+    128 MB bands are fastest -- fewer streaming passes, the 126 MB L2 still absorbs the REDs; with many pairs per pass
+    (workload E, mean order 8.5) 96 MB bands are, 128 MB thrashes."""
     if band_bytes is None:
-        band_bytes = int(float(os.environ.get("CPH_BAND_MB", "96")) * (1 << 20))
+        mb = os.environ.get("CPH_BAND_MB", "")
+        band_bytes = int((float(mb) if mb else (128.0 if mean_order <= 6.0 else 96.0)) * (1 << 20))
     cells = max(band_bytes // 8, n)          # at least one row
     # cells before row i: i (2n - i + 1) / 2; walk the rows with numpy (n <= 2^20)
     i = np.arange(n + 1, dtype=np.int64)
@@ -496,7 +500,7 @@ def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, ze
     if rc == _lib.ERR_TOO_LARGE:
         return False
     check(rc)
-    r0 = sweep_bands(n)
+    r0 = sweep_bands(n, mean_order=H.nnz / max(H.n_cols, 1))
     for k in range(len(r0) - 1):
         lo, hi = r0[k], r0[k + 1]
         check(lib().cph_expand_sweep_band(ptr(pe4), H.nnz, n, lo, hi, int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))
@@ -506,8 +510,9 @@ def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, ze
 
 
 def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w=None, frac_bits=None,
-                      acc=None, band_hook=None) -> Accumulator:
-    """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446)."""
+                      acc=None, band_hook=None, acc_out=None) -> Accumulator:
+    """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446).  `acc`: add onto an existing
+    triangle; `acc_out`: caller-owned storage for a fresh one; `band_hook`: see expand_accumulate_swept."""
     dev = H.device
     n = H.n_rows
     if frac_bits is None:
@@ -520,7 +525,7 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     tri = n * (n + 1) // 2
     zero = acc is None
     if acc is None:
-        acc = torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
+        acc = acc_out if acc_out is not None else torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     form = os.environ.get("CPH_EXPAND_FORM", "")          # "", "swept", "binned", "direct": A/B switch for measurements
     big = entry_w is None and n >= BINNED_MIN_N and H.nnz >= BINNED_MIN_NNZ
@@ -534,6 +539,8 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
                 diag.zero_()
             if expand_accumulate_swept(H, use_high_order, frac_bits, acc, diag, zero, band_hook):
                 return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
+            if band_hook is not None:
+                band_hook(-1, 0, 0, 0, 0)        # abandoned: the direct kernel below starts over
             if not zero:
                 raise _lib.CphError("swept expansion on top of an existing accumulator: entries do not fit the packed form")
         elif n <= BINNED_MAX_N:

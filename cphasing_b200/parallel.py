@@ -107,15 +107,77 @@ def sum_vector(v, group=None):
     return v
 
 
+def expand_accumulate_sum(H, use_high_order=True, group=None, on_local_done=None):
+    """this rank's partial accumulator of A = H W H^T summed over the ranks, in place and identical everywhere
+    (exchange 2).  When the accumulator is swept band by band (device.expand_accumulate_swept, n >= 5.6k) the sum of band
+    k travels on a side stream while band k + 1 is being accumulated, so only the last band's exchange is exposed;
+    otherwise one reduce-scatter + all-gather of the whole triangle follows the kernel.  `on_local_done()` is called when
+    the last local kernel has been launched (benchmarks mark the end of the local work there)."""
+    from . import device as D
+    rank, ws = world()
+    if ws == 1:
+        acc = D.expand_accumulate(H, use_high_order=use_high_order)
+        if on_local_done:
+            on_local_done()
+        return acc
+    overlap = dist.get_backend(group) == "nccl"
+    main = torch.cuda.current_stream() if overlap else None
+    comm = _comm_stream(H.device) if overlap else None
+    holder, bands = {}, []
+
+    def hook(k, lo, hi, c_lo, c_hi):
+        if k < 0:               # the swept attempt was abandoned (packed form does not fit): forget its exchanges
+            if overlap and bands:
+                done = torch.cuda.Event()
+                done.record(comm)
+                main.wait_event(done)
+            bands.clear()
+            return
+        bands.append((c_lo, c_hi))
+        if not overlap:
+            return
+        ev = torch.cuda.Event()
+        ev.record(main)
+        comm.wait_event(ev)
+        with torch.cuda.stream(comm):
+            dist.all_reduce(holder["acc"][c_lo:c_hi], op=dist.ReduceOp.SUM, group=group)
+
+    n = H.n_rows
+    holder["acc"] = torch.empty(max(n * (n + 1) // 2, 1), dtype=torch.int64, device=H.device)
+    acc = D.expand_accumulate(H, use_high_order=use_high_order, band_hook=hook, acc_out=holder["acc"])
+    if on_local_done:
+        on_local_done()
+    if bands and overlap:
+        done = torch.cuda.Event()
+        done.record(comm)
+        main.wait_event(done)
+    elif bands:
+        for c_lo, c_hi in bands:
+            dist.all_reduce(acc.acc[c_lo:c_hi], op=dist.ReduceOp.SUM, group=group)
+    else:
+        sum_triangle(acc.acc, acc.n, group)
+    sum_vector(acc.diag, group)
+    return acc
+
+
+_COMM = {}
+
+
+def _comm_stream(device):
+    key = str(device)
+    if key not in _COMM:
+        _COMM[key] = torch.cuda.Stream(device=device)
+    return _COMM[key]
+
+
 def sharded_clique_expansion(raw, min_contacts=25, min_weight=2.0, use_high_order=True, node_w=None, group=None,
-                             want32=True, want64=True):
+                             want32=True, want64=True, min_mapq=0, mapq_filter=True, row_drop=None):
     """stage 1c + 2 on this rank's shard `raw` (device.RawEdges of its concatemers) with the two exchanges.
+    `min_mapq` / `mapq_filter` / `row_drop` are HyperGraph's entry filter (min_quality) and remove_rows, as on one GPU.
     Returns (DeviceH of the shard, DeviceCSR of the GLOBAL A, identical on every rank)."""
     from . import device as D
-    H = D.incidence(raw, min_contacts=min_contacts, min_mapq=0,
+    H = D.incidence(raw, min_contacts=min_contacts, min_mapq=min_mapq, row_drop=row_drop, mapq_filter=mapq_filter,
                     rowsum_hook=lambda rs, mx: allreduce_rowsums(rs, mx, group))
-    acc = D.expand_accumulate(H, use_high_order=use_high_order)       # scale from the all-reduced bound: same everywhere
-    sum_triangle(acc.acc, acc.n, group)
-    sum_vector(acc.diag, group)
+    acc = expand_accumulate_sum(H, use_high_order=use_high_order, group=group)   # scale from the all-reduced bound
     A = D.expand_emit(acc, min_weight=min_weight, node_w=node_w, want32=want32, want64=want64)
     return H, A

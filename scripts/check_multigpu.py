@@ -26,7 +26,13 @@ def main():
     dev = torch.device(f"cuda:{local}")
     dist.init_process_group("nccl", device_id=dev)
     from cphasing_b200 import device as D, parallel as par, synth
-    n, m = 3000, 4_000_000
+    import argparse
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--contigs", type=int, default=3000, help="contigs; >= 5600 takes the swept expansion with the per-band "
+                                                        "exchange under the next band's kernels (CPH_BAND_MB sets the band size)")
+    ap.add_argument("--concatemers", type=int, default=4_000_000)
+    a = ap.parse_args()
+    n, m = a.contigs, a.concatemers
     g = synth.make_genome(n, 10, 4, seed=77)
     first, count = par.shard_range(m, rank, world)
     t = synth.porec_table_device(g, count, 78, law="poisson", first=first, device=dev)
