@@ -144,6 +144,23 @@ def check(status):
         raise CphError(f"libcph status {status}: {lib().cph_last_error().decode()}")
 
 
+def nvtx(name):
+    """decorator: an NVTX range per stage of the path (SURVEY.md 5: tracing) -- shows up in nsys / ncu --nvtx timelines;
+    a no-op cost of two calls when no tool listens."""
+    import functools
+
+    def deco(fn):
+        @functools.wraps(fn)
+        def wrapped(*a, **k):
+            torch.cuda.nvtx.range_push(name)
+            try:
+                return fn(*a, **k)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return wrapped
+    return deco
+
+
 def launches():
     return int(lib().cph_launch_count())
 

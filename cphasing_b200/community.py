@@ -13,9 +13,10 @@ import numpy as np
 import torch
 
 from . import device as D
-from ._lib import call_ws, ptr
+from ._lib import nvtx, call_ws, ptr
 
 LOUVAIN, LEIDEN = 0, 1
+LOUVAIN_ITERATIONS = 1     # multilevel passes restarted from the partition found (igraph's community_multilevel does one)
 
 
 class VertexClustering:
@@ -61,6 +62,7 @@ def _settings():
     return int(os.environ.get("CPH_COMMUNITY_PHASES", "0")), int(os.environ.get("CPH_COMMUNITY_MAX_SWEEPS", "0"))
 
 
+@nvtx("cph:community")
 def community_device(a: D.DeviceCSR, resolution=1.0, method="louvain", n_iterations=2, initial_membership=None,
                      use32=False):
     """a: symmetric CSR(A) on the device (both triangles, sorted indices; the diagonal is ignored).
@@ -81,8 +83,9 @@ def community_device(a: D.DeviceCSR, resolution=1.0, method="louvain", n_iterati
     d64 = None if d32 is not None else a.data64
     phases, sweeps = _settings()
     m = LEIDEN if method == "leiden" else LOUVAIN
+    iters = int(os.environ.get("CPH_COMMUNITY_ITERS", "0")) or (int(n_iterations) if m == LEIDEN else LOUVAIN_ITERATIONS)
     call_ws("cph_community", dev, ptr(a.indptr), ptr(a.indices), ptr(d32), ptr(d64), n, a.nnz, float(resolution), m,
-            int(n_iterations), phases, sweeps, ptr(init), ptr(mem), C.byref(q), st)
+            iters, phases, sweeps, ptr(init), ptr(mem), C.byref(q), st)
     stats = {"groups": int(st[0]), "levels": int(st[1]), "sweeps": int(st[2]), "refine_rounds": int(st[3])}
     return mem[:n], float(q.value), stats
 

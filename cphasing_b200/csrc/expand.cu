@@ -328,67 +328,65 @@ __global__ void __launch_bounds__(SW_T) sw_prep_kernel(const u32* __restrict__ p
     constexpr int NW = NQ * SW_T / 32;
     __shared__ u32 keys[L];                  // (row << 12) | position in the tile: distinct, ordered by (row, position)
     __shared__ u32 outs[L];
-    __shared__ u32 hm[NW];                   // head bits; positions past the input count as heads
+    __shared__ u32 hm[NW + 2];               // head bits; positions past the input count as heads
     const u64 t0 = (u64)blockIdx.x * SW_TILE;
+    if (threadIdx.x < 2) hm[NW + threadIdx.x] = 0xffffffffu;
+    const u32 nv = (u32)min((u64)L, nnz - t0);          // valid positions of the window (32-bit arithmetic from here on)
+    const u32* __restrict__ prow = pem_row + t0;
+    const u32* __restrict__ ppk = pem_pk + t0;
     const u32 lane = threadIdx.x & 31;
     u32 pkr[NQ];
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {           // all global loads of the tile are in flight together
         const u32 x = q * SW_T + threadIdx.x;
-        const bool ok = x < L && t0 + x < nnz;
-        const u32 v = ok ? pem_row[t0 + x] | (t0 + x == 0 ? CPH_HEAD : 0u) : CPH_HEAD;
-        pkr[q] = ok ? pem_pk[t0 + x] : 0u;
+        const bool ok = x < nv;
+        u32 v = ok ? prow[x] : CPH_HEAD;
+        pkr[q] = ok ? ppk[x] : 0u;
+        if (q == 0 && x == 0 && blockIdx.x == 0) v |= CPH_HEAD;
         if (x < L) keys[x] = ((v & CPH_ROWM) << 12) | x;
         const u32 mh = __ballot_sync(0xffffffffu, (v & CPH_HEAD) != 0u);
         if (lane == 0) hm[x >> 5] = mh;
     }
     __syncthreads();
     const u32 cmax = 1u << (24 - rb);
-    bool bad = false;
+    u32 bad = 0;
 #pragma unroll
     for (int q = 0; q < NQ; ++q) {
         const u32 x = q * SW_T + threadIdx.x;
-        if (x >= L || t0 + x >= nnz) continue;
-        // start of my run: last head at or before x, at most 63 back
-        u32 wi = x >> 5;
-        u32 mk = hm[wi] & (0xffffffffu >> (31u - (x & 31u)));
-        for (int st = 0; st < 2 && mk == 0u && wi > 0u; ++st) mk = hm[--wi];
-        if (mk == 0u) {
-            if (x >= SW_HALO) bad = true;     // run longer than the halo
-            continue;                         // (x < 64: the run started in the previous tile, which sorts it)
+        // start of my run: last head at or before x, at most 63 back (two words back at most)
+        const u32 wi = x >> 5, bi = x & 31u;
+        const u32 m0 = x < nv ? hm[wi] & (0xffffffffu >> (31u - bi)) : 0u;
+        const u32 m1 = wi >= 1u ? hm[wi - 1u] : 0u, m2 = wi >= 2u ? hm[wi - 2u] : 0u;
+        const u32 s = m0 ? wi * 32u + 31u - (u32)__clz(m0)
+                         : (m1 ? wi * 32u - 1u - (u32)__clz(m1) : (m2 ? wi * 32u - 33u - (u32)__clz(m2) : 0xffffffffu));
+        // end of my run: first head after x (positions past the window are heads)
+        const u32 a0 = bi == 31u ? 0u : hm[wi] & (0xffffffffu << (bi + 1u));
+        const u32 a1 = hm[wi + 1u], a2 = hm[wi + 2u];
+        const u32 e = a0 ? wi * 32u + (u32)__ffs(a0) - 1u
+                         : (a1 ? wi * 32u + 31u + (u32)__ffs(a1) : (a2 ? wi * 32u + 63u + (u32)__ffs(a2) : 0xffffffffu));
+        const bool mine = x < nv && s != 0xffffffffu && s < SW_TILE;       // runs that start here (see above)
+        if (x < nv && ((s == 0xffffffffu && x >= SW_HALO) || (s != 0xffffffffu && (x - s >= SW_HALO || e - s > SW_HALO)))) bad = 1u;
+        if (mine && e - s <= SW_HALO) {
+            const u32 ka = keys[x];
+            u32 rank = 0;
+            for (u32 b = s; b < e; ++b) rank += keys[b] < ka ? 1u : 0u;
+            const u32 pk = pkr[q];
+            const u32 c = pk & CPH_CNTM;
+            if (c >= cmax) bad = 1u;
+            const u32 D = use_high_order ? (pk >> 24) & 127u : 1u;
+            outs[s + rank] = (rank == 0 ? CPH_HEAD : 0u) | (D << 24) | (c << rb) | (ka >> 12);
         }
-        const u32 s = wi * 32u + 31u - (u32)__clz(mk);
-        if (x - s >= SW_HALO) {
-            bad = true;
-            continue;
-        }
-        if (s >= SW_TILE) continue;           // starts in the next tile
-        // end of my run: first head after x
-        wi = x >> 5;
-        mk = (x & 31u) == 31u ? 0u : hm[wi] & (0xffffffffu << ((x & 31u) + 1u));
-        while (mk == 0u) mk = hm[++wi];       // the words past the window are all heads
-        const u32 e = wi * 32u + (u32)__ffs(mk) - 1u;
-        if (e - s > SW_HALO) {
-            bad = true;
-            continue;
-        }
-        const u32 ka = keys[x];
-        u32 rank = 0;
-        for (u32 b = s; b < e; ++b) rank += keys[b] < ka ? 1u : 0u;
-        const u32 pk = pkr[q];
-        const u32 c = pk & CPH_CNTM;
-        if (c >= cmax) bad = true;
-        const u32 D = use_high_order ? (pk >> 24) & 127u : 1u;
-        outs[s + rank] = (rank == 0 ? CPH_HEAD : 0u) | (D << 24) | (c << rb) | (ka >> 12);
     }
     if (bad) atomicOr(flag, 1u);
     __syncthreads();
     // my output range: [first head of the tile, first head at or after its end)
     const u32 h0 = hm[0], h1 = hm[1], e0 = hm[SW_TILE / 32], e1 = hm[SW_TILE / 32 + 1];
     const u32 lo = h0 ? (u32)__ffs(h0) - 1u : (h1 ? 32u + (u32)__ffs(h1) - 1u : L);
-    const u32 hi = e0 ? SW_TILE + (u32)__ffs(e0) - 1u : (e1 ? SW_TILE + 32u + (u32)__ffs(e1) - 1u : L);
+    u32 hi = e0 ? SW_TILE + (u32)__ffs(e0) - 1u : (e1 ? SW_TILE + 32u + (u32)__ffs(e1) - 1u : L);
     if (lo >= SW_TILE) return;               // no run starts here (only when a run is too long: flagged)
-    for (u32 x = lo + threadIdx.x; x < hi && t0 + x < nnz; x += SW_T) pe4[t0 + x] = outs[x];
+    hi = min(hi, nv);
+    u32* __restrict__ po = pe4 + t0;
+    for (u32 x = lo + threadIdx.x; x < hi; x += SW_T) po[x] = outs[x];
 }
 
 // Band pass, warp-autonomous: every warp streams its own 512-entry tiles (4 x uint4 per lane + a 64-entry halo), keeps the

@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import call_ws, check, lib, ptr, stream
+from ._lib import call_ws, check, lib, nvtx, ptr, stream
 
 
 def _dev(device=None):
@@ -168,6 +168,7 @@ class PreFilter:
         return pf, keep
 
 
+@nvtx("cph:porec_to_edges")
 def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, contig_len=None, min_mapq=1,
                    min_order=2, max_order=50, edge_length=0, read_offset=0, device=None, prefilter: PreFilter = None) -> RawEdges:
     dev = _dev(device)
@@ -297,6 +298,7 @@ def _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_o
     return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed(), None
 
 
+@nvtx("cph:pairs_to_edges")
 def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig_len=None, min_mapq=1,
                    edge_length=0, device=None, prefilter: PreFilter = None) -> RawEdges:
     dev = _dev(device)
@@ -377,6 +379,7 @@ def row_sums(e, min_mapq=0, row_drop=None, use_mapq=True, packed=False):
     return out, mx
 
 
+@nvtx("cph:incidence")
 def incidence(e: RawEdges, min_contacts=1, min_mapq=0, row_drop=None, mapq_filter=True, rowsum_hook=None) -> DeviceH:
     """HyperGraph.get_data + remove_rows + incidence_matrix (algorithms/hypergraph.py:162-314).
 
@@ -429,6 +432,7 @@ def _incidence_build(row, col, count, mapq, nnz, n_contigs, min_mapq, row_map, n
     return DeviceH(pem_row[:k], pem_pk[:k], k, int(n_rows), n_cols, keep, rs)
 
 
+@nvtx("cph:sub_incidence")
 def sub_incidence(H: DeviceH, idx, col_min=2) -> DeviceH:
     """extract_incidence_matrix2 (algorithms/hypergraph.py:938-954): rows `idx` (in that order) of H,
     hyperedges whose remaining summed count <= 1 dropped and renumbered."""
@@ -509,6 +513,7 @@ def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, ze
     return int(flag.item()) == 0
 
 
+@nvtx("cph:expand_accumulate")
 def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w=None, frac_bits=None,
                       acc=None, band_hook=None, acc_out=None) -> Accumulator:
     """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446).  `acc`: add onto an existing
@@ -561,6 +566,7 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
     return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
 
 
+@nvtx("cph:expand_emit")
 def expand_emit(a: Accumulator, min_weight=0.1, node_w=None, want32=True, want64=True) -> DeviceCSR:
     """threshold (:453-455), optional w_i w_j normalisation (:590-602), CSR emit."""
     dev = a.acc.device

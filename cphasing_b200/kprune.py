@@ -14,7 +14,7 @@ import torch
 
 from . import device as D
 from . import graphops
-from ._lib import check, lib, ptr, stream
+from ._lib import nvtx, check, lib, ptr, stream
 
 logger = logging.getLogger(__name__)
 
@@ -54,6 +54,7 @@ def groups_from_first(first, n):
     return ptr_, idx
 
 
+@nvtx("cph:kprune")
 def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False, first=None):
     """-> (flag uint8[nnz] device, row_of int32[nnz] device[, best_with, best_all]).
     first: {contig: allele} overriding the allele groups derived from `allele_pairs` (max_alleles = 1 only)."""
