@@ -586,23 +586,31 @@ def run_own(args):
         if not args.no_partition and cfg["kind"] == "porec" and "hyperpartition" in out:
             out["hyperpartition"]["api"] = api_partition(cfg, g, host)
         t = {k: v.to(dev) for k, v in host.items()} if not args.no_cpu_baseline else None
-    if world > 1 and not args.no_e2e:
-        # every rank feeds its own shard from pinned host memory through the device-module API (chunked H2D under the
-        # group-by kernel, the two NCCL exchanges, CSR emit) and rank 0 reads A back; max over ranks
+    if world > 1 and not args.no_e2e and cfg["kind"] == "porec":
+        # every rank feeds ITS shard from pinned host memory through the public classes in column-shard mode
+        # (HyperExtractor -> HyperGraph(column_shard) .incidence_matrix -> clique_expansion_init: chunked H2D under the
+        # group-by kernel, row-sum all-reduce, the accumulator exchange, CSR emit) and rank 0 reads A back; max over ranks.
+        # The process is first bound to the NUMA node of its GPU so that the pinned staging buffers sit next to it.
         import torch
-        from cphasing_b200 import device as Dm
+        from cphasing_b200 import device as Dm, hypergraph as hg
+        from cphasing_b200.algorithms import hypergraph as ah
+        node = Dm.bind_host_to_gpu_node(local)
         host = {k: torch.empty(v.shape, dtype=v.dtype, pin_memory=True).copy_(v) for k, v in t.items()}
         h2d = sum(v.numel() * v.element_size() for v in host.values())
         del t, raw, H, A
         _lib.release_workspace(); torch.cuda.empty_cache()
 
         def e2e_multi():
-            evs = []
-            _, _, A2 = device_step(D, cfg, g, host, evs, world, rank)
+            ex = hg.HyperExtractor.from_arrays(host["read_idx"], host["contig_idx"], host["mapq"], g.contig_idx, g.contigsizes,
+                                               min_quality=PARAMS["min_mapq"], min_order=PARAMS["min_order"],
+                                               max_order=PARAMS["max_order"], edge_length=0)
+            HG = ah.HyperGraph(ex.edges, min_quality=PARAMS["min_mapq"], mapq_filter=False)
+            HG.column_shard = True
+            Hs = HG.incidence_matrix(PARAMS["min_contacts"])
+            A2 = ah.HyperGraph.clique_expansion_init(Hs, min_weight=PARAMS["min_weight"])
             nb = 0
             if rank == 0:
-                parts = [Dm.to_host(A2.indptr), Dm.to_host(A2.indices), Dm.to_host(A2.data32)]
-                nb = sum(x.nbytes for x in parts)
+                nb = A2.data.nbytes + A2.indices.nbytes + A2.indptr.nbytes     # touching .data materialises the scipy CSR
             torch.cuda.synchronize()
             return nb
         for _ in range(2):
@@ -619,10 +627,10 @@ def run_own(args):
         dist.all_reduce(sent)
         out["e2e"] = {"value": cfg["m"] * world / dt, "unit": "concatemers/s", "h2d_bytes_per_step": int(sent.item()),
                       "host_input_bytes_per_step": h2d * world, "host_pack_threads": Dm._pack_threads(),
-                      "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3,
-                      "api": "per rank: device.porec_to_edges(host columns) -> device.incidence (row-sum all-reduce) -> "
-                             "device.expand_accumulate -> triangle reduce-scatter/all-gather -> device.expand_emit; "
-                             "rank 0 reads CSR(A) back"}
+                      "host_numa_node_rank0": node, "d2h_bytes_per_step": d2h, "ms_per_step": dt * 1e3,
+                      "api": "per rank: HyperExtractor.from_arrays(host shard) -> HyperGraph(column_shard=True)"
+                             ".incidence_matrix (row-sum all-reduce) -> HyperGraph.clique_expansion_init (accumulator "
+                             "exchange over NCCL) ; rank 0 reads the scipy CSR of A back"}
     parity_ok = True
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         ah = reference_module()

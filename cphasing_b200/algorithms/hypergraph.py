@@ -328,9 +328,20 @@ class HyperGraph:
         self._trip = None
 
     # -- algorithms/hypergraph.py:249-314
+    #: one process per GPU, each holding the hyperedges of ITS concatemer range: set to True on every rank
+    #: and incidence_matrix all-reduces the per-contig contact sums (the min_contacts filter is global) while
+    #: clique_expansion_init sums the partial accumulators over the ranks (cphasing_b200/parallel.py) -- H stays the
+    #: rank's column shard, A comes out global and identical everywhere.  Not in the reference (single process).
+    column_shard = False
+
     def incidence_matrix(self, min_contacts=1):
+        hook = None
+        if self.column_shard:
+            from .. import parallel as par
+            hook = par.allreduce_rowsums
         H = D.incidence(self._raw, min_contacts=min_contacts, min_mapq=self.min_quality if self._use_mapq else 0,
-                        row_drop=self._row_drop, mapq_filter=self._use_mapq)
+                        row_drop=self._row_drop, mapq_filter=self._use_mapq, rowsum_hook=hook)
+        H.column_shard = bool(self.column_shard)
         if min_contacts:
             keep = H.row_keep.cpu().numpy()
             self.remove_contig_idx = np.where(~keep)[0]
@@ -369,8 +380,13 @@ class HyperGraph:
         node_w = None
         if NW is not None:
             node_w = _node_weights_from_NW(NW)
-        A, _acc = D.clique_expansion(dH, use_high_order=use_high_order, min_weight=float(min_weight), node_w=node_w,
-                                     entry_w=entry_w, want32=True, want64=True)
+        if getattr(dH, "column_shard", False) and entry_w is None:       # H is this rank's shard: A = sum over the ranks
+            from .. import parallel as par
+            acc = par.expand_accumulate_sum(dH, use_high_order=use_high_order)
+            A = D.expand_emit(acc, float(min_weight), node_w, True, True)
+        else:
+            A, _acc = D.clique_expansion(dH, use_high_order=use_high_order, min_weight=float(min_weight), node_w=node_w,
+                                         entry_w=entry_w, want32=True, want64=True)
         out = wrap_adjacency(A)
         if P_allelic_idx or P_weak_idx:                                   # :464-481
             out = HyperGraph.reweight_pairs(out, P_allelic_idx, P_weak_idx, allelic_factor)

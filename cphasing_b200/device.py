@@ -255,6 +255,33 @@ def _host_columns(read_idx, contig_idx, mapq):
     return out
 
 
+def bind_host_to_gpu_node(device_index=None):
+    """Pin this process (and, by first touch, the pinned staging buffers it allocates afterwards) to the CPUs of the NUMA
+    node the GPU hangs off.  With one process per GPU on a two-socket host the chunked H2D copies otherwise cross the
+    socket interconnect for half of the ranks.  Best effort: returns the node number, or None when the topology cannot be
+    read or the affinity cannot be set (containers with a restricted cpuset)."""
+    try:
+        idx = torch.cuda.current_device() if device_index is None else int(device_index)
+        p = torch.cuda.get_device_properties(idx)
+        bus = f"{getattr(p, 'pci_domain_id', 0):04x}:{p.pci_bus_id:02x}:{p.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{bus}/numa_node") as fh:
+            node = int(fh.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as fh:
+            cpus = set()
+            for part in fh.read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+        allowed = cpus & set(os.sched_getaffinity(0))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return node
+    except Exception:                                   # noqa: BLE001 -- topology files absent, no permission, ...
+        return None
+
+
 def _pack_threads():
     """host threads for the packed transfer: STREAM_PACK_THREADS, or (auto) the cores of this process less two.  The
     re-encoding is bound by host memory bandwidth (about 17 B of traffic per record against 9 B for the plain copy), so

@@ -530,11 +530,24 @@ class HyperPartition:
         itv = self.idx_to_vertices
         results, assignments = [], []
         self.exclude_groups = []
-        for num, sub_k in enumerate(self.K, 1):                                            # :2150-2190, in-process
-            sub_group_number = int(k[1][num - 1]) if isinstance(k[1], dict) else int(k[1])
+        # :2150-2190.  The reference hands one first-round group to each loky worker process (every worker gets H).  Here
+        # the groups run in-process, and when the caller runs one process per GPU with torch.distributed initialised and
+        # the same H on every rank ("replicas") rank r takes the groups r, r + world, ... and the results
+        # are all-gathered, so every rank ends with the same K.  `fan_out_groups = False` keeps everything on one rank.
+        from . import parallel as par
+        rank, world = par.world()
+        fan = world > 1 and getattr(self, "fan_out_groups", True)
+        jobs = []
+        for num, sub_k in enumerate(self.K, 1):
             if self.exclude_group_to_second and num in self.exclude_group_to_second:
                 self.exclude_groups.append(sub_k)
                 continue
+            jobs.append((num, sub_k))
+        done = {}
+        for j, (num, sub_k) in enumerate(jobs):
+            if fan and j % world != rank:
+                continue
+            sub_group_number = int(k[1][num - 1]) if isinstance(k[1], dict) else int(k[1])
             _, ca, new_K = HyperPartition._incremental_partition(
                 sub_k, itv, sub_group_number, self.alleletable if self.prunetable is None else None, prune_pair_df, self.H,
                 vertices_idx_sizes, self.NW, None, self.resolution2, init_resolution=self.init_resolution2,
@@ -543,6 +556,11 @@ class HyperPartition:
                 allelic_factor=self.allelic_factor, cross_allelic_factor=self.cross_allelic_factor,
                 min_scaffold_length=self.min_scaffold_length, threshold=self.threshold, max_round=self.max_round, num=num,
                 threads=self.threads, cluster_method=self.cluster_method)
+            done[num] = (ca, new_K)
+        if fan:
+            done = par.merge_group_results(done)
+        for num, _ in jobs:
+            ca, new_K = done[num]
             if new_K is not None:
                 results.append(new_K)
                 assignments.append(ca)

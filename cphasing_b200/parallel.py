@@ -101,6 +101,23 @@ def sum_triangle(acc, n, group=None):
     return acc
 
 
+def merge_group_results(local, group=None):
+    """second-round fan-out ("replicas"; replaces the loky workers of hyperpartition.py:2150-2189): every
+    rank contributes the {group number: result} of the first-round groups it ran; returns the union, same on every rank."""
+    rank, ws = world()
+    if ws == 1:
+        return dict(local)
+    parts = [None] * ws
+    dist.all_gather_object(parts, dict(local), group=group)
+    out = {}
+    for p in parts:
+        dup = set(out) & set(p)
+        if dup:
+            raise RuntimeError(f"first-round groups {sorted(dup)} were run by more than one rank")
+        out.update(p)
+    return out
+
+
 def sum_vector(v, group=None):
     if world()[1] > 1:
         dist.all_reduce(v, op=dist.ReduceOp.SUM, group=group)

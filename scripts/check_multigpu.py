@@ -64,6 +64,30 @@ def main():
             ok &= out["H_shards_tile_global_H"]
             del tf, rawf, Hf, Af
         dist.barrier()
+    # the same through the public classes in column-shard mode (host tables in, scipy CSR out)
+    from cphasing_b200 import hypergraph as hgm
+    from cphasing_b200.algorithms import hypergraph as ah
+    mc = min(m, 1_000_000)
+    f2, c2 = par.shard_range(mc, rank, world)
+    th = synth.porec_table(g, c2, seed=79, first=f2)
+    ex = hgm.HyperExtractor.from_arrays(th["read_idx"], th["contig_idx"], th["mapq"], g.contig_idx, g.contigsizes,
+                                        min_quality=1, edge_length=0)
+    HG = ah.HyperGraph(ex.edges, min_quality=1)
+    HG.column_shard = True
+    Hs = HG.incidence_matrix(min_contacts=10)
+    As = ah.HyperGraph.clique_expansion_init(Hs, min_weight=1.0)
+    if rank == 0:
+        tf = synth.porec_table(g, mc, seed=79)
+        exf = hgm.HyperExtractor.from_arrays(tf["read_idx"], tf["contig_idx"], tf["mapq"], g.contig_idx, g.contigsizes,
+                                             min_quality=1, edge_length=0)
+        HGf = ah.HyperGraph(exf.edges, min_quality=1)
+        Af = ah.HyperGraph.clique_expansion_init(HGf.incidence_matrix(min_contacts=10), min_weight=1.0)
+        same = (As.shape == Af.shape and np.array_equal(As.indptr, Af.indptr) and np.array_equal(As.indices, Af.indices)
+                and np.array_equal(As.data, Af.data))
+        out["class_layer_column_shard"] = {"A_identical": bool(same), "nnz_A": int(Af.nnz), "nodes_equal":
+                                           bool(np.array_equal(HG.nodes, HGf.nodes))}
+        ok &= same
+    dist.barrier()
     if rank == 0:
         out["ok"] = bool(ok)
         print(json.dumps(out), flush=True)

@@ -105,3 +105,44 @@ def test_two_rank_column_shards_reproduce_the_single_process_counts():
         assert mx_r == int(k.max())
         assert n_r == H.shape[0]
         assert np.array_equal(acc_r, C[iu]), "summed integer partials must be bit-exact"
+
+
+def _fan_worker(rank, ws, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        # 5 first-round groups; rank r runs the jobs r, r + ws, ... exactly as HyperPartition.incremental_partition does
+        jobs = [(num, list(range(10 * num, 10 * num + 4))) for num in range(1, 6)]
+        local = {num: (None, [grp[:2], grp[2:]]) for j, (num, grp) in enumerate(jobs) if j % ws == rank}
+        merged = par.merge_group_results(local)
+        q.put((rank, sorted(merged), merged[3][1]))
+        try:
+            par.merge_group_results({1: (None, [])})               # every rank claims group 1: must be refused
+            q.put((rank, "no error"))
+        except RuntimeError as e:
+            q.put((rank, "refused" if "more than one rank" in str(e) else repr(e)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_second_round_fan_out_gathers_every_group_on_every_rank():
+    """the replicas form of the second round (hyperpartition.py:2150-2189 loky fan-out): round-robin jobs, all-gather"""
+    ws = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_fan_worker, args=(r, ws, port, q)) for r in range(ws)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=240) for _ in range(2 * ws)]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    full = [g for g in got if len(g) == 3]
+    assert len(full) == ws
+    for rank, nums, grp3 in full:
+        assert nums == [1, 2, 3, 4, 5]
+        assert grp3 == [[30, 31], [32, 33]]
+    assert all(g[1] == "refused" for g in got if len(g) == 2)
