@@ -90,6 +90,10 @@ _SIGS = {
     "cph_dense_scale_pairs": (_I, [_P, _U32, _P, _P, _U64, _D, _P]),
     "cph_dense_to_csr_count": (_I, [_P, _U32, _I, C.POINTER(_U64)] + _WS),
     "cph_dense_to_csr_emit": (_I, [_P, _U32, _I, _P, _P, _P, _P, _P, _P]),
+    "cph_fnv1a": (_U64, [C.c_char_p, _U64]),
+    "cph_tsv_count_rows": (_I, [_P, _U64, _I, C.POINTER(_U64)]),
+    "cph_tsv_parse": (_I, [_P, _U64, _I, _I, C.POINTER(_I), C.POINTER(_I), C.POINTER(_P), _U64, _P, _P, _U32, _P, _U32,
+                           C.POINTER(_U64), C.POINTER(_U64)]),
     "cph_synth_porec_count": (_I, [_U64, _U64, _U64, _I, _P, C.POINTER(_U64)] + _WS),
     "cph_synth_porec_fill": (_I, [_U64, _U64, _U64, _I, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),
     "cph_synth_pairs": (_I, [_U64, _U64, _U64, _D, _U32, _U32, _U32, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _P]),

@@ -123,6 +123,10 @@ def _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_in
     return pf, names
 
 
+class _NotGrouped(Exception):
+    pass
+
+
 class HyperExtractor:
     """hypergraph.py:1483-1911."""
 
@@ -140,7 +144,7 @@ class HyperExtractor:
         self.prefilter, self.names = _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_invert)
         self.threads = threads
         self.is_parquet = is_parquet
-        tables = _tables if _tables is not None else [self._load(p) for p in self.pore_c_table_pathes]
+        tables = _tables if _tables is not None else list(self.pore_c_table_pathes)
         self.edges = self.generate_edges(tables)
 
     @classmethod
@@ -150,36 +154,80 @@ class HyperExtractor:
         return cls(None, contig_idx, contigsizes, _tables=[t], **kw)
 
     def _load(self, path):
+        """whole table in memory (parquet input, and the fallback for text tables that are not grouped by read)"""
         # porec table columns (hypergraph.py:1500-1504, 1706-1717): read_idx(0) chrom(5) start(6) end(7) mapq(8)
         if self.is_parquet:
             df = pd.read_parquet(path, columns=["read_idx", "chrom", "start", "end", "mapping_quality"])
             df.columns = ["read_idx", "chrom", "start", "end", "mapq"]
-        else:
-            try:
-                df = pd.read_csv(path, sep="\t", header=None, comment="#", usecols=[0, 5, 6, 7, 8],
-                                 names=["read_idx", "chrom", "start", "end", "mapq"],
-                                 dtype={"read_idx": np.uint32, "start": np.uint32, "end": np.uint32, "mapq": np.int8})
-            except (pd.errors.EmptyDataError, ValueError):
-                logger.error(f"The pore-c table `{path}` is empty or malformed, please check it.")   # :1621-1630
-                sys.exit(-1)
-        return {"read_idx": df["read_idx"].to_numpy(), "contig": _name_codes(df["chrom"], self.names),
-                "mapq": df["mapq"].to_numpy(), "start": df["start"].to_numpy(), "end": df["end"].to_numpy()}
+            return {"read_idx": df["read_idx"].to_numpy(), "contig": _name_codes(df["chrom"], self.names),
+                    "mapq": df["mapq"].to_numpy(), "start": df["start"].to_numpy(), "end": df["end"].to_numpy()}
+        from . import ingest
+        cols, bad = ingest.read_table(path, ingest.POREC_FIELDS, self.names, threads=max(int(self.threads or 1), 1))
+        self._check_table(path, cols, bad)
+        return cols
+
+    @staticmethod
+    def _check_table(path, cols, bad):
+        if bad or len(cols["read_idx"]) == 0:
+            logger.error(f"The pore-c table `{path}` is empty or malformed, please check it.")       # :1621-1630
+            sys.exit(-1)
+
+    def _stream(self, path):
+        """text table -> chunks of whole reads, decoded block by block while the previous chunk is on the GPU
+        (cphasing_b200/ingest.py).  Yields column dicts; raises _NotGrouped when the file is not ordered by read id (the
+        group-by of chunk k would then miss records that come later) -- the caller falls back to `_load`."""
+        from . import ingest
+        carry, last, total, nbad = None, -1, 0, 0
+        for cols, bad in ingest.read_table_chunks(path, ingest.POREC_FIELDS, self.names,
+                                                  threads=max(int(self.threads or 1), 1)):
+            nbad += bad
+            r = cols["read_idx"]
+            if len(r) == 0:
+                continue
+            if int(r[0]) < last or np.any(r[1:] < r[:-1]):
+                raise _NotGrouped()
+            last = int(r[-1])
+            if carry is not None:
+                cols = {k: np.concatenate([carry[k], v]) for k, v in cols.items()}
+                r = cols["read_idx"]
+            cut = int(np.searchsorted(r, r[-1], side="left"))          # the last read may continue in the next block
+            carry = {k: v[cut:] for k, v in cols.items()}
+            if cut:
+                total += cut
+                yield {k: v[:cut] for k, v in cols.items()}
+        if carry is not None and len(carry["read_idx"]):
+            total += len(carry["read_idx"])
+            yield carry
+        self._check_table(path, {"read_idx": np.empty(total, dtype=np.uint8)}, nbad)
+
+    def _edges_of(self, t, n, ln, offset):
+        return D.porec_to_edges(t["read_idx"], t["contig"], t["mapq"], n, start=t.get("start"), end=t.get("end"),
+                                contig_len=ln, min_mapq=self.min_quality, min_order=self.min_order,
+                                max_order=self.max_order, edge_length=self.edge_length, read_offset=offset,
+                                prefilter=self.prefilter)
 
     def generate_edges(self, tables):
+        """tables: in-memory column dicts (from_arrays) or paths (decoded here, streaming where the format allows)"""
         n = len(self.contig_idx)
         ln = _lengths(self.contig_idx, self.contigsizes) if self.edge_length else None
         parts = []
         offset = 0
         for t in tables:
-            raw = D.porec_to_edges(t["read_idx"], t["contig"], t["mapq"], n, start=t.get("start"), end=t.get("end"),
-                                   contig_len=ln, min_mapq=self.min_quality, min_order=self.min_order,
-                                   max_order=self.max_order, edge_length=self.edge_length, read_offset=offset,
-                                   prefilter=self.prefilter)
-            parts.append(raw)
+            if isinstance(t, dict):
+                mine = [self._edges_of(t, n, ln, offset)]
+            elif self.is_parquet:
+                mine = [self._edges_of(self._load(t), n, ln, offset)]
+            else:
+                try:
+                    mine = [self._edges_of(c, n, ln, offset) for c in self._stream(t)]
+                except _NotGrouped:
+                    logger.info(f"`{t}` is not ordered by read id: decoding it as one table.")
+                    mine = [self._edges_of(self._load(t), n, ln, offset)]
+            parts.extend(mine)
             # disjoint read ids per input file (hypergraph.py:1871-1875): the next file starts after the largest
             # SURVIVING (already shifted) read id of this one
-            if len(tables) > 1 and raw.nnz:
-                offset = raw.n_cols
+            if len(tables) > 1:
+                offset = max([offset] + [p.n_cols for p in mine if p.nnz])
         raw = parts[0] if len(parts) == 1 else _concat_raw(parts, n)
         logger.info(f"Only retained Pore-C concatemer that: {self.min_order} <= contig order <= {self.max_order}.")
         e = _edges_from_raw(raw, self.contig_idx, self.contigsizes)
@@ -221,7 +269,8 @@ class Extractor:
                            "against split contig sizes keeps nothing)")
             self.edge_length = 0
         self.prefilter, self.names = _prefilter(contig_idx, split_length, split_contig_boundarys, hcr_bed, hcr_invert)
-        tables = _tables if _tables is not None else [self._load(p) for p in self.pairs_pathes]
+        self.threads = threads
+        tables = _tables if _tables is not None else [t for p in self.pairs_pathes for t in self._load(p)]
         self.edges = self.generate_edges(tables)
 
     @classmethod
@@ -230,16 +279,27 @@ class Extractor:
         return cls(None, contig_idx, contigsizes, _tables=[t], **kw)
 
     def _load(self, path):
+        """-> list of column dicts: one for a pairs file, one per parquet chunk for a PQS directory"""
+        from . import ingest
+        if ingest.is_pqs(path):
+            # PQS store (pqs.py:112-131, 674-809): q1/*.parquet when MAPQ >= 1 is asked for, else q0/*.parquet.  The
+            # reference's q0 path additionally keeps only MAPQ-0 pairs and samples them (random, seed 0, :1190-1197,
+            # 708-722) on top of q1; that sampling is tied to polars' RNG and is not reproduced.
+            if self.min_mapq < 1:
+                raise NotImplementedError("PQS input with min_quality = 0 (q0 sampling against q1, pqs.py:708-722) is not "
+                                          "implemented; use min_quality >= 1 or a pairs file")
+            files, with_mapq = ingest.pqs_chunks(path, self.min_mapq)
+            if not files:
+                logger.error(f"The pqs `{path}` holds no parquet chunk, please check it.")
+                sys.exit(-1)
+            lut = lambda ser: _name_codes(ser, self.names)
+            return [ingest.read_pqs_chunk(f, lut, self.min_mapq, with_mapq) for f in files]
         # 4DN pairs columns (hypergraph.py:904-909): chrom1(1) pos1(2) chrom2(3) pos2(4) mapq(7)
-        try:
-            df = pd.read_csv(path, sep="\t", header=None, comment="#", usecols=[1, 2, 3, 4, 7],
-                             names=["chrom1", "pos1", "chrom2", "pos2", "mapq"])
-        except (pd.errors.EmptyDataError, ValueError):
+        cols, bad = ingest.read_table(path, ingest.PAIRS_FIELDS, self.names, threads=max(int(getattr(self, "threads", 4) or 1), 1))
+        if bad or len(cols["mapq"]) == 0:
             logger.error(f"The pairs `{path}` is empty, can not load anything, please check it.")
             sys.exit(-1)
-        return {"chrom1": _name_codes(df["chrom1"], self.names), "chrom2": _name_codes(df["chrom2"], self.names),
-                "mapq": df["mapq"].to_numpy().astype(np.int8), "pos1": df["pos1"].to_numpy().astype(np.uint32),
-                "pos2": df["pos2"].to_numpy().astype(np.uint32)}
+        return [cols]
 
     def generate_edges(self, tables):
         n = len(self.contig_idx)

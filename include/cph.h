@@ -362,6 +362,18 @@ int cph_dense_to_csr_count(const double* dense, uint32_t n, int mode, uint64_t* 
 int cph_dense_to_csr_emit(const double* dense, uint32_t n, int mode, const void* ws, int64_t* indptr, int32_t* indices,
                           float* data32, double* data64, cph_stream_t stream);
 
+/* ---- host-side table decode (replaces the polars CSV reader of hypergraph.py:1706-1717, 904-909) -------
+ * Multi-threaded TSV field parser, host memory in and out (no device work).  A block of whole lines is decoded into
+ * columnar arrays: n_fields selected columns in increasing column order, field_kind 0 = unsigned -> u32, 1 = contig name
+ * -> index through the open-addressing table (name_slots[h & (n_slots-1)] = index + 1, 0 = empty, linear probing, keyed
+ * by cph_fnv1a; unknown names -> n_names), 2 = integer -> i8 (saturating).  Lines starting with '#' and empty lines are
+ * skipped; malformed lines are skipped and counted in *n_bad.  out[k] must hold `cap` rows (cph_tsv_count_rows). */
+uint64_t cph_fnv1a(const char* p, uint64_t len);
+int cph_tsv_count_rows(const char* buf, uint64_t len, int n_threads, uint64_t* n_rows);
+int cph_tsv_parse(const char* buf, uint64_t len, int n_threads, int n_fields, const int* field_col, const int* field_kind,
+                  void* const* out, uint64_t cap, const char* names_blob, const uint64_t* names_off, uint32_t n_names,
+                  const uint32_t* name_slots, uint32_t n_slots, uint64_t* n_rows, uint64_t* n_bad);
+
 #ifdef __cplusplus
 }
 #endif
