@@ -594,6 +594,46 @@ def _upper_pairs_symmetric(P):
     return np.concatenate([ru, cu]), np.concatenate([cu, ru])
 
 
+class DevicePairs(list):
+    """A pair list `[rows, cols]` whose entries live on the DEVICE (int64 vectors); behaves like the two-element list of
+    pandas Series the reference passes around (hyperpartition.py:438-461: P_allelic_idx / P_weak_idx) -- indexing,
+    iteration, len() and truth value -- but the Series are only built when a host caller really looks, and IRMM /
+    re-weighting take the device vectors as they are.  Millions of cross-allelic pairs then never cross PCIe."""
+
+    def __init__(self, rows, cols):
+        super().__init__([None, None])
+        self.dev = (rows, cols)
+        self._upper = None
+
+    def _series(self, i):
+        if list.__getitem__(self, i) is None:
+            list.__setitem__(self, i, pd.Series(D.to_host(self.dev[i])))
+        return list.__getitem__(self, i)
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self._series(k) for k in range(2)][i]
+        return self._series(i if i >= 0 else 2 + i)
+
+    def __iter__(self):
+        return iter((self._series(0), self._series(1)))
+
+    def __bool__(self):
+        return True
+
+    def __reduce__(self):
+        return (list, ([self._series(0), self._series(1)],))
+
+    def upper_symmetric(self):
+        """the pairs listed with r < c, mirrored (what `_upper_pairs_symmetric` builds on the host)"""
+        if self._upper is None:
+            r, c = self.dev
+            up = r < c
+            ru, cu = r[up], c[up]
+            self._upper = (torch.cat([ru, cu]), torch.cat([cu, ru])) if ru.numel() else False
+        return self._upper or None
+
+
 _PAIR_CACHE = []        # (list object 0, list object 1, device, result): the resolution search calls IRMM with the SAME pair lists
 
 
@@ -603,6 +643,9 @@ def _upper_pairs_device(P, dev):
     more than the clustering).  A caller that edits a list IN PLACE between calls must pass a new object."""
     if not P:
         return None
+    if isinstance(P, DevicePairs):
+        up = P.upper_symmetric()
+        return None if up is None else (up[0].to(dev), up[1].to(dev))
     p0, p1 = (P[0], P[1]) if isinstance(P, (list, tuple)) and len(P) == 2 else (P, None)
     for a, b, d, n, res in _PAIR_CACHE:
         if a is p0 and b is p1 and d == dev and n == len(p0):

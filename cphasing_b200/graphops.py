@@ -39,6 +39,10 @@ def clone_adjacency(a: D.DeviceCSR) -> D.DeviceCSR:
 def _pairs(P, dev):
     if P is None:
         return None, None, 0
+    if hasattr(P, "dev"):                                    # algorithms.hypergraph.DevicePairs: never leaves the device
+        r = P.dev[0].to(device=dev, dtype=torch.int64).contiguous()
+        c = P.dev[1].to(device=dev, dtype=torch.int64).contiguous()
+        return (r, c, int(r.numel())) if r.numel() else (None, None, 0)
     if isinstance(P, (tuple, list)) and len(P) == 2 and isinstance(P[0], torch.Tensor):      # already on the device
         r = P[0].to(device=dev, dtype=torch.int64).contiguous()
         c = P[1].to(device=dev, dtype=torch.int64).contiguous()

@@ -227,8 +227,10 @@ class HyperPartition:
         A = HyperGraph.clique_expansion_init(self.H, NW=self.get_normalize_weight() if self.normalize else None)
         kph = KPruneHyperGraph(self.alleletable, A, self.vertices_idx)
         kph.run()
-        al, wk = kph.allelic_pairs, kph.weak_pairs
-        return ([pd.Series(al[:, 0]), pd.Series(al[:, 1])], [pd.Series(wk[:, 0]), pd.Series(wk[:, 1])], kph)
+        from .algorithms.hypergraph import DevicePairs
+        al, wk = kph.device_pairs()
+        return (DevicePairs(al[:, 0].contiguous(), al[:, 1].contiguous()),
+                DevicePairs(wk[:, 0].contiguous(), wk[:, 1].contiguous()), kph)
 
     @property
     def prunetable(self):
@@ -255,10 +257,11 @@ class HyperPartition:
         self._kph = kph
         self._prunetable = None
         self._prune_pair_df, self._prune_src = None, kph
-        al, wk = kph.allelic_pairs, kph.weak_pairs
+        al, wk = kph.device_pairs()             # int64 [k, 2] on the device: the symmetric lists are built there too
         sw = wk[:, 0] != wk[:, 1]
-        self.P_allelic_idx = [pd.Series(np.concatenate([al[:, 0], al[:, 1]])), pd.Series(np.concatenate([al[:, 1], al[:, 0]]))]
-        self.P_weak_idx = [pd.Series(np.concatenate([wk[:, 0], wk[sw, 1]])), pd.Series(np.concatenate([wk[:, 1], wk[sw, 0]]))]
+        from .algorithms.hypergraph import DevicePairs
+        self.P_allelic_idx = DevicePairs(torch.cat([al[:, 0], al[:, 1]]), torch.cat([al[:, 1], al[:, 0]]))
+        self.P_weak_idx = DevicePairs(torch.cat([wk[:, 0], wk[sw, 1]]), torch.cat([wk[:, 1], wk[sw, 0]]))
 
     @property
     def prune_pair_df(self):
@@ -274,9 +277,18 @@ class HyperPartition:
         self._prune_pair_df, self._prune_src = value, None
 
     # -- hyperpartition.py:4012-4044
+    def _vertex_lengths(self):
+        """contig length per vertex index (0 where the size table has no entry); rebuilt when `vertices` is replaced"""
+        key = id(self.vertices)
+        if getattr(self, "_vlen_key", None) != key:
+            cs = self.contig_sizes
+            self._vlen = np.array([cs.get(v, 0) if hasattr(cs, "get") else cs[v] for v in self.vertices], dtype=np.float64)
+            self._vlen_key = key
+        return self._vlen
+
     def filter_cluster(self, verbose=1):
-        size_dict = self.vertices_idx_sizes
-        _K = [g for g in self.K if sum(size_dict.get(x, 0) for x in g) >= self.min_scaffold_length]
+        ln = self._vertex_lengths()
+        _K = [g for g in self.K if ln[np.fromiter(g, dtype=np.int64, count=len(g))].sum() >= self.min_scaffold_length]
         if verbose == 1:
             logger.info(f"Removed groups less than {self.min_scaffold_length} in length. (--min-scaffold-length)")
         logger.info(f"After filtering, {len(_K)} groups remain.")

@@ -78,31 +78,33 @@ def kprune_device(a: D.DeviceCSR, allele_pairs, max_alleles=1, want_scores=False
     return out + (bw[:a.nnz], ba[:a.nnz]) if want_scores else out
 
 
-def kprune_arrays(A, allele_pairs, max_alleles=1, first=None):
+def kprune_device_pairs(A, allele_pairs, max_alleles=1, first=None):
     """A: scipy matrix / DeviceBackedCSR; allele_pairs: (i, j) contig-index pairs in allele-table order.
-    Returns (allelic int64[ka, 2], weak int64[kw, 2]), rows sorted by (i, j), i < j -- plus the (c, c) rows the
-    reference's weak list carries (see `_self_pairs`).  No Python-level loop over the pairs."""
+    Returns (allelic int64[ka, 2], weak int64[kw, 2]) as DEVICE tensors, rows sorted by (i, j), i < j -- plus the (c, c)
+    rows the reference's weak list carries (see `_self_pairs`).  Nothing of the size of the pair lists touches the host."""
     a = graphops.upload_adjacency(A)
     flag, row_of = kprune_device(a, allele_pairs, max_alleles, first=first)
     cols = a.indices
 
     def pick(code):             # CSR order = sorted by (row, col) already
         ix = torch.nonzero(flag == code).flatten()
-        return np.stack([D.to_host(row_of[ix]).astype(np.int64), D.to_host(cols[ix]).astype(np.int64)], axis=1)
+        return torch.stack([row_of[ix].long(), cols[ix].long()], dim=1)
     allelic, weak = pick(1), pick(2)
     if max_alleles == 1:
         selfp = np.asarray(sorted(_self_pairs(a, allele_pairs, first)), dtype=np.int64).reshape(-1, 2)
         if selfp.size:
             n = max(a.n, 1)
-            pos = np.searchsorted(weak[:, 0] * n + weak[:, 1], selfp[:, 0] * n + selfp[:, 1])
-            out = np.empty((len(weak) + len(selfp), 2), dtype=np.int64)        # merge of two sorted lists
-            at = pos + np.arange(len(selfp))
-            keep = np.ones(len(out), dtype=bool)
-            keep[at] = False
-            out[at] = selfp
-            out[keep] = weak
-            weak = out
+            sp = D.to_dev(selfp, torch.int64, weak.device)
+            both = torch.cat([weak, sp])
+            order = torch.argsort(both[:, 0] * n + both[:, 1], stable=True)        # (c, c) keys never collide with i < j rows
+            weak = both[order]
     return allelic, weak
+
+
+def kprune_arrays(A, allele_pairs, max_alleles=1, first=None):
+    """host (numpy) form of `kprune_device_pairs`"""
+    al, wk = kprune_device_pairs(A, allele_pairs, max_alleles, first)
+    return D.to_host(al).reshape(-1, 2), D.to_host(wk).reshape(-1, 2)
 
 
 def kprune_pairs(A, allele_pairs, max_alleles=1):
@@ -178,18 +180,38 @@ class KPruneHyperGraph:
         self.A = A
         self.contig2idx = contig2idx
         self.max_alleles = max_alleles
-        self.allelic_pairs = np.zeros((0, 2), dtype=np.int64)      # array forms of the two lists
-        self.weak_pairs = np.zeros((0, 2), dtype=np.int64)
+        self._al_d = self._wk_d = None          # device forms of the two lists (int64 [k, 2]); host arrays on first use
+        self._al_h = np.zeros((0, 2), dtype=np.int64)
+        self._wk_h = np.zeros((0, 2), dtype=np.int64)
         self._lists = None
 
     def run(self):
         pairs = self.alleletable_idx[[1, 2]].to_numpy()
-        al, wk = kprune_arrays(self.A, pairs, self.max_alleles, first=self.allele_group_db)
-        logger.info(f"Removed {len(al)} allelic contacts.")
-        logger.info(f"Removed {len(wk)} weak contacts with allelic.")
-        self.allelic_pairs = np.concatenate([self.allelic_pairs, al])
-        self.weak_pairs = np.concatenate([self.weak_pairs, wk])
+        al, wk = kprune_device_pairs(self.A, pairs, self.max_alleles, first=self.allele_group_db)
+        logger.info(f"Removed {al.shape[0]} allelic contacts.")
+        logger.info(f"Removed {wk.shape[0]} weak contacts with allelic.")
+        if self._al_d is not None:              # a second run appends, like the reference's list.extend
+            al = torch.cat([self._al_d, al])
+            wk = torch.cat([self._wk_d, wk])
+        self._al_d, self._wk_d = al, wk
+        self._al_h = self._wk_h = None
         self._lists = None
+
+    @property
+    def allelic_pairs(self):                # int64 [ka, 2] on the host
+        if self._al_h is None:
+            self._al_h = D.to_host(self._al_d).reshape(-1, 2)
+        return self._al_h
+
+    @property
+    def weak_pairs(self):
+        if self._wk_h is None:
+            self._wk_h = D.to_host(self._wk_d).reshape(-1, 2)
+        return self._wk_h
+
+    def device_pairs(self):
+        """(allelic, weak) int64 [k, 2] device tensors, or (None, None) before run()"""
+        return self._al_d, self._wk_d
 
     def _as_lists(self):
         if self._lists is None:
