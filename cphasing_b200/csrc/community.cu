@@ -27,6 +27,7 @@
 #include <math.h>
 #include <string.h>
 #include <stdlib.h>
+#include <cooperative_groups.h>
 
 namespace {
 
@@ -161,13 +162,12 @@ __device__ __forceinline__ Best group_best(Best b, Best* sm) {
 
 // proposals for the vertices v = first + phase + i * n_phases (< last).  prop[v] = chosen community (or comm[v]).
 // `strip` = one private row of g.n int64 zeros per group (left zero again on exit).
+// one phase of proposals by this CTA's groups (a warp, or the whole CTA on dense level-0 graphs, per vertex)
 template <int G>
-__global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int phase, int n_phases, int first, int last,
-                                                                  const i32* __restrict__ comm, const i64* __restrict__ tot,
-                                                                  const i32* __restrict__ csize, const i64* __restrict__ k,
-                                                                  double gamma, double m2, i64* __restrict__ strip,
-                                                                  i32* __restrict__ prop) {
-    __shared__ Best sm_best[CM_WPB];
+__device__ __forceinline__ void propose_phase(const LGraph& g, int phase, int n_phases, int first, int last,
+                                              const i32* __restrict__ comm, const i64* __restrict__ tot,
+                                              const i32* __restrict__ csize, const i64* __restrict__ k, double gamma, double m2,
+                                              i64* __restrict__ strip, i32* __restrict__ prop, Best* sm_best) {
     constexpr int GPB = CM_THREADS / G;                       // groups per block
     const int n_groups = gridDim.x * GPB;
     const int gi = blockIdx.x * GPB + threadIdx.x / G;
@@ -213,6 +213,51 @@ __global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int 
         group_sync<G>();
         if (lane == 0) prop[v] = (best.c >= 0 && best.gain > stay) ? best.c : old;
     }
+}
+
+// proposals for the vertices v = first + phase + i * n_phases (< last).  prop[v] = chosen community (or comm[v]).
+// `strip` = one private row of g.n int64 zeros per group (left zero again on exit).
+template <int G>
+__global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int phase, int n_phases, int first, int last,
+                                                                  const i32* __restrict__ comm, const i64* __restrict__ tot,
+                                                                  const i32* __restrict__ csize, const i64* __restrict__ k,
+                                                                  double gamma, double m2, i64* __restrict__ strip,
+                                                                  i32* __restrict__ prop) {
+    __shared__ Best sm_best[CM_WPB];
+    propose_phase<G>(g, phase, n_phases, first, last, comm, tot, csize, k, gamma, m2, strip, prop, sm_best);
+}
+
+// A whole sweep in ONE cooperative launch: for every phase, proposals -> grid barrier -> commit -> grid barrier.  With the
+// adaptive phase count the first sweeps of a level run up to 128 phases of a few dozen vertices each; as separate launches
+// (propose + commit per phase) that is 256 launch latencies per sweep and most of a clustering's time.
+template <int G>
+__global__ void __launch_bounds__(CM_THREADS) sweep_kernel(LGraph g, int n_phases, i32* __restrict__ comm, i64* __restrict__ tot,
+                                                           i32* __restrict__ csize, const i64* __restrict__ k, double gamma,
+                                                           double m2, i64* __restrict__ strip, i32* __restrict__ prop,
+                                                           ull* __restrict__ moves) {
+    __shared__ Best sm_best[CM_WPB];
+    cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+    const i64 gt = (i64)blockIdx.x * blockDim.x + threadIdx.x, nt = (i64)gridDim.x * blockDim.x;
+    u32 moved = 0;
+    for (int ph = 0; ph < n_phases; ++ph) {
+        propose_phase<G>(g, ph, n_phases, 0, g.n, comm, tot, csize, k, gamma, m2, strip, prop, sm_best);
+        grid.sync();
+        for (i64 v = ph + gt * n_phases; v < g.n; v += nt * n_phases) {
+            const int p = prop[v], old = comm[v];
+            if (p != old) {
+                const i64 kv = k[v];
+                add64(&tot[p], kv);
+                add64(&tot[old], -kv);
+                atomicAdd(&csize[p], 1);
+                atomicSub(&csize[old], 1);
+                comm[v] = p;
+                ++moved;
+            }
+        }
+        grid.sync();
+    }
+    moved = warp_sum(moved);
+    if (lane_id() == 0 && moved) atomicAdd(moves, (ull)moved);
 }
 
 __global__ void move_commit_kernel(int phase, int n_phases, int first, int last, i32* __restrict__ comm,
@@ -578,6 +623,7 @@ struct State {
     i64 nnz0;
     double gamma, m2;
     int n_phases, max_sweeps, pmax, pdiv;
+    int coop_blocks;     // > 0: co-resident CTAs for the one-launch sweep (sweep_kernel); 0: one launch per phase
     int blocks;          // persistent grid of the warp-per-vertex kernels; strip has blocks * CM_WPB rows of n0
     Scalars* sc;
     i64 *w0, *gw[2], *gbeg[2], *gend[2];
@@ -688,6 +734,28 @@ int local_moving(State& S, const LGraph& g, bool* moved) {
         }
         if (P > g.n) P = g.n > 0 ? g.n : 1;
         CUDA_TRY(cudaMemsetAsync(&S.sc->moves, 0, sizeof(ull), S.st));
+        if (S.coop_blocks > 0) {
+            // one cooperative launch for the whole sweep; the grid is what is co-resident and what the strips allow
+            const int per = cta_mode ? 1 : CM_WPB;
+            int cnt = (g.n + P - 1) / P;
+            int blocks = (int)ceil_div((size_t)cnt, (size_t)per);
+            if (blocks > S.coop_blocks) blocks = S.coop_blocks;
+            if (blocks < 1) blocks = 1;
+            LGraph gg = g;
+            int Pn = P;
+            i32* comm = S.comm;
+            i64* tot = S.tot;
+            i32* csize = S.csize;
+            const i64* kk = S.k;
+            double gamma = S.gamma, m2 = S.m2;
+            i64* strip = S.strip;
+            i32* prop = S.prop;
+            ull* mv = &S.sc->moves;
+            void* args[] = {&gg, &Pn, &comm, &tot, &csize, &kk, &gamma, &m2, &strip, &prop, &mv};
+            const void* fn = cta_mode ? (const void*)sweep_kernel<CM_THREADS> : (const void*)sweep_kernel<32>;
+            CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(CM_THREADS), args, 0, S.st));
+            KERNEL_CHECK();
+        } else
         for (int ph = 0; ph < P; ++ph) {
             int cnt = (g.n - ph + P - 1) / P;
             if (cnt <= 0) continue;
@@ -887,6 +955,22 @@ int cph_community(const int64_t* indptr, const int32_t* indices, const float* da
     TRY(carve(S, ar));
     WS_QUERY_RETURN(ar);
     ARG_CHECK(indptr && membership && (nnz == 0 || (indices && (data32 || data64))));
+    {   // co-resident grid of the one-launch sweep (CPH_COMMUNITY_SWEEP=launch: one launch per phase, for A/B timing)
+        static int coop_max = -1;
+        if (coop_max < 0) {
+            int dev = 0, sms = 0, ok = 0, nb_cta = 0, nb_warp = 0;
+            CUDA_TRY(cudaGetDevice(&dev));
+            CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            CUDA_TRY(cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb_cta, sweep_kernel<CM_THREADS>, CM_THREADS, 0));
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb_warp, sweep_kernel<32>, CM_THREADS, 0));
+            int nb = nb_cta < nb_warp ? nb_cta : nb_warp;
+            if (nb > 2) nb = 2;                 // a grid barrier costs more the more CTAs take part
+            coop_max = ok ? sms * nb : 0;
+        }
+        const char* e = getenv("CPH_COMMUNITY_SWEEP");
+        S.coop_blocks = (e && strcmp(e, "launch") == 0) ? 0 : (coop_max < S.blocks ? coop_max : S.blocks);
+    }
     if (n_iterations < 1) n_iterations = 1;
     CUDA_TRY(cudaMemsetAsync(S.strip, 0, sizeof(i64) * (size_t)S.blocks * CM_WPB * n, S.st));
 
