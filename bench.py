@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 # concatemer-column shards; N=1 is exactly the named config).  `--workload D` runs config D's genome (20k contigs) with
 # 62.5M concatemers per GPU (the named 500M at N=8); its numbers are recorded in profiles/ and DESIGN.md.
 # dram bytes per launch of the dominant kernel from the committed ncu --set full capture, keyed by (workload, m per GPU)
-NCU_TRAFFIC = {("C", 50_000_000): 2721182000 + 2306597000}      # profiles/r1j_ncu_full_top3.txt
+NCU_TRAFFIC = {("C", 50_000_000): 2723423000 + 2316372000}      # profiles/r2h_ncu_full_C.txt (porec_tile_kernel<1, 8>)
 PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight=2.0)   # cphasing/_config.py:38-45
 
 
@@ -36,7 +36,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default=None, help="A|B|C|D|E (default C; every GPU takes a full-size shard, D: 1/8 of its 500M)")
+    ap.add_argument("--workload", default=None, help="A|B|C|D|E (default C; every GPU takes a full-size shard, D and E: 1/8 of the named size)")
     ap.add_argument("--m", type=int, default=None, help="override the number of concatemers per GPU")
     ap.add_argument("--cpu-sample", type=int, default=10_000_000, help="concatemers in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -52,8 +52,8 @@ def workload(args):
     from cphasing_b200 import synth
     name = args.workload or "C"
     cfg = dict(synth.CONFIGS[name])
-    if name == "D":
-        cfg["m"] = cfg["m"] // 8                 # per GPU: 62.5M (the named 500M at 8 GPUs)
+    if name in ("D", "E"):
+        cfg["m"] = cfg["m"] // 8                 # per GPU: D 62.5M (the named 500M at 8 GPUs), E 25M (200M at 8 GPUs)
     elif args.gpus > 1:
         pass                                     # other shapes: every GPU takes a full-size shard
     if args.m:
