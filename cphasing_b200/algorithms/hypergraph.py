@@ -558,9 +558,50 @@ def extract_incidence_matrix2(mat, idx):
         h = upload_incidence(mat)
     idx = np.asarray(idx, dtype=np.int64)
     sub = D.sub_incidence(h, idx)
-    kept = _kept_columns(h, idx)
-    removed = np.setdiff1d(np.arange(h.n_cols), kept, assume_unique=True) if len(kept) < h.n_cols else np.array([])
-    return wrap_incidence(sub), removed, kept
+    # the reference's callers on this path drop the two index arrays (`H, _, _ = ...`, hyperpartition.py:1009, 1761):
+    # they are computed when somebody looks (they need the CSR view of the parent and nnz-sized passes)
+    box = {}
+
+    def kept():
+        if "k" not in box:
+            box["k"] = _kept_columns(h, idx)
+        return box["k"]
+
+    def removed():
+        k = kept()
+        return np.setdiff1d(np.arange(h.n_cols), k, assume_unique=True) if len(k) < h.n_cols else np.array([])
+    return wrap_incidence(sub), _LazyArray(removed), _LazyArray(kept)
+
+
+class _LazyArray:
+    """a numpy array computed on first use (len, indexing, iteration, np.asarray, attribute access)"""
+
+    def __init__(self, provider):
+        self._p, self._a = provider, None
+
+    def _arr(self):
+        if self._a is None:
+            self._a = np.asarray(self._p())
+            self._p = None
+        return self._a
+
+    def __array__(self, dtype=None, copy=None):
+        a = self._arr()
+        return a if dtype is None else a.astype(dtype, copy=False)
+
+    def __len__(self):
+        return len(self._arr())
+
+    def __getitem__(self, k):
+        return self._arr()[k]
+
+    def __iter__(self):
+        return iter(self._arr())
+
+    def __getattr__(self, name):
+        if name.startswith("_"):
+            raise AttributeError(name)
+        return getattr(self._arr(), name)
 
 
 def _kept_columns(h: D.DeviceH, idx):

@@ -801,6 +801,71 @@ class HyperPartition:
             iter_round += 1
         return K
 
+    # -- hyperpartition.py:3426-3575: unanchored contigs join the group they touch most.  The group scores S = A M of ALL
+    #    unanchored contigs come from the device in one call (cph_group_sums); a rescued contig changes the scores of the
+    #    ones after it (it joins K[best] at once, :3563), which is one sparse row of A added to column `best`.
+    @staticmethod
+    def _rescue_static(K, H, vertices_idx_sizes, prune_pair_df=None, min_weight=1.0, rescue_threshold=0.1, min_contacts=2,
+                       ambiguity_threshold=0.85, allelic_similarity=0.99, verbose=False):
+        if not K:
+            return K, 0
+        n = H.shape[0]
+        anchored = np.zeros(n, dtype=bool)
+        for grp in K:
+            anchored[np.asarray(list(grp), dtype=np.int64)] = True
+        un = np.flatnonzero(~anchored)
+        if len(un) == 0:
+            return K, 0
+        A = HyperGraph.clique_expansion_init(H, min_weight=min_weight)
+        constraints = defaultdict(set)
+        if prune_pair_df is not None:
+            try:
+                rows = prune_pair_df[(prune_pair_df['type'] == 0) & (prune_pair_df['similarity'] >= allelic_similarity)]
+                for c1, c2 in rows[['contig1', 'contig2']].values:
+                    constraints[int(c1)].add(int(c2))
+                    constraints[int(c2)].add(int(c1))
+            except KeyError:
+                if verbose:
+                    logger.warning("prune_pair_df format error in rescue.")
+        if isinstance(vertices_idx_sizes, dict):
+            ln = np.array([vertices_idx_sizes.get(int(i), 0) for i in un], dtype=np.float64)
+        else:
+            col = vertices_idx_sizes['length'] if hasattr(vertices_idx_sizes, 'columns') else vertices_idx_sizes
+            ln = col.reindex(un).fillna(0).to_numpy(dtype=np.float64)
+        un = un[np.argsort(-ln, kind="stable")]                        # longest first (list.sort(reverse=True) is stable)
+        S, _ = group_sums(A, K, want_S=True)
+        S = np.array(S[un], dtype=np.float64)                           # scores of the unanchored contigs only
+        pos = {int(c): t for t, c in enumerate(un)}
+        Ah = None
+        rescued = 0
+        for t, c in enumerate(un):
+            sc = S[t]
+            total = sc.sum()
+            if total <= 1e-6:
+                continue
+            best = int(np.argmax(sc))
+            if sc[best] < min_contacts or sc[best] / total < rescue_threshold:
+                continue
+            if len(sc) > 1:
+                second = np.partition(sc, -2)[-2]
+                if second > 0 and second / sc[best] > ambiguity_threshold:
+                    continue
+            c = int(c)
+            if c in constraints and not constraints[c].isdisjoint(K[best]):
+                continue
+            K[best].append(c)
+            rescued += 1
+            if Ah is None:
+                Ah = csr_matrix(A)
+            lo, hi = Ah.indptr[c], Ah.indptr[c + 1]                    # A is symmetric: column c = row c
+            for j, w in zip(Ah.indices[lo:hi], Ah.data[lo:hi]):
+                tj = pos.get(int(j))
+                if tj is not None and tj > t:
+                    S[tj, best] += w
+        if verbose and rescued > 0:
+            logger.info(f"Statically rescued {rescued} contigs.")
+        return K, rescued
+
     # -- hyperpartition.py:2860-2968: S = A M on the device, decisions on the host as in the reference
     def recluster_by_linkage(self, A=None, min_ratio=1.2, iter_count=1):
         if A is None:

@@ -147,3 +147,38 @@ def test_merge_split_matches_reference():
         ra, rb = a.merge_split(secondary=secondary), b.merge_split(secondary=secondary)
         assert ra[0] == rb[0] and ra[1] == rb[1] and ra[2] == rb[2]
         assert list(a.inc_chr_idx) == list(b.inc_chr_idx)
+
+
+@pytest.mark.gpu
+def test_rescue_static_matches_reference(setup):
+    """hyperpartition.py:3426-3575 on the same H: the reference's own static method (scipy H and A) against the drop-in's
+    (device A = H W H^T, S = A M from cph_group_sums) -- same groups after the rescue, same number of rescued contigs,
+    with an allelic constraint table in play."""
+    rhp, mgd = reference_module()
+    import cphasing.algorithms.hypergraph as rah
+    from scipy.sparse import csr_matrix
+    from cphasing_b200.algorithms import hypergraph as ah
+    from cphasing_b200.hyperpartition import HyperPartition
+    g, edges, sizes, ptf, wd, _ = setup
+    HG = ah.HyperGraph(edges, min_quality=1)
+    H = HG.incidence_matrix(min_contacts=5)
+    n = H.shape[0]
+    rng = np.random.default_rng(3)
+    truth = np.array([g.group[g.contig_idx[c]] for c in HG.nodes])
+    # groups = the planted ones with a third of the contigs left unanchored
+    loose = rng.random(n) < 0.33
+    K0 = [np.where((truth == t) & ~loose)[0].tolist() for t in np.unique(truth)]
+    K0 = [k for k in K0 if k]
+    un = np.where(loose)[0]
+    # constraints: some unanchored contigs may not join the group of an anchored "allele"
+    c1 = un[: len(un) // 4]
+    c2 = np.array([K0[int(truth[c]) % len(K0)][0] for c in c1])
+    ppd = pd.DataFrame({"contig1": c1, "contig2": c2, "mz1": 0, "mz2": 0, "mzShared": 0, "similarity": 0.995, "type": 0})
+    sizes_idx = {i: float(g.contigsizes[c]) for i, c in enumerate(HG.nodes)}
+    Hs = csr_matrix(H)
+    with contextlib.redirect_stderr(io.StringIO()):
+        Kr, nr = rhp.HyperPartition._rescue_static([list(k) for k in K0], Hs, dict(sizes_idx), ppd, min_weight=1.0)
+    Kd, nd = HyperPartition._rescue_static([list(k) for k in K0], H, dict(sizes_idx), ppd, min_weight=1.0)
+    assert nr == nd and nr > 20
+    assert [list(map(int, k)) for k in Kr] == [list(map(int, k)) for k in Kd]
+    assert any(set(map(int, c1)) - set(x for k in Kd for x in k))        # the constraints did hold something back
