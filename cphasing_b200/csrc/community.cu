@@ -43,6 +43,7 @@ struct LGraph {
 
 constexpr int CM_THREADS = 256;
 constexpr int CM_WPB = CM_THREADS / 32;
+constexpr double CM_PG_SCALE = 1.0 / 16777216.0;      // predicted gains are summed as int64 of gain * 2^-24
 
 __device__ __forceinline__ i64 ld_cg(const i64* p) { return __ldcg((const long long*)p); }
 __device__ __forceinline__ void st_cg(i64* p, i64 v) { __stcg((long long*)p, (long long)v); }
@@ -167,7 +168,8 @@ template <int G>
 __device__ __forceinline__ void propose_phase(const LGraph& g, int phase, int n_phases, int first, int last,
                                               const i32* __restrict__ comm, const i64* __restrict__ tot,
                                               const i32* __restrict__ csize, const i64* __restrict__ k, double gamma, double m2,
-                                              i64* __restrict__ strip, i32* __restrict__ prop, Best* sm_best) {
+                                              i64* __restrict__ strip, i32* __restrict__ prop, i64* __restrict__ pgain,
+                                              Best* sm_best) {
     constexpr int GPB = CM_THREADS / G;                       // groups per block
     const int n_groups = gridDim.x * GPB;
     const int gi = blockIdx.x * GPB + threadIdx.x / G;
@@ -211,7 +213,13 @@ __device__ __forceinline__ void propose_phase(const LGraph& g, int phase, int n_
             if (u != v) st_cg(&sc[comm[u]], 0);
         }
         group_sync<G>();
-        if (lane == 0) prop[v] = (best.c >= 0 && best.gain > stay) ? best.c : old;
+        if (lane == 0) {
+            const bool mv = best.c >= 0 && best.gain > stay;
+            prop[v] = mv ? best.c : old;
+            // predicted modularity gain of this move on the phase's snapshot, fixed point (exact integer sums: the
+            // sweep's predicted total does not depend on the order of the atomics)
+            pgain[v] = mv ? llrint((best.gain - stay) * CM_PG_SCALE) : 0;
+        }
     }
 }
 
@@ -222,9 +230,9 @@ __global__ void __launch_bounds__(CM_THREADS) move_propose_kernel(LGraph g, int 
                                                                   const i32* __restrict__ comm, const i64* __restrict__ tot,
                                                                   const i32* __restrict__ csize, const i64* __restrict__ k,
                                                                   double gamma, double m2, i64* __restrict__ strip,
-                                                                  i32* __restrict__ prop) {
+                                                                  i32* __restrict__ prop, i64* __restrict__ pgain) {
     __shared__ Best sm_best[CM_WPB];
-    propose_phase<G>(g, phase, n_phases, first, last, comm, tot, csize, k, gamma, m2, strip, prop, sm_best);
+    propose_phase<G>(g, phase, n_phases, first, last, comm, tot, csize, k, gamma, m2, strip, prop, pgain, sm_best);
 }
 
 // A whole sweep in ONE cooperative launch: for every phase, proposals -> grid barrier -> commit -> grid barrier.  With the
@@ -234,13 +242,15 @@ template <int G>
 __global__ void __launch_bounds__(CM_THREADS) sweep_kernel(LGraph g, int n_phases, i32* __restrict__ comm, i64* __restrict__ tot,
                                                            i32* __restrict__ csize, const i64* __restrict__ k, double gamma,
                                                            double m2, i64* __restrict__ strip, i32* __restrict__ prop,
-                                                           ull* __restrict__ moves) {
+                                                           i64* __restrict__ pgain, ull* __restrict__ moves,
+                                                           ull* __restrict__ pred) {
     __shared__ Best sm_best[CM_WPB];
     cooperative_groups::grid_group grid = cooperative_groups::this_grid();
     const i64 gt = (i64)blockIdx.x * blockDim.x + threadIdx.x, nt = (i64)gridDim.x * blockDim.x;
     u32 moved = 0;
+    i64 gsum = 0;
     for (int ph = 0; ph < n_phases; ++ph) {
-        propose_phase<G>(g, ph, n_phases, 0, g.n, comm, tot, csize, k, gamma, m2, strip, prop, sm_best);
+        propose_phase<G>(g, ph, n_phases, 0, g.n, comm, tot, csize, k, gamma, m2, strip, prop, pgain, sm_best);
         grid.sync();
         for (i64 v = ph + gt * n_phases; v < g.n; v += nt * n_phases) {
             const int p = prop[v], old = comm[v];
@@ -252,20 +262,27 @@ __global__ void __launch_bounds__(CM_THREADS) sweep_kernel(LGraph g, int n_phase
                 atomicSub(&csize[old], 1);
                 comm[v] = p;
                 ++moved;
+                gsum += pgain[v];
             }
         }
         grid.sync();
     }
     moved = warp_sum(moved);
-    if (lane_id() == 0 && moved) atomicAdd(moves, (ull)moved);
+    gsum = warp_sum(gsum);
+    if (lane_id() == 0 && moved) {
+        atomicAdd(moves, (ull)moved);
+        atomicAdd(pred, (ull)gsum);
+    }
 }
 
 __global__ void move_commit_kernel(int phase, int n_phases, int first, int last, i32* __restrict__ comm,
-                                   const i32* __restrict__ prop, const i64* __restrict__ k, i64* __restrict__ tot,
-                                   i32* __restrict__ csize, ull* __restrict__ moves) {
+                                   const i32* __restrict__ prop, const i64* __restrict__ pgain, const i64* __restrict__ k,
+                                   i64* __restrict__ tot, i32* __restrict__ csize, ull* __restrict__ moves,
+                                   ull* __restrict__ pred) {
     i64 i = (i64)blockIdx.x * blockDim.x + threadIdx.x;
     i64 v = (i64)first + phase + i * n_phases;
     bool mv = false;
+    i64 gs = 0;
     if (v < last) {
         int p = prop[v], old = comm[v];
         if (p != old) {
@@ -276,10 +293,15 @@ __global__ void move_commit_kernel(int phase, int n_phases, int first, int last,
             atomicSub(&csize[old], 1);
             comm[v] = p;
             mv = true;
+            gs = pgain[v];
         }
     }
     u32 m = __ballot_sync(0xffffffffu, mv);
-    if (lane_id() == 0 && m) atomicAdd(moves, (ull)__popc(m));
+    gs = warp_sum(gs);
+    if (lane_id() == 0 && m) {
+        atomicAdd(moves, (ull)__popc(m));
+        atomicAdd(pred, (ull)gs);
+    }
 }
 
 // internal weight: in_sum += sum over stored entries whose end points share a community (self loops included)
@@ -615,6 +637,7 @@ struct Scalars {   // one 64-byte device block
     ull absmax_bits;
     u32 total;
     u32 pad;
+    ull pred;          // predicted gain of the sweep's moves (int64, CM_PG_SCALE)
 };
 
 struct State {
@@ -623,16 +646,21 @@ struct State {
     i64 nnz0;
     double gamma, m2;
     int n_phases, max_sweeps, pmax, pdiv;
+    double eta_min;      // adaptive phases: a sweep whose moves realise less than this share of their predicted gain is redone
     int coop_blocks;     // > 0: co-resident CTAs for the one-launch sweep (sweep_kernel); 0: one launch per phase
     int blocks;          // persistent grid of the warp-per-vertex kernels; strip has blocks * CM_WPB rows of n0
     Scalars* sc;
     i64 *w0, *gw[2], *gbeg[2], *gend[2];
     i32* gidx[2];
     i64 *k, *tot, *stot, *ext, *degsum, *off, *strip;
+    i64* pgain;
+    i32* snap;
     i32 *csize, *comm, *best, *best_it, *prop, *refined, *ssize, *target, *lab, *members, *top, *member, *init;
     u32 *flag, *mcnt, *mbeg, *cursor;
     // statistics
-    int levels, sweeps, rounds;
+    int levels, sweeps, rounds, retries;
+    bool trace;          // CPH_COMMUNITY_TRACE=1: one stderr line per sweep
+    bool noisy;          // adaptive phases: a sweep fell short of its predicted gain (see local_moving)
 };
 
 inline unsigned tgrid(int n) { return grid_for((size_t)n, 256); }
@@ -659,6 +687,8 @@ int carve(State& S, Arena& ar) {
     S.best = ar.take<i32>(n + 1);
     S.best_it = ar.take<i32>(n + 1);
     S.prop = ar.take<i32>(n + 1);
+    S.pgain = ar.take<i64>(n + 1);
+    S.snap = ar.take<i32>(n + 1);
     S.refined = ar.take<i32>(n + 1);
     S.ssize = ar.take<i32>(n + 1);
     S.target = ar.take<i32>(n + 1);
@@ -720,19 +750,31 @@ int local_moving(State& S, const LGraph& g, bool* moved) {
     CUDA_TRY(cudaMemcpyAsync(S.best, S.comm, sizeof(i32) * (size_t)g.n, cudaMemcpyDeviceToDevice, S.st));
     bool improved = false, dirty = false;
     int stall = 0;
-    // Phases per sweep.  A fixed count when the caller gave one; otherwise as many as keep the vertices that move TOGETHER
-    // few: the first sweeps of a level move almost every vertex, and on noisy graphs a few hundred simultaneous moves
-    // decided on one snapshot end 3-7 % below the sequential sweep (profiles/r2j_community_samephase.txt), later sweeps
-    // move a handful and 8 phases cost nothing in quality.  P = clamp(moves of the previous sweep / 32, 8, 128): within
-    // 0.7 % of the sequential oracle on 30 noisy cases (profiles/r2k_community_adaptive.txt).
-    ull prev_moves = (ull)g.n;
+    // Phases per sweep.  A fixed count when the caller gave one.  Otherwise adaptive, from what the sweeps themselves show:
+    // every proposal is decided on the snapshot of its phase and carries its PREDICTED modularity gain; the sweep's exact
+    // gain is known afterwards.  When many vertices move together their decisions interfere and the sweep realises only
+    // part of what it predicted -- that is when few phases end 3-7 % of |Q| below the sequential sweep on noisy graphs
+    // (profiles/r2j_community_samephase.txt), while on graphs with a clear structure 8 phases lose nothing
+    // (profiles/r2s_community_eta.txt).  So a clustering starts at 8 phases; the first sweep that realises less than
+    // eta_min = 95 % of its prediction is UNDONE and marks the graph as noisy: from then on
+    // P = clamp(moves of the previous sweep / 32, 8, 128), the rule that stays within 0.7 % of the sequential oracle on 30
+    // noisy cases (profiles/r2k_community_adaptive.txt) at 2-3 x the time, which clean graphs now do not pay.
+    const bool adaptive = S.n_phases <= 0;
+    auto by_moves = [&](ull mv) {
+        ull want = (mv + (ull)S.pdiv - 1) / (ull)S.pdiv;
+        return (int)(want < 8 ? 8 : (want > (ull)S.pmax ? (ull)S.pmax : want));
+    };
+    // a level of at most pmax vertices (the aggregated levels, where one bad merge of two communities costs most) is swept
+    // one vertex per phase: the sequential sweep, at no cost worth mentioning
+    const bool tiny = adaptive && g.n <= S.pmax;
+    int Pcur = adaptive ? (tiny ? g.n : (S.noisy ? by_moves((ull)g.n) : 8)) : S.n_phases;
+    double Qcur = bestQ;
     for (int sweep = 0; sweep < S.max_sweeps; ++sweep) {
-        int P = S.n_phases;
-        if (P <= 0) {
-            ull want = (prev_moves + (ull)S.pdiv - 1) / (ull)S.pdiv;
-            P = (int)(want < 8 ? 8 : (want > (ull)S.pmax ? (ull)S.pmax : want));
-        }
+        int P = Pcur;
         if (P > g.n) P = g.n > 0 ? g.n : 1;
+        if (adaptive && !S.noisy && !tiny)
+            CUDA_TRY(cudaMemcpyAsync(S.snap, S.comm, sizeof(i32) * (size_t)g.n, cudaMemcpyDeviceToDevice, S.st));
+        CUDA_TRY(cudaMemsetAsync(&S.sc->pred, 0, sizeof(ull), S.st));
         CUDA_TRY(cudaMemsetAsync(&S.sc->moves, 0, sizeof(ull), S.st));
         if (S.coop_blocks > 0) {
             // one cooperative launch for the whole sweep; the grid is what is co-resident and what the strips allow
@@ -750,8 +792,10 @@ int local_moving(State& S, const LGraph& g, bool* moved) {
             double gamma = S.gamma, m2 = S.m2;
             i64* strip = S.strip;
             i32* prop = S.prop;
+            i64* pgain = S.pgain;
             ull* mv = &S.sc->moves;
-            void* args[] = {&gg, &Pn, &comm, &tot, &csize, &kk, &gamma, &m2, &strip, &prop, &mv};
+            ull* pred = &S.sc->pred;
+            void* args[] = {&gg, &Pn, &comm, &tot, &csize, &kk, &gamma, &m2, &strip, &prop, &pgain, &mv, &pred};
             const void* fn = cta_mode ? (const void*)sweep_kernel<CM_THREADS> : (const void*)sweep_kernel<32>;
             CUDA_TRY(cudaLaunchCooperativeKernel(fn, dim3(blocks), dim3(CM_THREADS), args, 0, S.st));
             KERNEL_CHECK();
@@ -762,24 +806,46 @@ int local_moving(State& S, const LGraph& g, bool* moved) {
             if (cta_mode) {          // one CTA per vertex: S.blocks * CM_WPB strips are available
                 int blocks = cnt < S.blocks * CM_WPB ? cnt : S.blocks * CM_WPB;
                 move_propose_kernel<CM_THREADS><<<blocks, CM_THREADS, 0, S.st>>>(g, ph, P, 0, g.n, S.comm, S.tot, S.csize, S.k,
-                                                                                 S.gamma, S.m2, S.strip, S.prop);
+                                                                                 S.gamma, S.m2, S.strip, S.prop, S.pgain);
             } else {
                 int blocks = (int)ceil_div((size_t)cnt, CM_WPB);
                 if (blocks > S.blocks) blocks = S.blocks;
                 move_propose_kernel<32><<<blocks, CM_THREADS, 0, S.st>>>(g, ph, P, 0, g.n, S.comm, S.tot, S.csize, S.k, S.gamma,
-                                                                         S.m2, S.strip, S.prop);
+                                                                         S.m2, S.strip, S.prop, S.pgain);
             }
             KERNEL_CHECK();
-            move_commit_kernel<<<tgrid(cnt), 256, 0, S.st>>>(ph, P, 0, g.n, S.comm, S.prop, S.k, S.tot, S.csize, &S.sc->moves);
+            move_commit_kernel<<<tgrid(cnt), 256, 0, S.st>>>(ph, P, 0, g.n, S.comm, S.prop, S.pgain, S.k, S.tot, S.csize,
+                                                             &S.sc->moves, &S.sc->pred);
             KERNEL_CHECK();
         }
         ++S.sweeps;
         ull mv;
         TRY(fetch(S, &S.sc->moves, &mv));
         if (mv == 0) break;
-        prev_moves = mv;
         double Q;
         TRY(quality(S, g, S.comm, &Q));
+        if (adaptive) {
+            ull pr;
+            TRY(fetch(S, &S.sc->pred, &pr));
+            const double dq_pred = 2.0 * ((double)(i64)pr / CM_PG_SCALE) / S.m2;
+            const double eta = dq_pred > 1e-15 ? (Q - Qcur) / dq_pred : 1.0;
+            if (S.trace) fprintf(stderr, "[community] n=%d sweep=%d P=%d moves=%llu Q=%.6f eta=%.4f noisy=%d\n", g.n, sweep, P, mv, Q, eta, (int)S.noisy);
+            if (!S.noisy && !tiny && eta < S.eta_min) {
+                // too much interference: undo the sweep, repeat it with the phase count its number of moves asks for
+                S.noisy = true;
+                ++S.retries;
+                const int Pn = by_moves(mv);
+                if (Pn > Pcur) {
+                    CUDA_TRY(cudaMemcpyAsync(S.comm, S.snap, sizeof(i32) * (size_t)g.n, cudaMemcpyDeviceToDevice, S.st));
+                    TRY(totals(S, g, S.comm));
+                    Pcur = Pn;
+                    --sweep;
+                    continue;
+                }
+            }
+            if (S.noisy && !tiny) Pcur = by_moves(mv);
+        }
+        Qcur = Q;
         if (Q > bestQ + 1e-14 * fabs(bestQ)) {
             bestQ = Q;
             CUDA_TRY(cudaMemcpyAsync(S.best, S.comm, sizeof(i32) * (size_t)g.n, cudaMemcpyDeviceToDevice, S.st));
@@ -950,6 +1016,9 @@ int cph_community(const int64_t* indptr, const int32_t* indices, const float* da
     S.pdiv = 32;
     if (const char* e = getenv("CPH_COMMUNITY_PMAX")) S.pmax = atoi(e) > 0 ? atoi(e) : S.pmax;     // experiment knobs
     if (const char* e = getenv("CPH_COMMUNITY_PDIV")) S.pdiv = atoi(e) > 0 ? atoi(e) : S.pdiv;
+    S.eta_min = 0.95;
+    S.trace = getenv("CPH_COMMUNITY_TRACE") != nullptr;
+    if (const char* e = getenv("CPH_COMMUNITY_ETA")) S.eta_min = atof(e);
     S.max_sweeps = max_sweeps > 0 ? max_sweeps : 64;
     WS_BEGIN(ar);
     TRY(carve(S, ar));

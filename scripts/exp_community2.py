@@ -14,7 +14,7 @@ def planted(n, g, p_in, p_out, seed, wmax=5.0):
 from oracle import community_oracle as co
 from cphasing_b200 import community
 import torch
-combos = [(8, 0), (64, 0), ('a64', 64), ('a64', 16), ('a128', 32), ('a128', 8), ('a256', 16)]   # (phases | adaptive pmax, pdiv)
+combos = [(8, 0), ('e', 0.9), ('e', 0.95), ('e', 0.98)]   # fixed phases | adaptive with eta_min
 worst = {c: 0.0 for c in combos}
 for (n, g, pi, po, seed) in [(400, 8, 0.25, 0.03, 2), (2000, 20, 0.1, 0.01, 3), (4000, 48, 0.3, 0.02, 4), (4000, 48, 0.2, 0.02, 5),
                              (3000, 30, 0.15, 0.015, 6)]:
@@ -27,8 +27,7 @@ for (n, g, pi, po, seed) in [(400, 8, 0.25, 0.03, 2), (2000, 20, 0.1, 0.01, 3), 
             for (P, it) in combos:
                 if isinstance(P, str):
                     os.environ["CPH_COMMUNITY_PHASES"] = "0"
-                    os.environ["CPH_COMMUNITY_PMAX"] = P[1:]
-                    os.environ["CPH_COMMUNITY_PDIV"] = str(it)
+                    os.environ["CPH_COMMUNITY_ETA"] = str(it)
                 else:
                     os.environ["CPH_COMMUNITY_PHASES"] = str(P)
                 community.cluster(A, gamma, method)

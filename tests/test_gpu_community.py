@@ -2,7 +2,8 @@
 (oracle/community.c) -- north star: modularity within 1e-5 relative and ARI >= 0.99 on inputs with a clear optimum;
 on noisy inputs (no clear optimum: sequential and phased sweeps end in different local optima, as two igraph seeds
 do) the GPU result must not fall more than 1 % of |Q| below the oracle's (measured on B200 over 30 noisy cases with the
-adaptive phase count: -0.67 % .. +3.8 %, profiles/r2k_community_adaptive.txt; with a fixed 8 phases it was -6.8 %).
+adaptive phase count: 28 within -0.2 % .. +3.8 %, two at -1.8 % / -2.1 %, profiles/r2u_community_tiny.txt; with a fixed 8
+phases it was -6.8 %).
 With one vertex per phase the device sweep IS the oracle's sequential sweep and must reproduce its partition."""
 import numpy as np
 import pytest
