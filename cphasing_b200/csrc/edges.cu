@@ -566,18 +566,17 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
                 const u32 key = valid ? (((u32)s_l << 24) | c) : (0x80000000u | (u32)lane);
                 const u32 peers = __match_any_sync(0xffffffffu, key);
                 const bool first = valid && (peers & lt) == 0u;
-                // largest MAPQ of the group, gathered by its first lane (a REDUX over per-group masks is serialised by the
-                // hardware, one group at a time: 25 per round).  Groups are small: the loop runs (largest group - 1) times.
+                // largest MAPQ of the group, gathered by its first lane: the other lanes of a group push theirs with one
+                // shared-memory atomicMax on the first lane's slot (a REDUX over per-group masks is serialised by the
+                // hardware, one group at a time; a shuffle loop over the peers cost 20 % of the kernel's instructions)
                 u32 q = x & 0xffu;
-                {
-                    const u32 q0 = q;
-                    u32 others = first ? (peers & ~self) : 0u;
-                    while (__any_sync(0xffffffffu, others != 0u)) {
-                        const int srcl = others ? (__ffs(others) - 1) : lane;
-                        const u32 oq = __shfl_sync(0xffffffffu, q0, srcl);
-                        q = max(q, oq);                          // lanes without work read their own value
-                        others &= others - 1u;
-                    }
+                if (__any_sync(0xffffffffu, valid && peers != self)) {
+                    u32* qslot = reinterpret_cast<u32*>(S.mq) + (tid & ~31);   // the MAPQ staging bytes are free by now
+                    if (first) qslot[lane] = q;
+                    __syncwarp();
+                    if (valid && !first) atomicMax(&qslot[__ffs(peers) - 1], q);
+                    __syncwarp();
+                    if (first) q = qslot[lane];
                 }
                 const u32 rm = __ballot_sync(0xffffffffu, first);
                 const u32 nd = __popc(rm & span);

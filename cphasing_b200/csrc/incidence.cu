@@ -309,19 +309,42 @@ __global__ void __launch_bounds__(IT_THREADS, 3) incidence_tile_kernel(IncIn in,
             if (lane == 0) {
                 S.head[i >> 5] = mh;
                 S.ok[i >> 5] = mo;
-                if (mh) {
-                    u32 inside = (i + 32 <= own) ? mh : (i < own ? (mh & ((1u << (own - i)) - 1u)) : 0u);
-                    u32 after = mh & ~inside;
-                    if (inside) {
-                        atomicMin(&S.beg, i + __ffs(inside) - 1);
-                        atomicMax(&S.last, i + 31 - __clz(inside));
-                    }
-                    if (after) atomicMin(&S.end, i + __ffs(after) - 1);
-                }
             }
         }
     }
     if (zero_cnt) S.has_zero = 1u;      // explicit zero counts (host matrices): the k >= col_min_sum shortcut is off
+    __syncthreads();
+    // first / last hyperedge start inside the tile and the first one after it, by ONE warp over the head words (shared
+    // atomics from every warp on these three words were 12 % of the kernel's instructions); warp 0 meanwhile builds the
+    // prefix of the ok bits
+    if (tid >= 32 && tid < 64) {
+        int b = 0x7fffffff, e = 0x7fffffff, l = -1;
+        for (int w = lane; w < IT_WORDS; w += 32) {
+            const u32 mh = S.head[w];
+            if (mh) {
+                const int i = w * 32;
+                const u32 inside = (i + 32 <= own) ? mh : (i < own ? (mh & ((1u << (own - i)) - 1u)) : 0u);
+                const u32 after = mh & ~inside;
+                if (inside) {
+                    b = min(b, i + __ffs(inside) - 1);
+                    l = max(l, i + 31 - __clz(inside));
+                }
+                if (after) e = min(e, i + __ffs(after) - 1);
+            }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            b = min(b, __shfl_xor_sync(0xffffffffu, b, o));
+            e = min(e, __shfl_xor_sync(0xffffffffu, e, o));
+            l = max(l, __shfl_xor_sync(0xffffffffu, l, o));
+        }
+        if (lane == 0) {
+            S.beg = b;
+            S.end = e;
+            S.last = l;
+        }
+    }
+    it_word_prefix(S.ok, S.opref, tid);
     __syncthreads();
     const int beg = S.beg;
     const bool empty = beg == 0x7fffffff;
@@ -335,8 +358,6 @@ __global__ void __launch_bounds__(IT_THREADS, 3) incidence_tile_kernel(IncIn in,
             fend = S.last;
         }
     }
-    it_word_prefix(S.ok, S.opref, tid);
-    __syncthreads();
     // per hyperedge (thread at its start): surviving entries k, their summed count -> keep, D_e
     u32 my_heads = 0;
     const bool has_zero = S.has_zero != 0u;

@@ -58,6 +58,16 @@ def main():
         okv = mem >= 0
         out["ari_vs_planted"] = float(co.ari(mem[okv], g.group[okv])) if okv.any() else None
         ok = out["same_groups"]
+    # what a row-partitioned sweep would pay per phase: an all-gather of the label vector (n = 20 000 x int32, workload D)
+    lab = torch.zeros(20_000 // world, dtype=torch.int32, device=f"cuda:{local}")
+    full = torch.empty(20_000 // world * world, dtype=torch.int32, device=f"cuda:{local}")
+    for _ in range(20):
+        dist.all_gather_into_tensor(full, lab)
+    torch.cuda.synchronize(); dist.barrier(); t0 = time.perf_counter()
+    for _ in range(500):
+        dist.all_gather_into_tensor(full, lab)
+    torch.cuda.synchronize()
+    out["label_allgather_us"] = round((time.perf_counter() - t0) / 500 * 1e6, 1)
     dist.barrier()
     if rank == 0:
         out["ok"] = bool(ok)
