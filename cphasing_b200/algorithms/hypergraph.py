@@ -268,7 +268,8 @@ class HyperGraph:
             raw = D.triplets_to_edges(self.edges.row, self.edges.col, self.edges.count, self.edges.mapq, n)
             self.edges._raw = raw
         if raw.n_contigs != n:
-            raw = D.RawEdges(raw.row, raw.col, raw.count, raw.mapq, raw.nnz, raw.n_cols, n)
+            raw = D.RawEdges(raw.row, raw.col, raw.count, raw.mapq, raw.nnz, raw.n_cols, n, raw.packed, raw.n_edges,
+                             raw.min_order)
         self._raw = raw
         self._row_drop = None
         self._use_mapq = bool(self.min_quality > 0 and len(self.edges.mapq) > 1 and self.mapq_filter)

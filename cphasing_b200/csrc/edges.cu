@@ -318,9 +318,10 @@ struct PtSmemT {
     u16 cnt[PT_WIN];               // record count of the list entry in the same slot (warp kernel: bit 15 = first entry of a hyperedge)
     u16 rn[WARP ? 2 : PT_WIN];     // walk kernel: at a read start, number of entries the read emits (0 = filtered out)
     u16 src[WARP ? 2 : PT_WIN];    // walk kernel: output slot -> window position of the list entry
+    u8 dk[WARP ? PT_WIN : 4];      // warp kernel: D_e of the hyperedge the list entry in the same slot belongs to
     u32 head[PT_WORDS + 3];        // + zero padding: the warp kernel reads 96-bit windows of the mask without bounds checks
     u32 hpref[PT_WORDS + 1];
-    u32 tile, base, long_order, scan[PT_THREADS / 32 + 1];
+    u32 tile, base, long_order, nheads, scan[PT_THREADS / 32 + 1];
     u32 wstart[PT_THREADS / 32], wcnt[PT_THREADS / 32];   // warp kernel: window position and length of each warp's compacted output
     unsigned long long long_end;
 };
@@ -388,6 +389,12 @@ __device__ __forceinline__ void mbar_wait(unsigned long long* bar, u32 phase) {
     } while (!ok);
 }
 
+// D_e = max(int8(k) - 1, 1) with numpy's int8 wrap-around (algorithms/hypergraph.py:385, 418), as incidence.cu edge_degree
+__device__ __forceinline__ u32 pt_degree(u32 k) {
+    const int d8 = (int)(int8_t)(u8)((k - 1u) & 0xffu);
+    return (u32)max(d8, 1);
+}
+
 template <bool WARP, int MINB = 6>
 __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in, int use_tma, u32 min_order, u32 max_order, u32 read_offset,
                                                                    unsigned long long* __restrict__ tile_state, u32* __restrict__ scal,
@@ -399,6 +406,7 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
     if (tid == 0) {
         S.tile = atomicAdd(&scal[3], 1u);        // ticket: every lower tile has already started
         S.long_order = 0;
+        S.nheads = 0;
         if (use_tma) mbar_init(&S.mbar, 1);
     }
     __syncthreads();
@@ -589,6 +597,7 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
                     S.cvq[slot] = (c << 8) | q;
                     S.read[slot] = r;
                     S.cnt[slot] = (u16)((u32)__popc(peers) | (hd ? 0x8000u : 0u));
+                    S.dk[slot] = (u8)pt_degree(nd);
                     my_max_read = max(my_max_read, r);
                 }
                 __syncwarp();
@@ -657,6 +666,7 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
                         if (d < nd) {
                             S.cvq[o + d] = x;
                             S.cnt[o + d] = (u16)((cn & 0x7fffu) | (d == 0 ? 0x8000u : 0u));
+                            S.dk[o + d] = (u8)pt_degree((u32)nd);
                             S.read[o + d] = r;
                         }
                         __syncwarp();
@@ -773,15 +783,26 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
         }
     } else {
         // every warp copies its own compacted run out: consecutive lanes, consecutive addresses
+        // The count word also carries D_e of the entry's hyperedge in its top byte (D_e << 24 | count = the packed form the
+        // clique expansion reads): when the incidence stage has nothing to drop, these arrays ARE the packed incidence.
         const u32 ws = S.wstart[tid >> 5], wc = S.wcnt[tid >> 5];
+        u32 nheads = 0;
         for (u32 k = lane; k < wc; k += 32) {
             const u32 x = S.cvq[ws + k];
             const u32 cn = S.cnt[ws + k];
             const size_t p = (size_t)base + my_ex + k;
             rem_row[p] = (x >> 8) | ((cn & 0x8000u) ? CPH_HEAD : 0u);
             rem_col[p] = S.read[ws + k] + read_offset;                          // generate_edges :1871-1875
-            rem_count[p] = cn & 0x7fffu;
+            rem_count[p] = (cn & 0x7fffu) | ((u32)S.dk[ws + k] << 24);
             rem_mapq[p] = (int8_t)((int)(x & 0xffu) - 128);
+            nheads += (cn >> 15) & 1u;
+        }
+        nheads = warp_sum(nheads);
+        if (lane == 0 && nheads) atomicAdd(&S.nheads, nheads);
+        __syncthreads();
+        if (tid == 0) {
+            const u32 nh = S.nheads + (long_kept ? 1u : 0u);
+            if (nh) atomicAdd(&scal[2], nh);                             // hyperedges emitted by the whole call
         }
     }
     if (long_kept) {     // slow path, part 2: emit the long read after the tile's fast entries
@@ -803,7 +824,7 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
                 u32 p = base + fast_total + k;
                 rem_row[p] = c | (k == 0 ? CPH_HEAD : 0u);
                 rem_col[p] = rid + read_offset;
-                rem_count[p] = cnt;
+                rem_count[p] = WARP ? (cnt | (pt_degree(long_kept) << 24)) : cnt;
                 rem_mapq[p] = (int8_t)q;
             }
             carry += tot;
@@ -998,6 +1019,7 @@ extern "C" int cph_porec_to_edges_pf(const u32* read_idx, const u32* contig_idx,
         ARG_CHECK(N == 0 || (read_idx && contig_idx && mapq));
         ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq && h_counts);
         ARG_CHECK(N == 0 || edge_length == 0 || (start && end && contig_len));
+        h_counts[4] = h_counts[5] = 0;
         if (N == 0) {
             h_counts[0] = h_counts[1] = 0;
             return CPH_OK;
@@ -1012,13 +1034,15 @@ extern "C" int cph_porec_to_edges_pf(const u32* read_idx, const u32* contig_idx,
         KERNEL_CHECK();
         u32 hs[4] = {0, 0, 0, 0};
         u64 last = 0;
-        CUDA_TRY(cudaMemcpyAsync(hs, scal, 2 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+        CUDA_TRY(cudaMemcpyAsync(hs, scal, 3 * sizeof(u32), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
         CUDA_TRY(cudaStreamSynchronize(st));
         if (hs[1] == 0) {
             const u64 total = last & ((1ull << 62) - 1);
             h_counts[0] = total;
             h_counts[1] = total ? (u64)hs[0] + read_offset + 1 : 0;
+            h_counts[4] = hs[2];                            // hyperedges emitted
+            h_counts[5] = pt_mode() != 0 ? 1 : 0;           // the warp kernels pack D_e into the top byte of rem_count
             return CPH_OK;
         }
     }
@@ -1279,7 +1303,7 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     unsigned char* dev_ring = packed ? ar.take<unsigned char>(slot_layout.bytes * PK_NDEV) : nullptr;
     WS_QUERY_RETURN(ar);
     ARG_CHECK(h_counts);
-    h_counts[0] = h_counts[1] = h_counts[2] = h_counts[3] = 0;
+    h_counts[0] = h_counts[1] = h_counts[2] = h_counts[3] = h_counts[4] = h_counts[5] = 0;
     if (N == 0) return CPH_OK;
     ARG_CHECK(h_read_idx && h_contig_idx && h_mapq && d_read_idx && d_contig_idx && d_mapq);
     ARG_CHECK(rem_row && rem_col && rem_count && rem_mapq);
@@ -1476,9 +1500,9 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
             t_done = t_hi;
         }
     }
-    u32 hs[2] = {0, 0};
+    u32 hs[3] = {0, 0, 0};
     u64 last = 0;
-    HT_TRY(cudaMemcpyAsync(hs, scal, 2 * sizeof(u32), cudaMemcpyDeviceToHost, st));
+    HT_TRY(cudaMemcpyAsync(hs, scal, 3 * sizeof(u32), cudaMemcpyDeviceToHost, st));
     HT_TRY(cudaMemcpyAsync(&last, tile_state + (ntiles - 1), sizeof(u64), cudaMemcpyDeviceToHost, st));
     HT_TRY(cudaStreamSynchronize(st));
     HT_TRY(cudaStreamSynchronize(cs));
@@ -1493,6 +1517,8 @@ extern "C" int cph_porec_to_edges_host(const u32* h_read_idx, const u32* h_conti
     const u64 total = last & ((1ull << 62) - 1);
     h_counts[0] = total;
     h_counts[1] = total ? (u64)hs[0] + read_offset + 1 : 0;
+    h_counts[4] = hs[2];
+    h_counts[5] = pt_mode() != 0 ? 1 : 0;
     return rc;
 }
 

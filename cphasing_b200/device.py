@@ -66,11 +66,21 @@ class RawEdges:
     nnz: int
     n_cols: int            # max col + 1
     n_contigs: int
+    packed: bool = False   # count carries D_e of the entry's hyperedge in its top byte (D_e << 24 | count): what the warp
+    #                        group-by kernel writes.  Together with `row` that is the packed incidence of the table itself.
+    n_edges: int = 0       # hyperedges (runs) in the arrays when known, else 0
+    min_order: int = 0     # smallest hyperedge order the extraction let through (0 = unknown)
 
     def trimmed(self):
         k = self.nnz
         return RawEdges(self.row[:k], self.col[:k], self.count[:k], None if self.mapq is None else self.mapq[:k],
-                        k, self.n_cols, self.n_contigs)
+                        k, self.n_cols, self.n_contigs, self.packed, self.n_edges, self.min_order)
+
+    def plain_count(self):
+        """the count column without the D_e byte"""
+        if not self.packed:
+            return self.count
+        return (self.count.view(torch.int32) & 0x00FFFFFF).view(torch.uint32)
 
 
 class DeviceH:
@@ -196,11 +206,12 @@ def porec_to_edges(read_idx, contig_idx, mapq, n_contigs, start=None, end=None, 
     o_col = torch.empty(cap, dtype=torch.uint32, device=dev)
     o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
     o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
-    h = (C.c_uint64 * 2)()
+    h = (C.c_uint64 * 6)()
     call_ws("cph_porec_to_edges", dev, ptr(r), ptr(c), ptr(q), ptr(st), ptr(en), ptr(ln), N, int(n_contigs),
             int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0,
             ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
-    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs), bool(h[5]), int(h[4]),
+                    int(min_order)).trimmed()
 
 
 def _porec_to_edges_pf(read_idx, contig_idx, mapq, n_contigs, start, end, contig_len, min_mapq, min_order, max_order,
@@ -218,13 +229,14 @@ def _porec_to_edges_pf(read_idx, contig_idx, mapq, n_contigs, start, end, contig
     o_col = torch.empty(cap, dtype=torch.uint32, device=dev)
     o_cnt = torch.empty(cap, dtype=torch.uint32, device=dev)
     o_mq = torch.empty(cap, dtype=torch.int8, device=dev)
-    h = (C.c_uint64 * 2)()
+    h = (C.c_uint64 * 6)()
     pf, keep = prefilter.struct(dev)
     call_ws("cph_porec_to_edges_pf", dev, ptr(r), ptr(c), ptr(q), ptr(st), ptr(en), ptr(ln), N, int(n_contigs),
             int(min_mapq), int(min_order), int(max_order), int(edge_length or 0), int(read_offset), 0, C.byref(pf),
             ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
     del keep
-    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs), bool(h[5]), int(h[4]),
+                    int(min_order)).trimmed()
 
 
 STREAM_MIN_RECORDS = 1 << 22      # below this the chunked host path has nothing to overlap
@@ -312,7 +324,7 @@ def _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_o
     o_col = torch.empty(N, dtype=torch.uint32, device=dev)
     o_cnt = torch.empty(N, dtype=torch.uint32, device=dev)
     o_mq = torch.empty(N, dtype=torch.int8, device=dev)
-    h = (C.c_uint64 * 4)()
+    h = (C.c_uint64 * 6)()
     nt = _pack_threads()
     call_ws("cph_porec_to_edges_host", dev, ptr(hr), ptr(hc), ptr(hq), ptr(r), ptr(c), ptr(q), N, int(n_contigs),
             int(min_mapq), int(min_order), int(max_order), int(read_offset),
@@ -322,7 +334,8 @@ def _porec_to_edges_host(host, n_contigs, min_mapq, min_order, max_order, read_o
     LAST_H2D_BYTES = int(h[3])
     if int(h[2]):
         return None, (r, c, q)
-    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed(), None
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs), bool(h[5]), int(h[4]),
+                    int(min_order)).trimmed(), None
 
 
 @nvtx("cph:pairs_to_edges")
@@ -366,7 +379,7 @@ def edges_to_triplets(e: RawEdges):
     col = torch.empty(k, dtype=torch.int32, device=dev)
     cnt = torch.empty(k, dtype=torch.uint32, device=dev)
     mq = torch.empty(k, dtype=torch.int8, device=dev) if e.mapq is not None else None
-    call_ws("cph_edges_to_triplets", dev, ptr(e.row), ptr(e.col), ptr(e.count), ptr(e.mapq), k, int(e.n_contigs),
+    call_ws("cph_edges_to_triplets", dev, ptr(e.row), ptr(e.col), ptr(e.plain_count()), ptr(e.mapq), k, int(e.n_contigs),
             ptr(row), ptr(col), ptr(cnt), ptr(mq))
     return row, col, cnt, mq
 
@@ -402,7 +415,7 @@ def row_sums(e, min_mapq=0, row_drop=None, use_mapq=True, packed=False):
     mx = torch.zeros(1, dtype=torch.int32, device=dev)
     mq = e.mapq if (use_mapq and min_mapq > 0 and e.mapq is not None) else None
     check(lib().cph_row_sums(ptr(e.row), ptr(e.count), ptr(mq), e.nnz, e.n_contigs, int(min_mapq), ptr(row_drop),
-                             int(packed), ptr(out), ptr(mx), stream()))
+                             int(packed or getattr(e, "packed", False)), ptr(out), ptr(mx), stream()))
     return out, mx
 
 
@@ -439,8 +452,15 @@ def incidence(e: RawEdges, min_contacts=1, min_mapq=0, row_drop=None, mapq_filte
     if int(sc[2]) > 0x00FFFFFF:
         raise _lib.CphError("an alignment count >= 2^24 cannot be represented exactly (the reference stores counts "
                             "as float32)")
-    H = _incidence_build(e.row, e.col, e.count, e.mapq if use_mq else None, e.nnz, n, min_mapq if use_mq else 0,
-                         row_map, n_rows, col_min, False, keep, rs, e.n_cols)
+    if (e.packed and e.n_edges and not use_mq and row_drop is None and n_rows == n and e.nnz
+            and col_min > 0 and e.min_order >= 2 and os.environ.get("CPH_INCIDENCE_FAST", "1") != "0"):
+        # Nothing to drop: no entry filter, every contig passes min_contacts, every hyperedge holds >= 2 entries of count
+        # >= 1 (so its summed count passes the column filter) -- the group-by kernel's own output already IS the packed
+        # incidence (row | head, D_e << 24 | count, hyperedges numbered in order): no second pass over the entries.
+        H = DeviceH(e.row, e.count, e.nnz, n, e.n_edges, keep, rs)
+    else:
+        H = _incidence_build(e.row, e.col, e.count, e.mapq if use_mq else None, e.nnz, n, min_mapq if use_mq else 0,
+                             row_map, n_rows, col_min, bool(e.packed), keep, rs, e.n_cols)
     H._bound = bound
     return H
 

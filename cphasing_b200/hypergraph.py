@@ -240,8 +240,11 @@ class HyperExtractor:
 
 def _concat_raw(parts, n):
     cat = lambda f: torch.cat([getattr(p, f) for p in parts])
-    return D.RawEdges(cat("row"), cat("col"), cat("count"), cat("mapq"), sum(p.nnz for p in parts),
-                      max(p.n_cols for p in parts), n)
+    packed = all(p.packed and (p.n_edges or not p.nnz) for p in parts)     # every part straight from the group-by kernel
+    count = cat("count") if packed else torch.cat([p.plain_count() for p in parts])
+    return D.RawEdges(cat("row"), cat("col"), count, cat("mapq"), sum(p.nnz for p in parts),
+                      max(p.n_cols for p in parts), n, packed, sum(p.n_edges for p in parts) if packed else 0,
+                      min(p.min_order for p in parts) if packed else 0)
 
 
 class Extractor:

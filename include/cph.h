@@ -69,7 +69,11 @@ int cph_pairs_to_edges(const uint32_t* chrom1, const uint32_t* chrom2, const int
  * (:1461-1468), group_by(read, contig) -> count, max(mapq) (:1470-1477); read ids are shifted by
  * `read_offset` (generate_edges :1871-1875).  start/end/contig_len may be NULL when edge_length==0.
  * `sorted_by_read` != 0 promises read_idx is non-decreasing (skips the global sort).
- * Outputs need capacity n_records.  h_counts[0] = nnz, h_counts[1] = max col + 1 (0 if empty). */
+ * Outputs need capacity n_records.  h_counts has SIX entries: [0] = nnz, [1] = max col + 1 (0 if empty), [4] = number of
+ * hyperedges emitted (0 when the general sort path ran), [5] = 1 when rem_count carries D_e of the entry's hyperedge in
+ * its top byte (D_e << 24 | count, what cph_expand_* read as `pem_pk`): then rem_row / rem_count are the packed incidence
+ * of the table itself, and consumers that want plain counts pass `packed = 1` (cph_row_sums, cph_incidence_build) or mask
+ * with 0x00ffffff.  [2], [3]: see cph_porec_to_edges_host. */
 int cph_porec_to_edges(const uint32_t* read_idx, const uint32_t* contig_idx, const int8_t* mapq,
                        const uint32_t* start, const uint32_t* end, const int64_t* contig_len,
                        uint64_t n_records, uint32_t n_contigs, int min_mapq, uint32_t min_order,
@@ -121,7 +125,7 @@ int cph_porec_to_edges_pf(const uint32_t* read_idx, const uint32_t* contig_idx, 
  * contigs] | one u32 anchor per 1024 records) = 4 B per record, and a kernel restores the device columns
  * bit for bit; a chunk whose read ids step by more than 255 is copied as it is; the h_* arrays may be
  * pageable.  pack_threads < 0: two fewer than the host has cores, at most 16.  No edge filter
- * (edge_length == 0 only).  h_counts has FOUR entries: [0] = nnz, [1] = max col + 1, [3] = bytes copied to the
+ * (edge_length == 0 only).  h_counts has SIX entries ([4], [5] as above): [0] = nnz, [1] = max col + 1, [3] = bytes copied to the
  * device, [2] = 1 if the table is
  * NOT grouped by read: the d_* columns are complete, the outputs are not -- call cph_porec_to_edges on them. */
 int cph_porec_to_edges_host(const uint32_t* h_read_idx, const uint32_t* h_contig_idx, const int8_t* h_mapq,
