@@ -124,7 +124,8 @@ __global__ void __launch_bounds__(TPB) pairs_emit_kernel(PairsIn in, const u32* 
     size_t t = (size_t)col * 2;
     *reinterpret_cast<uint2*>(rem_row + t) = make_uint2(a | CPH_HEAD, b);
     *reinterpret_cast<uint2*>(rem_col + t) = make_uint2(col, col);
-    *reinterpret_cast<uint2*>(rem_count + t) = make_uint2(1u, 1u);   // :1287-1292 count = ones
+    // :1287-1292 count = ones; the top byte carries D_e = max(2 - 1, 1) = 1 of the two-entry hyperedge (packed form)
+    *reinterpret_cast<uint2*>(rem_count + t) = make_uint2((1u << 24) | 1u, (1u << 24) | 1u);
     *reinterpret_cast<char2*>(rem_mapq + t) = make_char2(q, q);
 }
 

@@ -368,7 +368,8 @@ def pairs_to_edges(chrom1, chrom2, mapq, n_contigs, pos1=None, pos2=None, contig
     else:
         call_ws("cph_pairs_to_edges", dev, ptr(c1), ptr(c2), ptr(q), ptr(p1), ptr(p2), ptr(ln), P, int(n_contigs),
                 int(min_mapq), int(edge_length or 0), ptr(o_row), ptr(o_col), ptr(o_cnt), ptr(o_mq), h)
-    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs)).trimmed()
+    # every surviving pair is a hyperedge of two entries with count 1: the kernel writes D_e = 1 into the count's top byte
+    return RawEdges(o_row, o_col, o_cnt, o_mq, int(h[0]), int(h[1]), int(n_contigs), True, int(h[0]) // 2, 2).trimmed()
 
 
 def edges_to_triplets(e: RawEdges):

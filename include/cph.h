@@ -56,7 +56,8 @@ uint64_t cph_launch_count(void);
  * Replaces Extractor.generate_edges (hypergraph.py:895-1300): mapq filter (:970-971), both-ends
  * edge filter (:977-992), col = running number of the surviving pairs (:1031), two triplets per
  * pair with count 1 (:1033-1044, 1287-1292).  Outputs need capacity 2*n_pairs.
- * h_counts[0] = nnz (2 * surviving pairs), h_counts[1] = number of columns. */
+ * h_counts[0] = nnz (2 * surviving pairs), h_counts[1] = number of columns.  rem_count = (1 << 24) | 1 for every entry: count 1
+ * with D_e = 1 of the two-entry hyperedge in the top byte (the packed form, see cph_porec_to_edges). */
 int cph_pairs_to_edges(const uint32_t* chrom1, const uint32_t* chrom2, const int8_t* mapq,
                        const uint32_t* pos1, const uint32_t* pos2, const int64_t* contig_len,
                        uint64_t n_pairs, uint32_t n_contigs, int min_mapq, uint64_t edge_length,
