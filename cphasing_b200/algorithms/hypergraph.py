@@ -13,6 +13,7 @@ import os
 
 import msgspec
 import numpy as np
+import pandas as pd
 import torch
 from scipy.sparse import csr_matrix
 

@@ -146,3 +146,68 @@ def test_second_round_fan_out_gathers_every_group_on_every_rank():
         assert nums == [1, 2, 3, 4, 5]
         assert grp3 == [[30, 31], [32, 33]]
     assert all(g[1] == "refused" for g in got if len(g) == 2)
+
+
+def test_sweep_bands_partition_the_triangle():
+    from cphasing_b200 import device as D
+    for n, mb in ((1, 1), (7, 0.0001), (6000, 3), (20000, 128), (10000, 96), (100000, 96)):
+        r0 = D.sweep_bands(n, band_bytes=int(mb * (1 << 20)))
+        assert r0[0] == 0 and r0[-1] == n and all(a < b for a, b in zip(r0, r0[1:]))
+        cells = [b * (2 * n - b + 1) // 2 - a * (2 * n - a + 1) // 2 for a, b in zip(r0, r0[1:])]
+        assert sum(cells) == n * (n + 1) // 2
+        limit = max(int(mb * (1 << 20)) // 8, n)
+        assert all(c <= limit or b - a == 1 for c, a, b in zip(cells, r0, r0[1:]))     # a band is at most the limit (or one row)
+
+
+def _band_sum_worker(rank, ws, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        from cphasing_b200 import device as D
+
+        class H:                       # stands in for a DeviceH shard; the accumulate below is a host fake
+            n_rows, device = 50, torch.device("cpu")
+        n = H.n_rows
+        tri = n * (n + 1) // 2
+        real = D.expand_accumulate
+
+        def fake(Hs, use_high_order=True, band_hook=None, acc_out=None, **kw):
+            acc = acc_out if acc_out is not None else torch.empty(tri, dtype=torch.int64)
+            r0 = D.sweep_bands(n, band_bytes=8 * 200)          # ~7 bands
+            for k in range(len(r0) - 1):
+                lo, hi = r0[k], r0[k + 1]
+                c_lo, c_hi = lo * (2 * n - lo + 1) // 2, hi * (2 * n - hi + 1) // 2
+                acc[c_lo:c_hi] = torch.arange(c_lo, c_hi, dtype=torch.int64) * (rank + 1)
+                band_hook(k, lo, hi, c_lo, c_hi)
+            return D.Accumulator(acc, torch.full((n,), rank + 1, dtype=torch.int64), n, 0, bool(use_high_order))
+        D.expand_accumulate = fake
+        marks = []
+        acc = par.expand_accumulate_sum(H, use_high_order=False, on_local_done=lambda: marks.append(1))
+        D.expand_accumulate = real
+        q.put((rank, acc.acc.clone(), acc.diag.clone(), len(marks)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_band_by_band_exchange_sums_every_cell_once():
+    """parallel.expand_accumulate_sum with a swept accumulator: every band all-reduced exactly once (gloo: after the local
+    work; NCCL runs the same calls on a side stream under the next band), diagonal summed, hook for the benchmark called"""
+    ws = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_band_sum_worker, args=(r, ws, port, q)) for r in range(ws)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(ws)]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    n = 50
+    tri = n * (n + 1) // 2
+    for rank, acc, diag, nm in res:
+        assert torch.equal(acc, torch.arange(tri, dtype=torch.int64) * 3)      # (1 + 2) x the cell's own index
+        assert torch.equal(diag, torch.full((n,), 3, dtype=torch.int64))
+        assert nm == 1
