@@ -26,7 +26,7 @@ sys.path.insert(0, ROOT)
 # concatemer-column shards; N=1 is exactly the named config).  `--workload D` runs config D's genome (20k contigs) with
 # 62.5M concatemers per GPU (the named 500M at N=8); its numbers are recorded in profiles/ and DESIGN.md.
 # dram bytes per launch of the dominant kernel from the committed ncu --set full capture, keyed by (workload, m per GPU)
-NCU_TRAFFIC = {("C", 50_000_000): 2723423000 + 2316372000}      # profiles/r2h_ncu_full_C.txt (porec_tile_kernel<1, 8>)
+NCU_TRAFFIC = {("C", 50_000_000): 2724058000 + 2344288000}      # profiles/r2w_ncu_full_C.txt (porec_tile_kernel<1, 8>)
 PARAMS = dict(min_mapq=1, min_order=2, max_order=50, min_contacts=25, min_weight=2.0)   # cphasing/_config.py:38-45
 
 
