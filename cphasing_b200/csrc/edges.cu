@@ -733,10 +733,12 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
     // decoupled look-back (warp 0): exclusive prefix of the tile totals
     if (tid < 32) {
         u32 base = 0;
+        // the state word (flag + value in one aligned 64-bit word) is published with a plain volatile store: nothing waits
+        // for it here, where an atomicExch would hold warp 0 -- and the seven warps behind the barrier -- for an L2 round trip
         if (tile == 0) {
-            if (lane == 0) atomicExch(&tile_state[0], PT_INCL | (u64)total);
+            if (lane == 0) *((volatile unsigned long long*)&tile_state[0]) = PT_INCL | (u64)total;
         } else {
-            if (lane == 0) atomicExch(&tile_state[tile], PT_AGG | (u64)total);
+            if (lane == 0) *((volatile unsigned long long*)&tile_state[tile]) = PT_AGG | (u64)total;
             u64 running = 0;
             long j = (long)tile - 1;
             for (;;) {
@@ -756,7 +758,7 @@ __global__ void __launch_bounds__(PT_THREADS, MINB) porec_tile_kernel(PorecIn in
                 j -= 32;
             }
             base = (u32)running;
-            if (lane == 0) atomicExch(&tile_state[tile], PT_INCL | (running + total));
+            if (lane == 0) *((volatile unsigned long long*)&tile_state[tile]) = PT_INCL | (running + total);
         }
         if (lane == 0) S.base = base;
     }
