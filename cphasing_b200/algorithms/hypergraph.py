@@ -501,11 +501,37 @@ class HyperGraph:
     #    positive factors are experimental branches no live caller selects)
     @staticmethod
     def reweight_adjacency_matrix(A, P_allelic_idx=None, P_weak_idx=None, allelic_factor=-1, cross_allelic_factor=0):
+        if P_allelic_idx and isinstance(allelic_factor, (int, float)) and not isinstance(allelic_factor, bool) \
+                and allelic_factor > 0:
+            # :674-681 -- the branch `--allelic-positive-factor` (CLI default 3.0) takes when the first round merges
+            # homologous clusters (hyperpartition.py:1903-1907): listed pairs become (A_ij + half the 90th percentile of the
+            # stored weights) x factor, INCLUDING pairs that had no contact (the assignment creates the entry).  A few
+            # thousand pairs, once per partition: done on the host copy, the structure of A changes.
+            out = HyperGraph._reweight_positive(A, P_allelic_idx, float(allelic_factor))
+            if P_weak_idx:
+                out = HyperGraph.reweight_adjacency_matrix(out, None, P_weak_idx, 0, cross_allelic_factor)
+            return out
         if P_allelic_idx or P_weak_idx:
             from .. import graphops
             return graphops.reweight_pairs(A, P_allelic_idx if P_allelic_idx else None,
                                            P_weak_idx if P_weak_idx else None, allelic_factor, cross_allelic_factor)
         return A
+
+    @staticmethod
+    def _reweight_positive(A, P, factor):
+        Ah = csr_matrix(A, copy=True)
+        Ah.sum_duplicates()
+        n = Ah.shape[0]
+        r, c = HyperGraph._normalize_pair_index(P)
+        key = np.unique(r * n + c)                               # a pair listed twice is assigned once
+        r, c = key // n, key % n
+        baseline = 0.5 * (float(np.percentile(Ah.data, 90)) if Ah.nnz else 1.0)
+        vals = np.asarray(Ah[r, c]).ravel().astype(np.float64)
+        delta = (vals + baseline) * factor - vals                # what has to be ADDED to reach the assigned value
+        from scipy.sparse import coo_matrix
+        out = (Ah + coo_matrix((delta.astype(Ah.dtype), (r, c)), shape=Ah.shape).tocsr()).tocsr()
+        out.sort_indices()
+        return out
 
     # -- algorithms/hypergraph.py:712-753 (TSV writer: host I/O)
     @staticmethod

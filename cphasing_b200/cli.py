@@ -6,8 +6,9 @@
     python -m cphasing_b200 utils hg2contacts <in.hg> <contigsizes> -o <out.contacts>            (cli.py:9290-9401)
 
 Same positional arguments, option names and defaults (cphasing/_config.py:30-55) for the options that belong to the
-accelerated path (HCR BED, contig splitting, prune / allele tables included); the reference's remaining options steer stages
-that are out of scope (fasta alleles, ultra-long reads, plotting) and are not accepted.  This is a thin argparse layer over
+accelerated path (HCR BED, contig splitting, prune / allele tables included); the reference's remaining `hyperpartition`
+options parse as well -- those that steer stages out of scope (fasta alleles, ultra-long reads, collapsed rescue, the
+experimental post-passes) raise NotImplementedError when used, never silently.  This is a thin argparse layer over
 HyperExtractor / Extractor / HyperPartition / KPrunerRust.
 """
 from __future__ import annotations
@@ -117,7 +118,29 @@ def cmd_hyperpartition(args):
                                                                           else "basal")
     if not n and args.resolution1 < 0:
         args.resolution1 = args.init_resolution1          # no group number to search for: one clustering at the start value
+    # options that steer stages outside the accelerated path: accepted where they change nothing here, refused loudly where
+    # they would (cli.py:3945-4597 defines them all; a pipeline script must not die on an unknown flag)
+    if args.ultra_long:
+        raise NotImplementedError("-ul / --ultra-long: ultra-long hypergraphs are outside the accelerated path")
+    if args.collapsed_contigs:
+        raise NotImplementedError("--collapsed-contigs (collapsed rescue) is outside the accelerated path")
+    if args.contacts:
+        logger.info("--contacts is not needed: the in-process kprune reads its contacts off the hypergraph "
+                    "(hyperpartition.py:399-421)")
+    if args.kprune_norm_method not in ("none", "cis"):
+        logger.warning(f"--kprune-norm-method {args.kprune_norm_method}: defined by the cphasing-rs binary only; the in-process "
+                       "kprune scores raw contacts")
+    groups_1based = lambda v: [int(x) for x in str(v).split(",") if x.strip()] if v else None
+    if args.output_hg and (args.porec or args.pairs):
+        ex.save(re.sub(r"\.(porec|pairs)(\.gz)?$|\.pqs$", "", args.hypergraph) + ".hg")                 # cli.py:4796-4834
     hp = HyperPartition(edges, sizes, k=n, alleletable=at, prunetable=args.prunetable, normalize=args.normalize, split=split,
+                        fasta=args.fasta, kprune_norm_method=args.kprune_norm_method,
+                        merge_use_allele=not args.disable_merge_use_allele,
+                        allelic_positive_factor=float(args.allelic_positive_factor),
+                        exclude_group_to_second=groups_1based(args.exclude_group_to_second),
+                        exclude_group_from_first=groups_1based(args.exclude_group_from_first),
+                        is_recluster_contigs=args.recluster_contigs, refine=args.refine,
+                        disable_recluster_by_linkage=args.disable_recluster_by_linkage,
                         allelic_factor=args.allelic_factor, cross_allelic_factor=args.cross_allelic_factor,
                         allelic_similarity=args.allelic_similarity, min_allelic_overlap=args.min_allelic_overlap,
                         disable_merge_in_first=args.disable_merge_in_first, whitelist=read_list(args.whitelist),
@@ -128,7 +151,15 @@ def cmd_hyperpartition(args):
                         cluster_method=args.cluster_method, min_quality1=args.min_quality1,
                         min_quality2=args.min_quality2, min_scaffold_length=_size(args.min_scaffold_length),
                         threshold=args.threshold, max_round=args.max_round, threads=args.threads)
-    if mode == "phasing":                                                                   # cli.py:5334-5346
+    if args.merge_cluster:                                                                  # cli.py:4885-4892, 5005-5018
+        if mode == "phasing":
+            logger.error("Imcomplete function of merge cluster in phasing mode.")            # the reference's own message
+            sys.exit(-1)
+        groups = [l.rstrip("\n").split("\t")[2].split(" ") for l in open(args.merge_cluster) if l.strip()]
+        hp.merge_cluster(groups)
+        hp.to_cluster(args.output)
+        return 0
+    if mode == "phasing" or args.incremental:                                               # cli.py:5334-5346
         first = None
         if args.first_cluster:
             first = [l.rstrip("\n").split("\t")[2].split(" ") for l in open(args.first_cluster) if l.strip()]
@@ -212,6 +243,33 @@ def build_parser():
     h.add_argument("--cluster-method", choices=["louvain", "leiden"], default="louvain")
     h.add_argument("--threshold", type=float, default=0.01)
     h.add_argument("--max-round", type=int, default=1)
+    # the rest of cli.py:3945-4597, so that a command line written for the reference parses; see cmd_hyperpartition for what
+    # each of them does here
+    h.add_argument("-c", "--contacts", default=None)
+    h.add_argument("-ul", "--ultra-long", dest="ultra_long", default=None)
+    h.add_argument("-ul-w", "--ul-weight", dest="ul_weight", type=int, default=1)
+    h.add_argument("-f", "--fasta", default=None)
+    h.add_argument("-alleles-k", "--alleles-k", "--alleles-kmer-size", dest="alleles_kmer_size", type=int, default=19)
+    h.add_argument("-alleles-w", "--alleles-w", "--alleles-window-size", dest="alleles_window_size", type=int, default=19)
+    h.add_argument("-alleles-m", "--alleles-m", "--alleles-minimum-similarity", dest="alleles_minimum_similarity", type=float,
+                   default=0.2)
+    h.add_argument("-alleles-d", "--alleles-d", "--alleles-diff-thres", dest="alleles_diff_thres", type=float, default=0.1)
+    h.add_argument("-alleles-tl", "--alleles-trim-length", dest="alleles_trim_length", type=int, default=25000)
+    h.add_argument("-inc", "--incremental", action="store_true")
+    h.add_argument("-knm", "--kprune-norm-method", dest="kprune_norm_method", choices=["none", "re", "cis", "cis_density"],
+                   default="cis")
+    h.add_argument("--merge-cluster", dest="merge_cluster", default=None)
+    h.add_argument("--disable-merge-use-allele", "--disable-merge-first-use-allele", dest="disable_merge_use_allele",
+                   action="store_true")
+    h.add_argument("-apf", "--allelic-positive-factor", dest="allelic_positive_factor", default="3.0")
+    h.add_argument("--exclude-group-to-second", "--exclude-to-second", dest="exclude_group_to_second", default=None)
+    h.add_argument("--exclude-from-first", "--exclude-group-from-first", dest="exclude_group_from_first", default=None)
+    h.add_argument("--enable-misassembly-remove", dest="enable_misassembly_remove", action="store_true", default=True)
+    h.add_argument("--is-recluster-contigs", "--recluster-contigs", dest="recluster_contigs", action="store_true")
+    h.add_argument("--disable-recluster-by-linkage", dest="disable_recluster_by_linkage", action="store_true")
+    h.add_argument("--refine", action="store_true")
+    h.add_argument("--collapsed-contigs", dest="collapsed_contigs", default=None)
+    h.add_argument("--output-hg", dest="output_hg", action="store_true")
     h.set_defaults(fn=cmd_hyperpartition)
 
     k = sub.add_parser("kprune")                                                   # cli.py:3525-3645

@@ -82,6 +82,10 @@ class HyperPartition:
                  collapsed_contigs_df=None, threshold=0.01, max_round=1, threads=4, chunksize=None, **kw):
         if ultra_long is not None or chunksize:
             raise NotImplementedError("ultra-long edges / chunked H are outside the accelerated path")
+        if is_remove_misassembly or is_recluster_contigs or refine or collapsed_contigs_df is not None:
+            raise NotImplementedError("--remove-misassembly / --recluster-contigs / --refine / collapsed contigs: the "
+                                      "experimental second-round post-passes (hyperpartition.py:2742, 3095, 3575) are not "
+                                      "implemented")
         self.edges = edges
         if isinstance(contigsizes, dict):
             contigsizes = pd.DataFrame({"length": pd.Series(contigsizes)})
@@ -800,6 +804,27 @@ class HyperPartition:
             V = np.delete(np.delete(V, i2, axis=0), i2, axis=1)
             iter_round += 1
         return K
+
+    # -- hyperpartition.py:2674-2719 (`--merge-cluster`): no clustering, the given groups are merged down to k[0]
+    def merge_cluster(self, groups):
+        vi = self.vertices_idx
+        vertices_idx_sizes = pd.DataFrame({'length': pd.Series(self.vertices_idx_sizes)})
+        A = self.HG.clique_expansion_init(self.H, P_allelic_idx=self.P_allelic_idx, P_weak_idx=self.P_weak_idx, NW=self.NW,
+                                          allelic_factor=self.allelic_factor, min_weight=self.min_weight)
+        # (the reference indexes vertices_idx[x] and dies on a contig that was filtered out; such contigs are skipped here)
+        self.K = [[vi[x] for x in grp if x in vi] for grp in groups]
+        self.K = sorted([g for g in self.K if g], key=lambda x: vertices_idx_sizes.loc[x]['length'].sum(), reverse=True)
+        allelic_idx_set = getattr(self, "allelic_idx_set", None)
+        if allelic_idx_set is None:
+            if self.alleletable is not None:
+                raise NotImplementedError("merge_cluster with an allele table weighs group overlaps by shared minimizers "
+                                          "(_merge(alleletable_df=...), hyperpartition.py:2696-2715): not implemented; pass "
+                                          "a prune table instead")
+            allelic_idx_set = set()
+        self.K = HyperPartition._merge(A, self.K, vertices_idx_sizes, self.k[0], allelic_idx_set=allelic_idx_set,
+                                       min_allelic_overlap=0.8, allele_use_method="merge", method='sum')
+        self.K = sorted(self.K, key=lambda x: vertices_idx_sizes.loc[x]['length'].sum(), reverse=True)
+        return self.K
 
     # -- hyperpartition.py:3426-3575: unanchored contigs join the group they touch most.  The group scores S = A M of ALL
     #    unanchored contigs come from the device in one call (cph_group_sums); a rescued contig changes the scores of the

@@ -97,3 +97,17 @@ def test_cli_files_end_to_end(tmp_path):
     pt3 = tmp_path / "prune.precise.table"
     run("kprune", str(at), str(contacts), "-o", str(pt3))
     assert {l.split("\t")[6] for l in pt3.read_text().strip().split("\n")} == {"0", "1"}
+    # a command line written for the reference parses (cli.py:3945-4597 options that steer other stages are accepted, the ones
+    # that would change the result here refuse loudly): --merge-cluster merges the 20 groups of `out` down to 5 (cli.py:5013)
+    merged = tmp_path / "merged.clusters.txt"
+    run("hyperpartition", str(hgf), str(sizes), str(merged), "-n", "5", "--merge-cluster", str(out), "-knm", "cis", "-apf", "3.0",
+        "--disable-merge-use-allele", "-c", str(contacts), "--enable-misassembly-remove", "-alleles-k", "19")
+    lm = merged.read_text().strip().split("\n")
+    assert len(lm) == 5
+    before = sorted(m for l in lines for m in l.split("\t")[2].split(" "))
+    after = sorted(m for l in lm for m in l.split("\t")[2].split(" "))
+    assert after == before                                                  # the same contigs, now in 5 groups (_merge, :2711)
+    out_hg = tmp_path / "reads.hg2"
+    r = subprocess.run([sys.executable, "-m", "cphasing_b200", "hyperpartition", str(hgf), str(sizes), str(tmp_path / "x.txt"),
+                        "-n", "5:4", "--refine"], cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode != 0 and "not implemented" in r.stderr
