@@ -70,16 +70,24 @@ def _extract(args, sizes):
     boundarys = None
     if sl:
         sizes, boundarys = split_contigs(sizes, sl)
+    wl = getattr(args, "extract_whitelist", None)
+    if wl:                                                                      # cli.py hypergraph: only whitelisted contigs are indexed
+        keep = {l.strip() for l in open(wl) if l.strip()}
+        sizes = sizes[[c.split("|")[0] in keep for c in sizes.index]]
     idx = {c: i for i, c in enumerate(sizes.index)}
     sz = sizes["length"].to_dict()
-    el = _size(args.edge_length) if args.edge_length else 0
+    el = _size(args.edge_length) if str(args.edge_length).lower() not in ("none", "", "0") else 0
+    tables = [args.table]
+    if getattr(args, "fofn", False):                                            # a file of file names
+        tables = [l.strip() for l in open(args.table) if l.strip()]
     pre = dict(hcr_bed=getattr(args, "hcr_bed", None), hcr_invert=getattr(args, "hcr_invert", False), split_length=sl,
                split_contig_boundarys=boundarys)
     if args.pairs:
-        return hg.Extractor([args.table], idx, sz, min_quality=args.min_quality, edge_length=el, threads=args.threads,
+        return hg.Extractor(tables, idx, sz, min_quality=args.min_quality, edge_length=el, threads=args.threads,
                             **pre), sizes
-    return hg.HyperExtractor([args.table], idx, sz, min_order=args.min_order, max_order=args.max_order,
-                             min_quality=args.min_quality, edge_length=el, threads=args.threads, **pre), sizes
+    return hg.HyperExtractor(tables, idx, sz, min_order=args.min_order, max_order=args.max_order,
+                             min_alignments=getattr(args, "min_alignments", 30), min_quality=args.min_quality, edge_length=el,
+                             threads=args.threads, **pre), sizes
 
 
 def cmd_hypergraph(args):
@@ -211,6 +219,9 @@ def build_parser():
     g = sub.add_parser("hypergraph", aliases=["hg"])
     g.add_argument("table"); g.add_argument("contigsizes"); g.add_argument("output")
     extract_opts(g)
+    g.add_argument("-ma", "--min-alignments", dest="min_alignments", type=int, default=30)
+    g.add_argument("--fofn", action="store_true", help="the first argument is a file of contact-table file names")
+    g.add_argument("-wl", "--whitelist", dest="extract_whitelist", default=None)
     g.set_defaults(fn=cmd_hypergraph)
 
     h = sub.add_parser("hyperpartition", aliases=["hp"])
