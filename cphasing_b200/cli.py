@@ -47,14 +47,33 @@ def load_hg(path):
     return hgio.load(path)
 
 
-def split_contigs(sizes, split_length):
-    """cli.py:4776-4790: contigs cut into `split_length` bins named `ctg|start_end`.  -> (split sizes DataFrame, dict
-    original contig -> index of its first bin)"""
+def auto_split_length(sizes, max_split_len=20_000_000, min_split_len=1_000_000, outlier_factor=5.0):
+    """`--split-length auto` (utilities.py:1709-1744): split only when one contig is an outlier -- longer than 5 x the 95th
+    length percentile and than 20 Mb; the bin length is then that percentile, kept within [1 Mb, 20 Mb] and rounded up to
+    the next whole Mb.  None: no splitting."""
+    ln = sizes["length"]
+    if len(ln) < 10:
+        return None
+    longest, p95 = ln.max(), ln.quantile(0.95)
+    if not (longest > p95 * outlier_factor and longest > max_split_len):
+        return None
+    sl = int(max(int(min(p95, max_split_len)), min_split_len))
+    return (sl // 1_000_000 + 1) * 1_000_000
+
+
+def split_contigs(sizes, split_length, trim_length=0):
+    """cli.py:4776-4790 / utilities.binnify (:1430-1480): contigs, in NAME order, cut into `split_length` bins named
+    `ctg|start_end`; with `trim_length` (hyperpartition: --alleles-trim-length) the bin edges of a contig longer than three
+    times that are pulled `trim_length` in from both ends.  -> (split sizes DataFrame, dict original contig -> index of its
+    first bin)"""
     names, lens, first = [], [], {}
-    for c, L in zip(sizes.index, sizes["length"].astype(int)):
+    for c, L in sorted(zip(sizes.index, sizes["length"].astype(int)), key=lambda x: x[0]):
         first[c] = len(names)
-        for a in range(0, max(L, 1), split_length):
-            b = min(L, a + split_length)
+        nb = max(int(-(-L // split_length)), 1)
+        edges = [min(k * split_length, L) for k in range(nb)] + [L]
+        if trim_length and L > 3 * trim_length:
+            edges = [min(max(e, trim_length), L - trim_length) for e in edges]
+        for a, b in zip(edges[:-1], edges[1:]):
             names.append(f"{c}|{a}_{b}")
             lens.append(b - a)
     return pd.DataFrame({"length": lens}, index=pd.Index(names, name="contig")), first
@@ -64,12 +83,16 @@ def _extract(args, sizes):
     """-> (extractor, contig sizes actually indexed: the split bins when --split-length is on)"""
     from . import hypergraph as hg
     sl = getattr(args, "split_length", "none")
-    if str(sl).lower() == "auto":
-        raise NotImplementedError("--split-length auto (utilities.determine_split_length) is not built; give a length or `none`")
-    sl = None if str(sl).lower() in ("none", "no", "null", "0") else _size(sl)
+    if sl is None or str(sl).lower() in ("none", "no", "null", "0"):
+        sl = None
+    elif str(sl).lower() == "auto":
+        sl = auto_split_length(sizes)                                           # cli.py:4757-4758
+        logger.info(f"--split-length auto: {'no splitting' if not sl else sl}")
+    else:
+        sl = _size(sl)
     boundarys = None
     if sl:
-        sizes, boundarys = split_contigs(sizes, sl)
+        sizes, boundarys = split_contigs(sizes, sl, trim_length=getattr(args, "alleles_trim_length", 0) or 0)
     wl = getattr(args, "extract_whitelist", None)
     if wl:                                                                      # cli.py hypergraph: only whitelisted contigs are indexed
         keep = {l.strip() for l in open(wl) if l.strip()}
@@ -213,8 +236,9 @@ def build_parser():
         p.add_argument("-t", "--threads", type=int, default=4)
         p.add_argument("-hcr", "--hcr-bed", dest="hcr_bed", default=None, help="BED of high-confidence regions")
         p.add_argument("-hcr-invert", "--hcr-invert", dest="hcr_invert", action="store_true")
-        p.add_argument("-sl", "--split-length", dest="split_length", default="none",
-                       help="split contigs into bins of this length (`none`: off; the reference's `auto` rule is not built)")
+        p.add_argument("-sl", "--split-length", dest="split_length", default=None,
+                       help="split contigs into bins of this length; `auto` (the default of hyperpartition, as in the "
+                            "reference): only when one contig is an outlier in length; `none`: off")
 
     g = sub.add_parser("hypergraph", aliases=["hg"])
     g.add_argument("table"); g.add_argument("contigsizes"); g.add_argument("output")
@@ -281,7 +305,7 @@ def build_parser():
     h.add_argument("--refine", action="store_true")
     h.add_argument("--collapsed-contigs", dest="collapsed_contigs", default=None)
     h.add_argument("--output-hg", dest="output_hg", action="store_true")
-    h.set_defaults(fn=cmd_hyperpartition)
+    h.set_defaults(fn=cmd_hyperpartition, split_length="auto")
 
     k = sub.add_parser("kprune")                                                   # cli.py:3525-3645
     k.add_argument("alleletable", metavar="AlleleTable")
