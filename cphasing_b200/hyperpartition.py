@@ -423,6 +423,7 @@ class HyperPartition:
         vertices_idx_sizes = pd.DataFrame({'length': pd.Series(self.vertices_idx_sizes)})   # = DataFrame(d, index=['length']).T, without 1 column per contig
         A = HyperGraph.normalize_adjacency_matrix(A, self.NW) if self.NW is not None else A
         allelic_idx_set = None
+        at_df_idx = None                                                                   # index-space allele table for _merge
         if self.merge_use_allele:                                                          # :1794-1896 (no fasta branch)
             if self.prune_pair_df is not None:
                 df = self.prune_pair_df
@@ -430,11 +431,14 @@ class HyperPartition:
                                           [['contig1', 'contig2']].values))
             elif self.alleletable is not None:
                 at_df = _allele_frame(self.alleletable)
-                at_df = at_df[(at_df['similarity'] >= 0.90) & (at_df['mzShared'] >= 100)]
+                at_df = at_df[(at_df['similarity'] >= 0.90) & (at_df['mzShared'] >= 100)].copy()
                 vi = self.vertices_idx
-                c1, c2 = at_df[1].map(vi.get), at_df[2].map(vi.get)
-                ok = c1.notna() & c2.notna()
-                allelic_idx_set = set(zip(c1[ok].astype(int), c2[ok].astype(int)))
+                at_df[1] = at_df[1].map(vi.get)
+                at_df[2] = at_df[2].map(vi.get)
+                at_df = at_df.dropna(subset=[1, 2])
+                at_df[1] = at_df[1].astype(int); at_df[2] = at_df[2].astype(int)
+                allelic_idx_set = set(map(tuple, at_df[[1, 2]].values))
+                at_df_idx = at_df
             else:
                 allelic_idx_set = set()
         raw_A = A
@@ -500,7 +504,8 @@ class HyperPartition:
                     self.K = sorted(self.K, key=lambda x: vertices_idx_sizes.loc[x]["length"].sum(), reverse=True)[:k[0]]
                 elif allelic_idx_set is not None and self.merge_use_allele:
                     self.K = HyperPartition._merge(A1, self.K, vertices_idx_sizes, k[0], allelic_idx_set=allelic_idx_set,
-                                                   min_allelic_overlap=0.8, allele_use_method='merge', method='sum')
+                                                   alleletable_df=at_df_idx, min_allelic_overlap=0.8,
+                                                   allele_use_method='merge', method='sum')
                 else:
                     self.K = HyperPartition._merge(A1, self.K, vertices_idx_sizes, k[0],
                                                    min_allelic_overlap=self.min_allelic_overlap, method='sum')
@@ -742,8 +747,12 @@ class HyperPartition:
                allele_use_method="conflict", method='mean'):
         if not k:
             return K
+        # with an allele table the overlap of two groups is weighed in MINIMIZERS, not bases (:2308-2319, 2366-2368): a
+        # group's size is the summed mz1 of its contigs (first row per contig), a linked pair counts its mzShared
+        shared_mz, contig_mz = None, None
         if alleletable_df is not None:
-            raise NotImplementedError("_merge with minimizer-weighted allele overlaps (alleletable_df) is not implemented")
+            shared_mz = alleletable_df[[1, 2, 'mzShared']].set_index([1, 2])['mzShared'].to_dict()
+            contig_mz = alleletable_df[[1, 'mz1']].drop_duplicates(subset=[1]).set_index(1)['mz1'].to_dict()
         if hasattr(vertices_idx_sizes, 'to_dict'):
             size_db = vertices_idx_sizes.to_dict()
             if 'length' in size_db:
@@ -760,22 +769,31 @@ class HyperPartition:
             g = len(K)
             if iter_round > (g - k + 100):
                 break
-            group_lengths = np.array([sum(size_db.get(c, 0.0) for c in grp) for grp in K], dtype=np.float64)
+            len_db = contig_mz if contig_mz is not None else size_db
+            group_lengths = np.array([sum(len_db.get(c, 0.0) for c in grp) for grp in K], dtype=np.float64)
             flag = np.ones((g, g))
             overlap = np.zeros((g, g))
             if allelic_idx_set:                                                           # :2349-2392
                 c2g = {c: i for i, grp in enumerate(K) for c in grp}
                 s1, s2 = defaultdict(set), defaultdict(set)
+                m1, m2 = defaultdict(float), defaultdict(float)
                 for c1, c2 in allelic_idx_set:
                     g1, g2 = c2g.get(c1), c2g.get(c2)
                     if g1 is not None and g2 is not None and g1 != g2:
                         if g1 > g2:
                             g1, g2, c1, c2 = g2, g1, c2, c1
-                        s1[(g1, g2)].add(c1)
-                        s2[(g1, g2)].add(c2)
-                for (i, j), a in s1.items():
-                    l1 = float(sum(size_db.get(c, 0.0) for c in a))
-                    l2 = float(sum(size_db.get(c, 0.0) for c in s2.get((i, j), set())))
+                        if shared_mz is not None:
+                            m1[(g1, g2)] += shared_mz.get((c1, c2), 0.0)
+                            m2[(g1, g2)] += shared_mz.get((c2, c1), 0.0)
+                        else:
+                            s1[(g1, g2)].add(c1)
+                            s2[(g1, g2)].add(c2)
+                for (i, j) in (m1 if shared_mz is not None else s1):
+                    if shared_mz is not None:
+                        l1, l2 = m1[(i, j)], m2.get((i, j), 0.0)
+                    else:
+                        l1 = float(sum(size_db.get(c, 0.0) for c in s1[(i, j)]))
+                        l2 = float(sum(size_db.get(c, 0.0) for c in s2.get((i, j), set())))
                     o1 = l1 / group_lengths[i] if group_lengths[i] > 0 else 0
                     o2 = l2 / group_lengths[j] if group_lengths[j] > 0 else 0
                     if o1 > min_allelic_overlap or o2 > min_allelic_overlap:
@@ -815,14 +833,21 @@ class HyperPartition:
         self.K = [[vi[x] for x in grp if x in vi] for grp in groups]
         self.K = sorted([g for g in self.K if g], key=lambda x: vertices_idx_sizes.loc[x]['length'].sum(), reverse=True)
         allelic_idx_set = getattr(self, "allelic_idx_set", None)
+        at_df = None
         if allelic_idx_set is None:
-            if self.alleletable is not None:
-                raise NotImplementedError("merge_cluster with an allele table weighs group overlaps by shared minimizers "
-                                          "(_merge(alleletable_df=...), hyperpartition.py:2696-2715): not implemented; pass "
-                                          "a prune table instead")
-            allelic_idx_set = set()
+            if self.alleletable is not None:                                               # :2696-2705
+                at_df = _allele_frame(self.alleletable)
+                at_df = at_df[at_df['similarity'] >= 0.85].copy()
+                at_df[1] = at_df[1].map(vi.get)
+                at_df[2] = at_df[2].map(vi.get)
+                at_df = at_df.dropna(subset=[1, 2])
+                at_df[1] = at_df[1].astype(int); at_df[2] = at_df[2].astype(int)
+                allelic_idx_set = set(map(tuple, at_df[[1, 2]].values))
+            else:
+                allelic_idx_set = set()
         self.K = HyperPartition._merge(A, self.K, vertices_idx_sizes, self.k[0], allelic_idx_set=allelic_idx_set,
-                                       min_allelic_overlap=0.8, allele_use_method="merge", method='sum')
+                                       alleletable_df=at_df, min_allelic_overlap=0.8, allele_use_method="merge",
+                                       method='sum')
         self.K = sorted(self.K, key=lambda x: vertices_idx_sizes.loc[x]['length'].sum(), reverse=True)
         return self.K
 

@@ -182,3 +182,45 @@ def test_rescue_static_matches_reference(setup):
     assert nr == nd and nr > 20
     assert [list(map(int, k)) for k in Kr] == [list(map(int, k)) for k in Kd]
     assert any(set(map(int, c1)) - set(x for k in Kd for x in k))        # the constraints did hold something back
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("use_mode", ["merge", "conflict"])
+def test_merge_with_allele_table_matches_reference(setup, use_mode):
+    """_merge(alleletable_df=...) (hyperpartition.py:2288-2471): group overlaps weighed in shared minimizers, the form the
+    first round takes with the CLI defaults and an allele table (:1987-1995) -- the reference's own static method on the
+    scipy A against the drop-in's (V = M^T A M from the device, rank-1 updates)."""
+    rhp, mgd = reference_module()
+    from scipy.sparse import csr_matrix
+    from cphasing_b200 import synth
+    from cphasing_b200.algorithms import hypergraph as ah
+    from cphasing_b200.hyperpartition import HyperPartition
+    g, edges, sizes, ptf, wd, _ = setup
+    HG = ah.HyperGraph(edges, min_quality=1)
+    H = HG.incidence_matrix(min_contacts=5)
+    A = ah.HyperGraph.clique_expansion_init(H, min_weight=1.0)
+    n = A.shape[0]
+    name_idx = {c: i for i, c in enumerate(HG.nodes)}
+    truth = np.array([g.group[g.contig_idx[c]] for c in HG.nodes])
+    rng = np.random.default_rng(7)
+    K0 = []
+    for t in np.unique(truth):                                  # every planted group in two random pieces
+        m = np.where(truth == t)[0]
+        cut = rng.random(len(m)) < 0.5
+        K0 += [m[cut].tolist(), m[~cut].tolist()]
+    K0 = [k for k in K0 if k]
+    rows = [(name_idx[g.names[a]], name_idx[g.names[b]], m1, sh) for a, b, m1, m2, sh, sim in synth.allele_pairs(g, seed=3)
+            if g.names[a] in name_idx and g.names[b] in name_idx]
+    at_df = pd.DataFrame(rows, columns=[1, 2, "mz1", "mzShared"])
+    aset = set(map(tuple, at_df[[1, 2]].values))
+    vsz = pd.DataFrame({"length": {i: float(g.contigsizes[c]) for i, c in enumerate(HG.nodes)}})
+    k = len(np.unique(truth))
+    with contextlib.redirect_stderr(io.StringIO()):
+        Kr = rhp.HyperPartition._merge(csr_matrix(A), [list(x) for x in K0], vsz, k, allelic_idx_set=aset,
+                                       alleletable_df=at_df.copy(), min_allelic_overlap=0.8 if use_mode == "merge" else 0.1,
+                                       allele_use_method=use_mode, method="sum")
+    Kd = HyperPartition._merge(A, [list(x) for x in K0], vsz, k, allelic_idx_set=aset, alleletable_df=at_df.copy(),
+                               min_allelic_overlap=0.8 if use_mode == "merge" else 0.1, allele_use_method=use_mode,
+                               method="sum")
+    assert len(Kr) == len(Kd) == k
+    assert {frozenset(map(int, x)) for x in Kr} == {frozenset(map(int, x)) for x in Kd}
