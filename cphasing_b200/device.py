@@ -488,8 +488,10 @@ def sub_incidence(H: DeviceH, idx, col_min=2) -> DeviceH:
     idx_t = to_dev(np.asarray(idx, dtype=np.int64), torch.int64, dev)
     row_map = torch.full((H.n_rows,), -1, dtype=torch.int32, device=dev)
     row_map[idx_t] = torch.arange(idx_t.numel(), dtype=torch.int32, device=dev)
-    return _incidence_build(H.pem_row, None, H.pem_pk, None, H.nnz, H.n_rows, 0, row_map, int(idx_t.numel()), col_min,
-                            True, None, None, H.n_cols)
+    sub = _incidence_build(H.pem_row, None, H.pem_pk, None, H.nnz, H.n_rows, 0, row_map, int(idx_t.numel()), col_min,
+                           True, None, None, H.n_cols)
+    sub.column_shard = getattr(H, "column_shard", False)      # rows of a shard are a shard (the column filter is column-local)
+    return sub
 
 
 # ------------------------------------------------------------------------------------------------

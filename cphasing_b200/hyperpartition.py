@@ -79,7 +79,8 @@ class HyperPartition:
                  init_resolution2=0.8, min_weight=1.0, min_cis_weight=1.0, cluster_method='louvain', min_quality1=1,
                  min_quality2=2, mapq_filter_1_to_2=False, min_scaffold_length=10000, is_remove_misassembly=False,
                  is_recluster_contigs=False, disable_recluster_by_linkage=False, refine=False,
-                 collapsed_contigs_df=None, threshold=0.01, max_round=1, threads=4, chunksize=None, **kw):
+                 collapsed_contigs_df=None, threshold=0.01, max_round=1, threads=4, chunksize=None, column_shard=False,
+                 **kw):
         if ultra_long is not None or chunksize:
             raise NotImplementedError("ultra-long edges / chunked H are outside the accelerated path")
         if is_remove_misassembly or is_recluster_contigs or refine or collapsed_contigs_df is not None:
@@ -135,6 +136,13 @@ class HyperPartition:
         else:
             self.HG = HyperGraph(self.edges, min_quality=self.min_quality2,
                                  mapq_filter=self.min_quality2 > self.min_quality1)
+        # one process per GPU, `edges` = the hyperedges of this rank's concatemer range (not in the reference, which is one
+        # process): H stays the rank's column shard, every A is summed over the ranks, and the decisions that follow (kprune,
+        # clustering, merges) run identically on every rank -- the kernels are deterministic, so all ranks end with the same K
+        self.column_shard = bool(column_shard)
+        self.HG.column_shard = self.column_shard
+        if self.column_shard and self.max_round > 1:
+            raise NotImplementedError("column_shard with max_round > 1: the IRMM re-weighting rounds need the whole H")
         self.filter_hypergraph()
         self.H, self.vertices = self.get_hypergraph()
         self.NW = self.get_normalize_weight() if self.normalize else None
@@ -198,6 +206,9 @@ class HyperPartition:
         from ._lib import check, lib, stream
         check(lib().cph_row_sums(ptr(dH.pem_row), ptr(dH.pem_pk), None, dH.nnz, max(dH.n_rows, 1), 0, None, 1, ptr(rs),
                                  None, stream()))
+        if getattr(dH, "column_shard", False):
+            from . import parallel as par
+            par.sum_vector(rs)
         deg = rs[:dH.n_rows].cpu().numpy().astype(np.float64)                         # H.sum(axis=1)
         deg[deg <= 0] = 1.0
         global_density = np.sum(deg) / np.sum(a)
@@ -535,6 +546,7 @@ class HyperPartition:
             itv = self.idx_to_vertices
             tmp_K = [[itv[x] for x in grp] for grp in self.K]
             self.HG = HyperGraph(self.edges, min_quality=self.min_quality2)
+            self.HG.column_shard = self.column_shard
             self.filter_hypergraph()
             self.H, self.vertices = self.get_hypergraph()
             raw_A = HyperGraph.clique_expansion_init(self.H, min_weight=self.min_weight, use_high_order=False)
@@ -557,7 +569,7 @@ class HyperPartition:
         # are all-gathered, so every rank ends with the same K.  `fan_out_groups = False` keeps everything on one rank.
         from . import parallel as par
         rank, world = par.world()
-        fan = world > 1 and getattr(self, "fan_out_groups", True)
+        fan = world > 1 and getattr(self, "fan_out_groups", True) and not self.column_shard   # shards: every rank, every group
         jobs = []
         for num, sub_k in enumerate(self.K, 1):
             if self.exclude_group_to_second and num in self.exclude_group_to_second:
@@ -638,6 +650,9 @@ class HyperPartition:
         rowsq = torch.empty(max(sub.n_rows, 1), dtype=torch.int64, device=sub.device)
         from ._lib import check, lib, stream
         check(lib().cph_row_sq_sums(ptr(sub.indptr), ptr(sub.pk), max(sub.n_rows, 1), ptr(rowsq), stream()))
+        if getattr(sub, "column_shard", False):
+            from . import parallel as par
+            par.sum_vector(rowsq)
         dia = rowsq[:sub.n_rows].cpu().numpy().astype(np.float64)
         retain_mask = dia >= min_cis_weight
         raw_contig_counts = len(K)
