@@ -490,3 +490,30 @@ def test_binned_expansion_is_bit_identical(api, use_high_order, form, monkeypatc
     assert torch.equal(a1.diag, a2.diag)
     assert torch.equal(a1.acc, a2.acc)
     assert int((a1.acc != 0).sum().item()) > 1_000_000
+
+
+@pytest.mark.parametrize("longest", [64, 65, 90])
+def test_swept_expansion_run_length_boundary(api, longest, monkeypatch):
+    """the swept form holds hyperedge runs of up to 64 entries in its halo; a longer run raises the device flag and the call
+    falls back to the direct kernel -- either way triangle and diagonal equal the direct kernel's"""
+    ah, _, D, _ = api
+    import torch
+    from scipy.sparse import csr_matrix
+    rng = np.random.default_rng(longest)
+    n, m = 300, 4000
+    k = rng.integers(2, 9, size=m)
+    k[17] = longest                                      # one long hyperedge in the middle of a tile
+    k[m - 1] = min(longest, 64)                          # and one at the very end
+    cols = np.repeat(np.arange(m), k)
+    rows = np.concatenate([rng.choice(n, size=x, replace=False) for x in k])
+    data = rng.integers(1, 4, size=rows.size).astype(np.float32)
+    H = ah.upload_incidence(csr_matrix((data, (rows, cols)), shape=(n, m)))
+    monkeypatch.setenv("CPH_EXPAND_FORM", "direct")
+    ref = D.expand_accumulate(H, use_high_order=True)
+    monkeypatch.setenv("CPH_EXPAND_FORM", "swept")
+    monkeypatch.setenv("CPH_BAND_MB", "0.05")
+    l0 = __import__("cphasing_b200")._lib.launches()
+    got = D.expand_accumulate(H, use_high_order=True)
+    launches = __import__("cphasing_b200")._lib.launches() - l0
+    assert torch.equal(got.acc, ref.acc) and torch.equal(got.diag, ref.diag)
+    assert launches >= 5                                  # the band passes did run (and, beyond 64, the direct kernel after them)
