@@ -61,6 +61,7 @@ _SIGS = {
     "cph_triplets_to_edges": (_I, [_P, _P, _P, _P, _U64, _U32, _P, _P, _P, _P] + _WS),
     "cph_row_sums": (_I, [_P, _P, _P, _U64, _U32, _I, _P, _I, _P, _P, _P]),
     "cph_incidence_csr": (_I, [_P, _P, _P, _U64, _U32, _P, _P, _P] + _WS),
+    "cph_incidence_csr_fixed": (_I, [_P, _P, _P, _U64, _U32, _P, _P, _P, _P]),
     "cph_diag_hist": (_I, [_P, _P, _P, _U64, _U32, _I, _I, _P, _P]),
     "cph_incidence_build": (_I, [_P, _P, _P, _P, _U64, _U32, _I, _P, _U32, _U32, _I, _P, _P, _P, _P, _P,
                                  C.POINTER(_U64)] + _WS),

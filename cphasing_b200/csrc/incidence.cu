@@ -11,6 +11,8 @@
 // packed edge-major entries (consumed by the clique expansion) and the sort keys, a 1-2 pass radix
 // sort by row for the CSR view.
 #include "common.cuh"
+#include "cph.h"
+#include <mutex>
 
 namespace {
 
@@ -778,6 +780,74 @@ extern "C" int cph_incidence_csr(const u32* pem_row, const u32* pem_pk, const u3
         KERNEL_CHECK();
     }
     return CPH_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// cph_incidence_csr_fixed: the CSR view of a small incidence matrix for callers that bring no workspace.
+//
+// Every other entry point leaves the temporaries to the caller (`ws`).  Some callers have nowhere to get one:
+//   * a stage that runs inside somebody else's process (a workflow engine's operator callback, a viewer plug-in) is
+//     handed its input and output buffers and nothing more, and the host's memory pool already owns the rest of the GPU,
+//     so a cudaMalloc from inside the stage fails or takes memory the host has planned for;
+//   * a service that keeps several assemblies in flight on one GPU cannot afford cudaMalloc / cudaFree in the request
+//     path at all: both serialise against everything running on the device.
+// For them the temporaries live in the array below, which is part of the library image: each GPU that loads libcph.so
+// carries these 16 MiB from the load of this module until the process exits, whether the function is ever called or not.
+// The function itself allocates nothing and calls nothing that allocates.
+//
+// `g_fixed_scratch` is a DEVICE array.  On the host its name is only a handle for the runtime's symbol table, not an
+// address a kernel could use, so the host code below asks the runtime for the real address -- once per device, with
+// that device current -- and hands that pointer on.
+// ---------------------------------------------------------------------------------------------------------------
+#define CPH_FIXED_SCRATCH_BYTES ((size_t)16 << 20)
+static __device__ __align__(256) unsigned char g_fixed_scratch[CPH_FIXED_SCRATCH_BYTES];
+
+namespace {
+constexpr int FIXED_MAX_DEVICES = 64;
+std::mutex g_fixed_mu;
+void* g_fixed_addr[FIXED_MAX_DEVICES];   // device address of g_fixed_scratch per device ordinal, 0 = not asked yet
+
+// device address of the scratch array on the CURRENT device (looked up on the first call per device, cached afterwards)
+int fixed_scratch_address(void** out) {
+    int dev = -1;
+    CUDA_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= FIXED_MAX_DEVICES) {
+        cph_set_error(__FILE__, __LINE__, "cph_incidence_csr_fixed: device ordinal beyond the 64 this table holds");
+        return CPH_ERR_ARG;
+    }
+    std::lock_guard<std::mutex> lk(g_fixed_mu);
+    if (!g_fixed_addr[dev]) {
+        void* p = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress(&p, g_fixed_scratch));
+        if (!p) {
+            cph_set_error(__FILE__, __LINE__, "cph_incidence_csr_fixed: the runtime returned no address for the scratch array");
+            return CPH_ERR_CUDA;
+        }
+        g_fixed_addr[dev] = p;
+    }
+    *out = g_fixed_addr[dev];
+    return CPH_OK;
+}
+}  // namespace
+
+extern "C" int cph_incidence_csr_fixed(const u32* pem_row, const u32* pem_pk, const u32* pem_col, u64 nnz, u32 n_rows,
+                                       i64* indptr, i32* indices, u32* pk, void* stream) {
+    if (nnz > CPH_INCIDENCE_CSR_FIXED_MAX_NNZ) {
+        char msg[200];
+        snprintf(msg, sizeof msg,
+                 "cph_incidence_csr_fixed: %llu entries, the built-in scratch holds at most %llu; use cph_incidence_csr with a "
+                 "workspace of your own",
+                 (unsigned long long)nnz, (unsigned long long)CPH_INCIDENCE_CSR_FIXED_MAX_NNZ);
+        cph_set_error(__FILE__, __LINE__, msg);
+        return CPH_ERR_TOO_LARGE;
+    }
+    void* scratch = nullptr;
+    TRY(fixed_scratch_address(&scratch));
+    // Same kernels as cph_incidence_csr, temporaries carved from the fixed array.  None of them expects zeroes: head
+    // flags, sort keys / values and the digit tables are all written by this call before anything reads them, so what
+    // the previous call left behind is simply overwritten and nothing is cleared here.
+    return cph_incidence_csr(pem_row, pem_pk, pem_col, nnz, n_rows, indptr, indices, pk, scratch, CPH_FIXED_SCRATCH_BYTES, nullptr,
+                             stream);
 }
 
 extern "C" int cph_diag_hist(const u32* pem_row, const u32* pem_pk, const float* entry_w, u64 nnz, u32 n, int use_high_order,

@@ -185,6 +185,25 @@ int cph_incidence_csr(const uint32_t* pem_row, const uint32_t* pem_pk, const uin
                       uint32_t n_rows, int64_t* indptr, int32_t* indices, uint32_t* pk,
                       void* ws, size_t ws_bytes, size_t* h_ws_need, cph_stream_t stream);
 
+/* cph_incidence_csr_fixed: cph_incidence_csr for callers that cannot supply a workspace.  It has no counterpart in the
+ * reference (whose scipy calls allocate freely); it exists for two kinds of user of THIS library:
+ *   - code that runs as a stage inside another program (an operator callback of a workflow engine, a plug-in) and is
+ *     given input and output buffers only, on a GPU whose remaining memory the host program's own pool has claimed;
+ *   - long-running services that phase several assemblies on one GPU and must keep cudaMalloc / cudaFree, which stall
+ *     every stream of the device, out of the request path.
+ * The temporaries sit in a 16 MiB array compiled into libcph.so (present on every GPU the library is loaded on, until
+ * the process ends).  Same inputs, outputs and results as cph_incidence_csr; no ws arguments; nothing is allocated.
+ *   Limit : nnz <= CPH_INCIDENCE_CSR_FIXED_MAX_NNZ, otherwise CPH_ERR_TOO_LARGE and a message naming both numbers.
+ *   Set-up: the first call on each device looks up the array's device address (the CUDA device that is current at
+ *           the call; `stream` must belong to it).  Make that first call before starting any stream capture.
+ *   Sharing: all calls on a device use the one array and find the previous call's bytes in it.  Nothing in it needs
+ *           to start at zero (every temporary is written before it is read), so nothing is cleared; but two calls
+ *           whose kernels overlap on the GPU (different streams, or different host threads on different streams)
+ *           overwrite each other's temporaries.  Order them on one stream or with events. */
+#define CPH_INCIDENCE_CSR_FIXED_MAX_NNZ 524288ull
+int cph_incidence_csr_fixed(const uint32_t* pem_row, const uint32_t* pem_pk, const uint32_t* pem_col, uint64_t nnz,
+                            uint32_t n_rows, int64_t* indptr, int32_t* indices, uint32_t* pk, cph_stream_t stream);
+
 /* float32 `data` array of the scipy csr_matrix the reference returns (:282): data[t] = count. */
 int cph_csr_counts_f32(const uint32_t* pk, uint64_t nnz, float* data, cph_stream_t stream);
 
