@@ -34,6 +34,8 @@ def to_dev(x, dtype, device):
             torch.float32: np.float32, torch.float64: np.float64, torch.uint8: np.uint8}[dtype]
     if a.dtype != want:
         a = a.astype(want)
+    elif not a.flags.writeable:
+        a = a.copy()       # torch.from_numpy on a read-only array (np.load mmap, pandas views) is undefined once written to
     return torch.from_numpy(a).to(device, non_blocking=True)
 
 
@@ -542,32 +544,57 @@ def sweep_bands(n, band_bytes=None, mean_order=4.0):
     return r0
 
 
-def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, zero, band_hook=None):
+class LocalConsensus:
+    """Choices of the accumulate stage that every rank of a column-shard job must make alike, because they decide which
+    collectives follow and how large they are: direct or swept form, the band size, and whether the packed 4-byte form
+    fits.  One process agrees with itself; parallel.RankConsensus is the several-rank form (all-reduce SUM / MAX)."""
+    world_size = 1
+
+    def sums(self, *vals):
+        return tuple(int(v) for v in vals)
+
+    def any(self, flag):
+        return bool(flag)
+
+
+_LOCAL = LocalConsensus()
+
+
+def expand_accumulate_swept(H: DeviceH, use_high_order, frac_bits, acc, diag, zero, band_hook=None, consensus=None,
+                            mean_order=None):
     """sorted 4-byte entries + one pass per L2-sized row band (expand.cu, swept form).  `band_hook(k, lo, hi, cell_lo,
     cell_hi)` runs after band k was launched (multi-GPU: start that band's exchange).  -> False when the packed form
-    does not fit (the caller falls back)."""
+    does not fit (the caller falls back).  The prep kernel's flag is read (one 4-byte copy) BEFORE any band is launched:
+    a flagged run leaves pe4 slots unwritten, and the band kernel must never walk those.  With several ranks the flag is
+    MAX-reduced first, so either every rank sweeps or none does."""
     dev = H.device
     n = H.n_rows
+    cons = consensus or _LOCAL
     pe4 = torch.empty(max(H.nnz, 1), dtype=torch.int32, device=dev)
     flag = torch.empty(1, dtype=torch.int32, device=dev)
     rc = lib().cph_expand_sweep_prep(ptr(H.pem_row), ptr(H.pem_pk), H.nnz, n, int(use_high_order), ptr(pe4), ptr(flag), stream())
     if rc == _lib.ERR_TOO_LARGE:
         return False
     check(rc)
-    r0 = sweep_bands(n, mean_order=H.nnz / max(H.n_cols, 1))
+    if cons.any(int(flag.item()) != 0):
+        return False
+    if mean_order is None:
+        mean_order = H.nnz / max(H.n_cols, 1)
+    r0 = sweep_bands(n, mean_order=mean_order)
     for k in range(len(r0) - 1):
         lo, hi = r0[k], r0[k + 1]
         check(lib().cph_expand_sweep_band(ptr(pe4), H.nnz, n, lo, hi, int(frac_bits), int(zero), ptr(acc), ptr(diag), stream()))
         if band_hook is not None:
             band_hook(k, lo, hi, lo * (2 * n - lo + 1) // 2, hi * (2 * n - hi + 1) // 2)
-    return int(flag.item()) == 0
+    return True
 
 
 @nvtx("cph:expand_accumulate")
 def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w=None, frac_bits=None,
-                      acc=None, band_hook=None, acc_out=None) -> Accumulator:
+                      acc=None, band_hook=None, acc_out=None, consensus=None) -> Accumulator:
     """fixed-point accumulation of A = H diag(d) H^T (algorithms/hypergraph.py:385-446).  `acc`: add onto an existing
-    triangle; `acc_out`: caller-owned storage for a fresh one; `band_hook`: see expand_accumulate_swept."""
+    triangle; `acc_out`: caller-owned storage for a fresh one; `band_hook`: see expand_accumulate_swept; `consensus`:
+    how the shard-dependent choices (form, band size, packed-form flag) are made the same on every rank (LocalConsensus)."""
     dev = H.device
     n = H.n_rows
     if frac_bits is None:
@@ -583,16 +610,19 @@ def expand_accumulate(H: DeviceH, use_high_order=True, entry_w=None, csr_entry_w
         acc = acc_out if acc_out is not None else torch.empty(max(tri, 1), dtype=torch.int64, device=dev)
     diag = torch.empty(max(n, 1), dtype=torch.int64, device=dev)
     form = os.environ.get("CPH_EXPAND_FORM", "")          # "", "swept", "binned", "direct": A/B switch for measurements
-    big = entry_w is None and n >= BINNED_MIN_N and H.nnz >= BINNED_MIN_NNZ
-    if form == "swept" and entry_w is None:
-        big = True
+    cons = consensus or _LOCAL
+    big, mean_order = False, None
+    if entry_w is None and (n >= BINNED_MIN_N or form == "swept"):     # a condition every rank evaluates alike
+        g_nnz, g_cols = cons.sums(H.nnz, H.n_cols)                     # shard sizes differ: decide on the job's totals
+        mean_order = g_nnz / max(g_cols, 1)
+        big = form == "swept" or g_nnz // cons.world_size >= BINNED_MIN_NNZ
     if big and form != "direct":
         # the packed triangle does not fit in L2: update it region by region (expand.cu: "swept" = sorted 4-byte entries,
         # one streaming pass per row band; "binned" = the round-1 pair records grouped by 2-D block)
         if form != "binned" and n <= SWEEP_MAX_N:
             if not zero:
                 diag.zero_()
-            if expand_accumulate_swept(H, use_high_order, frac_bits, acc, diag, zero, band_hook):
+            if expand_accumulate_swept(H, use_high_order, frac_bits, acc, diag, zero, band_hook, cons, mean_order):
                 return Accumulator(acc, diag, n, int(frac_bits), bool(use_high_order))
             if band_hook is not None:
                 band_hook(-1, 0, 0, 0, 0)        # abandoned: the direct kernel below starts over

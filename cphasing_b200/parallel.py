@@ -124,6 +124,29 @@ def sum_vector(v, group=None):
     return v
 
 
+class RankConsensus:
+    """device.LocalConsensus over a process group.  The accumulate stage picks its form (direct / swept), its band size
+    and its fallback from shard-local numbers (entries, hyperedges, the prep kernel's flag); were each rank to decide
+    alone, ranks near a threshold would issue different collectives (per-band all-reduces of different sizes against a
+    reduce-scatter) and NCCL would hang or add mismatched cells.  Here the numbers are all-reduced first, so the sequence
+    and the sizes of the collectives are the same everywhere."""
+
+    def __init__(self, device, group=None):
+        self.group = group
+        self.world_size = world()[1]
+        self.device = device if dist.get_backend(group) == "nccl" else torch.device("cpu")
+
+    def sums(self, *vals):
+        t = torch.tensor([int(v) for v in vals], dtype=torch.int64, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return tuple(int(v) for v in t.tolist())
+
+    def any(self, flag):
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+        return bool(int(t.item()))
+
+
 def expand_accumulate_sum(H, use_high_order=True, group=None, on_local_done=None):
     """this rank's partial accumulator of A = H W H^T summed over the ranks, in place and identical everywhere
     (exchange 2).  When the accumulator is swept band by band (device.expand_accumulate_swept, n >= 5.6k) the sum of band
@@ -161,7 +184,8 @@ def expand_accumulate_sum(H, use_high_order=True, group=None, on_local_done=None
 
     n = H.n_rows
     holder["acc"] = torch.empty(max(n * (n + 1) // 2, 1), dtype=torch.int64, device=H.device)
-    acc = D.expand_accumulate(H, use_high_order=use_high_order, band_hook=hook, acc_out=holder["acc"])
+    acc = D.expand_accumulate(H, use_high_order=use_high_order, band_hook=hook, acc_out=holder["acc"],
+                              consensus=RankConsensus(H.device, group))
     if on_local_done:
         on_local_done()
     if bands and overlap:

@@ -516,4 +516,7 @@ def test_swept_expansion_run_length_boundary(api, longest, monkeypatch):
     got = D.expand_accumulate(H, use_high_order=True)
     launches = __import__("cphasing_b200")._lib.launches() - l0
     assert torch.equal(got.acc, ref.acc) and torch.equal(got.diag, ref.diag)
-    assert launches >= 5                                  # the band passes did run (and, beyond 64, the direct kernel after them)
+    if longest <= 64:
+        assert launches >= 5                              # the band passes did run
+    else:
+        assert launches <= 3                              # flag read before any band: prep, then the direct kernel only

@@ -211,3 +211,40 @@ def test_band_by_band_exchange_sums_every_cell_once():
         assert torch.equal(acc, torch.arange(tri, dtype=torch.int64) * 3)      # (1 + 2) x the cell's own index
         assert torch.equal(diag, torch.full((n,), 3, dtype=torch.int64))
         assert nm == 1
+
+
+def _consensus_worker(rank, ws, port, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=ws)
+    try:
+        c = par.RankConsensus(torch.device("cpu"))
+        # shard sizes on either side of a threshold, a flag raised on one rank only
+        q.put((rank, c.world_size, c.sums(100 + rank, 7), c.any(rank == 1), c.any(False)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_rank_consensus_gives_every_rank_the_same_answer():
+    """the form / band-size / fallback choices of the accumulate stage are taken on all-reduced numbers (ADVICE r2:
+    rank-local choices could issue mismatched collectives)"""
+    ws = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_consensus_worker, args=(r, ws, port, q)) for r in range(ws)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(ws)]
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    for rank, w, sums, flagged, clean in res:
+        assert w == 2 and sums == (201, 14) and flagged is True and clean is False
+
+
+def test_local_consensus_is_the_identity():
+    from cphasing_b200 import device as D
+    c = D.LocalConsensus()
+    assert c.world_size == 1 and c.sums(5, 6) == (5, 6) and c.any(0) is False and c.any(3) is True
