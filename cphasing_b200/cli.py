@@ -79,9 +79,13 @@ def split_contigs(sizes, split_length, trim_length=0):
     return pd.DataFrame({"length": lens}, index=pd.Index(names, name="contig")), first
 
 
-def _extract(args, sizes):
-    """-> (extractor, contig sizes actually indexed: the split bins when --split-length is on)"""
-    from . import hypergraph as hg
+def _index_contigs(args, sizes):
+    """which contigs (or split bins) get a row of H, and in which order -> (sizes of the indexed rows, name -> row,
+    split length or None, dict original contig -> row of its first bin or None).
+    As in the reference's `hypergraph` command (cli.py:3885-3908) the whitelist only acts when the contigs are NOT split:
+    with `--split-length` the reference replaces the contig list by ALL split bins after the whitelist was applied, and
+    the row of an alignment is `first bin of its contig + mid // split_length` in that unfiltered numbering, so filtering
+    the bins afterwards would put alignments into the wrong rows."""
     sl = getattr(args, "split_length", "none")
     if sl is None or str(sl).lower() in ("none", "no", "null", "0"):
         sl = None
@@ -91,13 +95,23 @@ def _extract(args, sizes):
     else:
         sl = _size(sl)
     boundarys = None
+    wl = getattr(args, "extract_whitelist", None)
     if sl:
         sizes, boundarys = split_contigs(sizes, sl, trim_length=getattr(args, "alleles_trim_length", 0) or 0)
-    wl = getattr(args, "extract_whitelist", None)
-    if wl:                                                                      # cli.py hypergraph: only whitelisted contigs are indexed
+        if wl:
+            logger.warning("--whitelist has no effect together with --split-length (every split bin is indexed, as in the "
+                           "reference)")
+    elif wl:                                                                    # cli.py:3890-3892: only whitelisted contigs are indexed
         keep = {l.strip() for l in open(wl) if l.strip()}
-        sizes = sizes[[c.split("|")[0] in keep for c in sizes.index]]
+        sizes = sizes[[c in keep for c in sizes.index]]
     idx = {c: i for i, c in enumerate(sizes.index)}
+    return sizes, idx, sl, boundarys
+
+
+def _extract(args, sizes):
+    """-> (extractor, contig sizes actually indexed: the split bins when --split-length is on)"""
+    from . import hypergraph as hg
+    sizes, idx, sl, boundarys = _index_contigs(args, sizes)
     sz = sizes["length"].to_dict()
     el = _size(args.edge_length) if str(args.edge_length).lower() not in ("none", "", "0") else 0
     tables = [args.table]
@@ -311,7 +325,8 @@ def build_parser():
     k.add_argument("alleletable", metavar="AlleleTable")
     k.add_argument("contacts", metavar="INPUT_CONTACTS_PATH")
     k.add_argument("-o", "--output", default="prune.contig.table")
-    k.add_argument("-m", "--method", choices=["fast", "precise", "greedy"], default="precise")
+    k.add_argument("-m", "--method", choices=["fast", "precise"], default="precise",
+                   help="`greedy` exists only inside the cphasing-rs binary (parity unpinned) and is not offered")
     k.add_argument("-fc", "--first-cluster", dest="first_cluster", default=None)
     k.add_argument("-cr", "--countre", "--count-re", dest="count_re", default=None)
     k.add_argument("-n", "--norm-method", dest="norm_method", choices=["none", "cis", "cis_unique", "auto"], default="none")

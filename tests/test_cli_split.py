@@ -41,3 +41,28 @@ def test_split_and_auto_rule_match_reference():
             assert list(mine["length"]) == list((ref["end"] - ref["start"]).astype(int))
             assert first == ref.reset_index().groupby("chrom")["index"].apply(lambda x: x.min()).to_dict()
     assert None in seen_auto and len(seen_auto) > 1
+
+
+def test_whitelist_and_split_length_together(tmp_path):
+    """`hypergraph -sl N -wl file`: the rows are the split bins of EVERY contig (the reference overwrites the whitelisted
+    list with all bins, cli.py:3890-3906) and each contig's first-bin index points into that same numbering; without
+    splitting the whitelist selects the indexed contigs."""
+    from types import SimpleNamespace
+    from cphasing_b200 import cli
+    sizes = pd.DataFrame({"length": [2_500_000, 900_000, 4_100_000]}, index=pd.Index(["ctgB", "ctgA", "ctgC"], name="contig"))
+    wl = tmp_path / "wl.txt"
+    wl.write_text("ctgC\nctgA\n")
+    a = SimpleNamespace(split_length="1m", extract_whitelist=str(wl), alleles_trim_length=0)
+    sz, idx, sl, first = cli._index_contigs(a, sizes)
+    assert sl == 1_000_000
+    assert list(sz.index) == ["ctgA|0_900000", "ctgB|0_1000000", "ctgB|1000000_2000000", "ctgB|2000000_2500000",
+                              "ctgC|0_1000000", "ctgC|1000000_2000000", "ctgC|2000000_3000000", "ctgC|3000000_4000000",
+                              "ctgC|4000000_4100000"]
+    assert first == {"ctgA": 0, "ctgB": 1, "ctgC": 4}
+    for c, f in first.items():                        # row of an alignment = first[c] + mid // sl lands on a bin of c
+        nb = -(-int(sizes.loc[c, "length"]) // sl)
+        assert all(sz.index[f + k].split("|")[0] == c for k in range(nb))
+        assert idx[sz.index[f]] == f
+    b = SimpleNamespace(split_length="none", extract_whitelist=str(wl), alleles_trim_length=0)
+    sz, idx, sl, first = cli._index_contigs(b, sizes)
+    assert sl is None and first is None and list(sz.index) == ["ctgA", "ctgC"] and idx == {"ctgA": 0, "ctgC": 1}
