@@ -163,13 +163,18 @@ class HyperExtractor:
                     "mapq": df["mapq"].to_numpy(), "start": df["start"].to_numpy(), "end": df["end"].to_numpy()}
         from . import ingest
         cols, bad = ingest.read_table(path, ingest.POREC_FIELDS, self.names, threads=max(int(self.threads or 1), 1))
-        self._check_table(path, cols, bad)
+        self._check_table(path, len(cols["read_idx"]), bad)
         return cols
 
     @staticmethod
-    def _check_table(path, cols, bad):
-        if bad or len(cols["read_idx"]) == 0:
-            logger.error(f"The pore-c table `{path}` is empty or malformed, please check it.")       # :1621-1630
+    def _check_table(path, n_rows, bad):
+        """stop (exit status -1 like hypergraph.py:1621-1630) on a table that cannot be used, saying which of the two it is"""
+        if bad:
+            logger.error(f"The pore-c table `{path}` holds {bad} malformed line(s) (fewer than 9 tab-separated columns, or a "
+                         "non-numeric read_idx / start / end / mapping_quality), please check it.")
+            sys.exit(-1)
+        if n_rows == 0:
+            logger.error(f"The pore-c table `{path}` is empty, please check it.")
             sys.exit(-1)
 
     def _stream(self, path):
@@ -177,10 +182,11 @@ class HyperExtractor:
         (cphasing_b200/ingest.py).  Yields column dicts; raises _NotGrouped when the file is not ordered by read id (the
         group-by of chunk k would then miss records that come later) -- the caller falls back to `_load`."""
         from . import ingest
-        carry, last, total, nbad = None, -1, 0, 0
+        carry, last, total = None, -1, 0
         for cols, bad in ingest.read_table_chunks(path, ingest.POREC_FIELDS, self.names,
                                                   threads=max(int(self.threads or 1), 1)):
-            nbad += bad
+            if bad:                      # fail at the first bad block, before more chunks are grouped on the GPU
+                self._check_table(path, 1, bad)
             r = cols["read_idx"]
             if len(r) == 0:
                 continue
@@ -198,7 +204,7 @@ class HyperExtractor:
         if carry is not None and len(carry["read_idx"]):
             total += len(carry["read_idx"])
             yield carry
-        self._check_table(path, {"read_idx": np.empty(total, dtype=np.uint8)}, nbad)
+        self._check_table(path, total, 0)
 
     def _edges_of(self, t, n, ln, offset):
         return D.porec_to_edges(t["read_idx"], t["contig"], t["mapq"], n, start=t.get("start"), end=t.get("end"),
@@ -299,7 +305,12 @@ class Extractor:
             return [ingest.read_pqs_chunk(f, lut, self.min_mapq, with_mapq) for f in files]
         # 4DN pairs columns (hypergraph.py:904-909): chrom1(1) pos1(2) chrom2(3) pos2(4) mapq(7)
         cols, bad = ingest.read_table(path, ingest.PAIRS_FIELDS, self.names, threads=max(int(getattr(self, "threads", 4) or 1), 1))
-        if bad or len(cols["mapq"]) == 0:
+        if bad:
+            logger.error(f"The pairs `{path}` holds {bad} line(s) without the columns this step reads (chrom1, pos1, chrom2, "
+                         "pos2 in columns 2-5 and the mapq in column 8: a 7-column pairs file has no mapq) or with "
+                         "non-numeric values in them, please check it.")
+            sys.exit(-1)
+        if len(cols["mapq"]) == 0:
             logger.error(f"The pairs `{path}` is empty, can not load anything, please check it.")
             sys.exit(-1)
         return [cols]

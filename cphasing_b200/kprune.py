@@ -309,8 +309,12 @@ class KPrunerRust:
     """Same constructor and `run()` as the reference's wrapper of the `cphasing-rs kprune` binary (kprune.py:51-85), but the
     scoring runs in-process on the device (csrc/kprune.cu) and no subprocess is started."""
     METHODS = {"fast": 1, "precise": 5}          # alleles per contig that enter the score block (KP_MAXL - 1 = 5)
+    # DEVIATION, on purpose: the reference's constructor defaults to method="greedy" (kprune.py:57), which only the
+    # cphasing-rs binary defines (PARITY UNPINNED, DESIGN.md 2).  Defaulting to it would make `KPrunerRust(at, contacts)`
+    # -- how reference-style callers construct it -- raise; the default here is `precise`, the command line's own default
+    # (cli.py:3601), and an explicit method="greedy" still refuses loudly.
 
-    def __init__(self, alleletable, contacts, output="prune.contig.table", method="greedy", first_cluster=None, count_re=None,
+    def __init__(self, alleletable, contacts, output="prune.contig.table", method="precise", first_cluster=None, count_re=None,
                  whitelist=None, norm_method="none", threads=4, log_dir="logs"):
         self.alleletable = alleletable
         self.contacts = contacts
