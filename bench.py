@@ -43,7 +43,10 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-partition", action="store_true", help="skip the kprune + clustering tail (hyperpartition wall s)")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra workloads (D and E shards) after the headline one")
-    ap.add_argument("--extra", default="D,E", help="comma-separated extra workloads, each at 1/8 of its named size per GPU")
+    ap.add_argument("--extra", default="B,D,E", help="comma-separated extra workloads: D and E at 1/8 of the named size per GPU, "
+                                                     "B (Hi-C pairs) at its full 100 M pairs per GPU")
+    ap.add_argument("--extra-parity-sample", type=int, default=2_000_000,
+                    help="concatemers of each extra workload that the CPU path recomputes for the parity check (E: half of it)")
     ap.add_argument("--extra-steps", type=int, default=5)
     return ap.parse_args()
 
@@ -381,6 +384,8 @@ def parity_check(D, cfg, g, host, dev_t, H_cpu, A_cpu, ah):
                             D.to_host(H.indptr)), shape=(H.n_rows, H.n_cols)))
     Hc = _canon(H_cpu)
     out = {"sample_concatemers": None, "H_shape": list(Hs.shape), "H_nnz": int(Hs.nnz)}
+    out["expansion_form"] = "swept row bands (sw_prep + sw_band)" if (H.n_rows >= D.BINNED_MIN_N and H.nnz >= D.BINNED_MIN_NNZ) \
+        else "direct (expand_diag_kernel)"
     out["H_bit_exact"] = bool(Hs.shape == Hc.shape and np.array_equal(Hs.indptr, Hc.indptr)
                               and np.array_equal(Hs.indices, Hc.indices) and np.array_equal(Hs.data, Hc.data))
     # integer contact counts (use_high_order=False): bit-exact against the CPU integer matrix
@@ -643,8 +648,9 @@ def run_own(args):
         par_["cpu_side"] = cb["kind"]
         out["parity"] = par_
         parity_ok = par_["ok"]
-    # ---- extra workloads, driver-timed next to the headline one: D (north_star's 8-GPU config: n = 20k, 62.5 M
-    # concatemers per GPU = 500 M at N = 8) and E (high-order HiFi-C: n = 10k, order <= 50, 25 M per GPU = 200 M at N = 8)
+    # ---- extra workloads, driver-timed next to the headline one: B (Hi-C pairs: n = 1k, 100 M pairs per GPU), D
+    # (north_star's 8-GPU config: n = 20k, 62.5 M concatemers per GPU = 500 M at N = 8) and E (high-order HiFi-C: n = 10k,
+    # order <= 50, 25 M per GPU = 200 M at N = 8), each with its own parity check against the CPU path at N = 1
     if not args.no_extra and args.workload is None and not args.m:
         import gc
         from cphasing_b200 import synth
@@ -654,13 +660,29 @@ def run_own(args):
         extra = {}
         for xn in args.extra.split(","):
             xcfg = dict(synth.CONFIGS[xn])
-            xcfg["m"] = xcfg["m"] // 8
+            if xn in ("D", "E"):
+                xcfg["m"] = xcfg["m"] // 8
             try:
                 xg, xt = gen_table(xcfg, rank, dev)
                 xo, xraw, xH, xA = timed_run(D, _lib, xn, xcfg, xg, xt, args.extra_steps, 3, world, rank, local, dev, barrier,
                                              clocks_on=False)
-                del xraw, xt
-                if not args.no_partition:
+                del xraw
+                if rank == 0 and world == 1 and not args.no_cpu_baseline:
+                    # parity at the benched shape: the CPU path recomputes a sample of THIS table (n = 20k swept bands
+                    # for D, orders up to 50 for E, duplicated intra-contig pairs for B); rc != 0 on mismatch as for C
+                    ah_x = reference_module()
+                    ks = args.extra_parity_sample // 2 if xn == "E" else args.extra_parity_sample
+                    xhost, xdev, xk = sample_of(xcfg, xt, ks)
+                    xcb, xHc, xAc = cpu_baseline(xcfg, xg, xhost, xk, ah_x)
+                    xpar = parity_check(D, xcfg, xg, xhost, xdev, xHc, xAc, ah_x)
+                    xpar["sample_concatemers"] = xk
+                    xpar["cpu_side"] = xcb["kind"]
+                    xo["cpu_baseline"] = xcb
+                    xo["parity"] = xpar
+                    parity_ok = parity_ok and xpar["ok"]
+                    del xhost, xdev, xHc, xAc
+                del xt
+                if not args.no_partition and xcfg["kind"] != "pairs":      # the tail needs an allele table: Pore-C configs only
                     tail = partition_tail(D, xcfg, xg, xH, xA, reps=1, world=world, rank=rank)
                     barrier()
                     if rank == 0:

@@ -3,7 +3,7 @@
 on noisy inputs (no clear optimum: sequential and phased sweeps end in different local optima, as two igraph seeds
 do) the GPU result must not fall more than 1 % of |Q| below the oracle's (measured on B200 over 30 noisy cases with the
 adaptive phase count: 28 within -0.2 % .. +3.8 %, two at -1.8 % / -2.1 %, profiles/r2u_community_tiny.txt; with a fixed 8
-phases it was -6.8 %).
+phases it was -6.8 %).  The two violators (n = 2 000, gamma = 1) are in this file as strict expected failures.
 With one vertex per phase the device sweep IS the oracle's sequential sweep and must reproduce its partition."""
 import numpy as np
 import pytest
@@ -77,6 +77,28 @@ def test_noisy_4000_vertices_within_one_percent(method, gamma, case):
     """the n = 4 000 graphs of profiles/r1c_community_phases.txt (in-group degree 25, out-group degree 78: Q ~ 0.2) and a
     noisier one (Q ~ 0.15), the size of workload C's contig graph"""
     A, truth = noisy_4k(case)
+    mem_o, _ = co.community(A, gamma, method)
+    mem, vc = gpu_cluster(A, gamma, method)
+    q_o = co.modularity(A, mem_o, gamma)
+    q_g = co.modularity(A, mem, gamma)
+    assert q_g >= q_o - 0.01 * abs(q_o), (q_g, q_o)
+
+
+KNOWN_GAP = {("louvain", 1.0): "-1.79 %", ("leiden", 1.0): "-2.08 %"}     # profiles/r2u_community_tiny.txt:8, 11
+
+
+@pytest.mark.parametrize("method,gamma", [
+    pytest.param(m, g_, marks=pytest.mark.xfail(strict=True, reason=f"known violator of the 1 % bound: {KNOWN_GAP[(m, g_)]} "
+                                                                    "of the oracle's Q on B200 (phased sweeps end in a "
+                                                                    "worse local optimum on this graph); kept in the gate "
+                                                                    "so that a fix flips it"))
+    if (m, g_) in KNOWN_GAP else pytest.param(m, g_)
+    for m in ("louvain", "leiden") for g_ in (0.5, 1.0, 2.0)])
+def test_noisy_2000_vertices_within_one_percent(method, gamma):
+    """the n = 2 000 graph of scripts/exp_community2.py (20 groups, in-group degree 10, out-group degree 19: Q ~ 0.28 at
+    gamma = 1).  Four of its six cases hold the 1 % bound; the two at gamma = 1 do NOT (measured -1.8 % / -2.1 %) and are
+    listed as strict expected failures rather than left out: the tolerance of this file is not met everywhere."""
+    A, truth = noisy_4k((2000, 20, 0.1, 0.01, 3))
     mem_o, _ = co.community(A, gamma, method)
     mem, vc = gpu_cluster(A, gamma, method)
     q_o = co.modularity(A, mem_o, gamma)
