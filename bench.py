@@ -776,6 +776,33 @@ def run_reference(args):
         a.send(("stop",))
     v = m / dt
     stage_s = {k_: round(float(np.mean([r[0][k_] for r in res])), 3) for k_ in res[0][0]}
+    for p, _ in procs:
+        p.join(30)
+    # The timed replicas above hold REF_SAMPLE concatemers each, not the 50 M of the named table (hours of CPU time).  To show
+    # what that does to the number, time ONE step of the same path on tables of 1 M, 4 M and 10 M concatemers per replica at
+    # a fixed concurrency of 4 replicas (N = 1 arm only: the other arms of the scaling run would repeat the same figures).
+    size_sweep = None
+    if args.gpus == 1 and not os.environ.get("CPH_REF_NO_SWEEP"):
+        size_sweep = {"replicas": min(4, cores), "unit": "concatemers/s per replica", "per_replica_concatemers": {}}
+        for per_s in (1_000_000, 4_000_000, 10_000_000):
+            ws_ = []
+            for i in range(size_sweep["replicas"]):
+                a, b = ctx.Pipe()
+                p = ctx.Process(target=_ref_worker, args=(b, cfg, i * per_s, per_s), daemon=True)
+                p.start()
+                ws_.append((p, a))
+            for _, a in ws_:
+                a.recv()
+            t1 = time.perf_counter()
+            for _, a in ws_:
+                a.send(("step",))
+            for _, a in ws_:
+                a.recv()
+            d1 = time.perf_counter() - t1
+            for p, a in ws_:
+                a.send(("stop",))
+                p.join(30)
+            size_sweep["per_replica_concatemers"][str(per_s)] = round(per_s / d1, 1)
     what = ("the UNMODIFIED reference (baseline/_ref): HyperEdges -> HyperGraph(mapq_filter=False).incidence_matrix(25) -> "
             "clique_expansion_init(min_weight=2.0), float32 scipy; its polars group-by replaced by the oracle's numpy port "
             "(polars not installable)") if kind == "reference" else "oracle/hypergraph_oracle.py port (reference install absent)"
@@ -789,7 +816,8 @@ def run_reference(args):
                       "config": {"workload": f"{name}: n={cfg['n']} contigs, law={cfg['law']}, kind={cfg['kind']} "
                                              f"(bounded sample: {per} concatemers x {cores} replicas per step)",
                                  "params": PARAMS},
-                      "cpu_baseline": {"value": v, "unit": "concatemers/s", "cores": cores, "kind": kind, "sample": sample},
+                      "cpu_baseline": {"value": v, "unit": "concatemers/s", "cores": cores, "kind": kind, "sample": sample,
+                                       "size_sweep": size_sweep},
                       "e2e": {"value": v, "unit": "concatemers/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
