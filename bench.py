@@ -43,8 +43,9 @@ def parse():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-partition", action="store_true", help="skip the kprune + clustering tail (hyperpartition wall s)")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra workloads (D and E shards) after the headline one")
-    ap.add_argument("--extra", default="B,D,E", help="comma-separated extra workloads: D and E at 1/8 of the named size per GPU, "
-                                                     "B (Hi-C pairs) at its full 100 M pairs per GPU")
+    ap.add_argument("--extra", default="B,Cf,D,E", help="comma-separated extra workloads: D and E at 1/8 of the named size per GPU, "
+                                                        "B (Hi-C pairs) at its full 100 M pairs per GPU, Cf = C with the "
+                                                        "reference's default edge filter (--edge-length 5m, 17 B records)")
     ap.add_argument("--extra-parity-sample", type=int, default=2_000_000,
                     help="concatemers of each extra workload that the CPU path recomputes for the parity check (E: half of it)")
     ap.add_argument("--extra-steps", type=int, default=5)
@@ -125,8 +126,28 @@ def gen_table(cfg, rank, dev):
     if cfg["kind"] == "pairs":
         t = synth.pairs_table_device(g, cfg["m"], cfg["seed"], first=first, device=dev)
     else:
-        t = synth.porec_table_device(g, cfg["m"], cfg["seed"], law=cfg["law"], first=first, device=dev)
+        t = synth.porec_table_device(g, cfg["m"], cfg["seed"], law=cfg["law"], first=first, device=dev,
+                                     positions=bool(cfg.get("edge_length")))
     return g, t
+
+
+_LEN_DEV = {}
+
+
+def edge_filter_args(cfg, g, t, dev=None):
+    """keyword arguments of the reference's edge filter (hypergraph.py:1438-1457; `--edge-length 5m` is the default of
+    `cphasing hyperpartition`, _config.py:37) for D.porec_to_edges / the oracle: {} when the config has it off"""
+    el = int(cfg.get("edge_length") or 0)
+    if not el:
+        return {}
+    if dev is None:
+        return dict(start=t["start"], end=t["end"], contig_len=g.length, edge_length=el)
+    key = (id(g), str(dev))
+    if key not in _LEN_DEV:
+        import torch
+        _LEN_DEV.clear()
+        _LEN_DEV[key] = torch.from_numpy(np.ascontiguousarray(g.length.astype(np.int64))).to(dev)
+    return dict(start=t["start"], end=t["end"], contig_len=_LEN_DEV[key], edge_length=el)
 
 
 def device_step(D, cfg, g, t, ev, world, rank):
@@ -143,7 +164,8 @@ def device_step(D, cfg, g, t, ev, world, rank):
         raw = D.pairs_to_edges(t["chrom1"], t["chrom2"], t["mapq"], g.n, min_mapq=PARAMS["min_mapq"])
     else:
         raw = D.porec_to_edges(t["read_idx"], t["contig_idx"], t["mapq"], g.n, min_mapq=PARAMS["min_mapq"],
-                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"])
+                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"],
+                               **edge_filter_args(cfg, g, t, t["mapq"].device))
     mark("edges")
     from cphasing_b200 import parallel as par
     # exchange 1 (world > 1): global per-contig contact sums + largest count for the min_contacts row filter
@@ -316,7 +338,8 @@ def cpu_path(cfg, g, t, ah, counts=False, high_order=True):
         r, c, cnt, mq = orc.pairs_edges(t["chrom1"], t["chrom2"], t["mapq"], min_mapq=PARAMS["min_mapq"], n_contigs=g.n)
     else:
         r, c, cnt, mq = orc.porec_edges(t["read_idx"], t["contig_idx"], t["mapq"], min_mapq=PARAMS["min_mapq"],
-                                        min_order=PARAMS["min_order"], max_order=PARAMS["max_order"], n_contigs=g.n)
+                                        min_order=PARAMS["min_order"], max_order=PARAMS["max_order"], n_contigs=g.n,
+                                        **edge_filter_args(cfg, g, t))
     tm["triplets"] = time.perf_counter() - t0; t0 = time.perf_counter()
     if ah is not None:
         edges = ah.HyperEdges(idx=g.contig_idx, row=r, col=c, count=cnt, contigsizes=g.contigsizes, mapq=mq)
@@ -378,7 +401,8 @@ def parity_check(D, cfg, g, host, dev_t, H_cpu, A_cpu, ah):
         raw = D.pairs_to_edges(dev_t["chrom1"], dev_t["chrom2"], dev_t["mapq"], g.n, min_mapq=PARAMS["min_mapq"])
     else:
         raw = D.porec_to_edges(dev_t["read_idx"], dev_t["contig_idx"], dev_t["mapq"], g.n, min_mapq=PARAMS["min_mapq"],
-                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"])
+                               min_order=PARAMS["min_order"], max_order=PARAMS["max_order"],
+                               **edge_filter_args(cfg, g, dev_t, dev_t["mapq"].device))
     H = D.incidence(raw, min_contacts=PARAMS["min_contacts"], min_mapq=0)
     Hs = _canon(csr_matrix(((D.to_host(H.pk).view(np.uint32) & 0xFFFFFF).astype(np.float32), D.to_host(H.indices),
                             D.to_host(H.indptr)), shape=(H.n_rows, H.n_cols)))
@@ -491,20 +515,21 @@ def timed_run(D, _lib, name, cfg, g, t, steps, warmup, world, rank, local, dev, 
     nnzH, nnzA, n_rows = H.nnz, A.nnz, H.n_rows
     acc_ms = stages.get("accumulate", float("nan"))
     edges_ms = stages.get("edges", float("nan"))
-    stage1_bytes = 9 * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
+    rec_b = 17 if cfg.get("edge_length") else 9        # + start, end (u32 each) when the edge filter reads them
+    stage1_bytes = rec_b * n_rec + 8 * raw.nnz + 8 * (g.n + 1)
     stage2_bytes = 8 * nnzH + 4 * H.n_cols + 12 * nnzA + 16 * (n_rows + 1)
     s1_ms = stages.get("edges", 0) + stages.get("incidence", 0)
     s2_ms = stages.get("accumulate", 0) + stages.get("emit", 0)
     xname = "expansion kernel(s) (cph_expand_accumulate_*)"
     per_kernel = {xname: {"bytes": 8 * nnzH, "ms": acc_ms, "GBps": 8 * nnzH / acc_ms / 1e6, "frac": 8 * nnzH / acc_ms / 1e6 / peak}}
     gname = "porec_tile_kernel (cph_porec_to_edges)" if cfg["kind"] != "pairs" else "pairs_flag/emit_kernel (cph_pairs_to_edges)"
-    per_kernel[gname] = {"bytes": 9 * n_rec + 8 * raw.nnz, "ms": edges_ms, "GBps": (9 * n_rec + 8 * raw.nnz) / edges_ms / 1e6,
-                         "frac": (9 * n_rec + 8 * raw.nnz) / edges_ms / 1e6 / peak}
+    per_kernel[gname] = {"bytes": rec_b * n_rec + 8 * raw.nnz, "ms": edges_ms, "GBps": (rec_b * n_rec + 8 * raw.nnz) / edges_ms / 1e6,
+                         "frac": (rec_b * n_rec + 8 * raw.nnz) / edges_ms / 1e6 / peak}
     traffic = None
     if cfg["kind"] == "pairs" or acc_ms > edges_ms:
         kname, kbytes, kms = xname, 8 * nnzH, acc_ms
     else:
-        kname, kbytes, kms = gname, 9 * n_rec + 8 * raw.nnz, edges_ms
+        kname, kbytes, kms = gname, rec_b * n_rec + 8 * raw.nnz, edges_ms
         # ncu --set full, one launch on this workload: dram__bytes_read + dram__bytes_write (profiles/)
         traffic = NCU_TRAFFIC.get((name, cfg["m"]))
     roof = {"bound": "hbm", "kernel": kname, "achieved": kbytes / kms / 1e6, "peak": peak, "unit": "GB/s",
@@ -518,7 +543,8 @@ def timed_run(D, _lib, name, cfg, g, t, steps, warmup, world, rank, local, dev, 
            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u64 fixed-point / f64",
            "data": "synthetic", "gpu_launches": launches,
            "config": {"workload": f"{name}: n={cfg['n']} contigs, m={cfg['m']} concatemers/GPU x {world} GPU, law={cfg['law']}, "
-                                  f"kind={cfg['kind']}", "records_per_gpu": n_rec, "nnz_H": nnzH, "nnz_A": nnzA,
+                                  f"kind={cfg['kind']}" + (f", edge_length={cfg['edge_length']}" if cfg.get("edge_length") else ""),
+                      "records_per_gpu": n_rec, "nnz_H": nnzH, "nnz_A": nnzA,
                       "params": PARAMS, "l2": "inputs (>2 GB) and intermediates exceed the 126 MB L2; no flush needed",
                       "parallelism": f"concatemer-column shards x{world}" if world > 1 else "single GPU"},
            "stages_ms": stages, "roofline": roof, "clocks": clk}
@@ -659,7 +685,9 @@ def run_own(args):
         _lib.release_workspace(); torch.cuda.empty_cache()
         extra = {}
         for xn in args.extra.split(","):
-            xcfg = dict(synth.CONFIGS[xn])
+            xcfg = dict(synth.CONFIGS["C" if xn == "Cf" else xn])
+            if xn == "Cf":                 # workload C with the reference's DEFAULT extraction filter (--edge-length 5m)
+                xcfg["edge_length"] = 5_000_000
             if xn in ("D", "E"):
                 xcfg["m"] = xcfg["m"] // 8
             try:
@@ -682,7 +710,7 @@ def run_own(args):
                     parity_ok = parity_ok and xpar["ok"]
                     del xhost, xdev, xHc, xAc
                 del xt
-                if not args.no_partition and xcfg["kind"] != "pairs":      # the tail needs an allele table: Pore-C configs only
+                if not args.no_partition and xcfg["kind"] != "pairs" and xn != "Cf":   # tail: Pore-C configs (Cf would repeat C's)
                     tail = partition_tail(D, xcfg, xg, xH, xA, reps=1, world=world, rank=rank)
                     barrier()
                     if rank == 0:
